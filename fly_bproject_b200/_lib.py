@@ -1,0 +1,109 @@
+"""ctypes binding of libflyb200.so (the C ABI declared in include/flyb200.h).
+
+The product path has no CPU implementation: `lib()` raises when the shared object is missing, and every compute
+call raises `FlybError` when the library reports a failure (no CUDA device, bad argument, launch error).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+MAX_DOF = 64
+NUM_ABDOMEN = 5
+NUM_LEGTIPS = 6
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libflyb200.so")
+
+
+class FlybError(RuntimeError):
+    pass
+
+
+class EnvCfg(C.Structure):
+    _fields_ = [
+        ("num_envs", C.c_int32), ("num_dof", C.c_int32), ("num_act", C.c_int32), ("num_bodies", C.c_int32),
+        ("action_idx", C.c_int32 * MAX_DOF),
+        ("abdomen_local", C.c_int32 * NUM_ABDOMEN), ("legtip_local", C.c_int32 * NUM_LEGTIPS),
+        ("lower", C.c_float * MAX_DOF), ("upper", C.c_float * MAX_DOF),
+        ("initial_pos", C.c_float * MAX_DOF), ("initial_vel", C.c_float * MAX_DOF),
+        ("origin_root", C.c_float * 13), ("target", C.c_float * 3), ("inv_start_rot", C.c_float * 4),
+        ("basis0", C.c_float * 3), ("basis1", C.c_float * 3),
+        ("dt", C.c_float), ("dof_vel_scale", C.c_float), ("heading_weight", C.c_float), ("up_weight", C.c_float),
+        ("actions_cost_scale", C.c_float), ("energy_cost_scale", C.c_float),
+        ("joints_at_limit_cost_scale", C.c_float), ("death_cost", C.c_float), ("termination_height", C.c_float),
+        ("termination_height_up", C.c_float), ("max_episode_length", C.c_float), ("walking", C.c_int32),
+    ]
+
+
+class NetLayout(C.Structure):
+    _fields_ = [("num_obs", C.c_int32), ("num_act", C.c_int32), ("k0_pad", C.c_int32), ("total", C.c_int32),
+                ("off", C.c_int32 * 12)]
+
+
+class PpoCfg(C.Structure):
+    _fields_ = [("clip", C.c_float), ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
+                ("eps", C.c_float), ("max_grad_norm", C.c_float)]
+
+
+_P = C.c_void_p
+# name -> (restype, argtypes); must list every symbol include/flyb200.h declares (tests check this)
+SIGNATURES = {
+    "flyb_abi_version": (C.c_int, []),
+    "flyb_last_error": (C.c_char_p, []),
+    "flyb_device_count": (C.c_int, []),
+    "flyb_net_layout": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(NetLayout)]),
+    "flyb_env_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 18),
+    "flyb_env_pre_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 10),
+    "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64,
+                                  _P, _P, _P, _P, C.POINTER(EnvCfg)] + [_P] * 9),
+    "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.c_int64, _P, _P, _P]),
+    "flyb_gae": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, _P]),
+    "flyb_ppo_workspace_bytes": (C.c_size_t, [C.POINTER(NetLayout), C.c_int64]),
+    "flyb_ppo_grad": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 7 + [C.c_int64] + [_P] * 4),
+    "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5 + [C.c_float, _P, _P]),
+    "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libflyb200.so once.  Raises (never falls back) when it is missing or lacks a declared symbol."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FlybError(
+                f"{LIB_PATH} not found: build it with `python -m fly_bproject_b200.build` "
+                "(__graft_entry__.build()).  flyb200 has no CPU or PyTorch fallback.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (restype, argtypes) in SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError if the .so does not export it
+            fn.restype = restype
+            fn.argtypes = argtypes
+        if handle.flyb_abi_version() != 1:
+            raise FlybError("libflyb200.so ABI version mismatch")
+        _lib = handle
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = lib().flyb_last_error().decode("utf-8", "replace")
+        raise FlybError(f"{what or 'flyb200'} failed ({rc}): {msg}")
+
+
+def ptr(t) -> int | None:
+    """Device pointer of a torch tensor (None -> NULL).  Tensors must be contiguous CUDA tensors."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise FlybError("flyb200 kernels take CUDA tensors only (no CPU fallback); got a CPU tensor")
+    if not t.is_contiguous():
+        raise FlybError("flyb200 kernels take contiguous tensors")
+    return t.data_ptr()
+
+
+def current_stream() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream

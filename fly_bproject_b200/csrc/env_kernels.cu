@@ -1,0 +1,338 @@
+// Kernel (a): fused observation + reward + termination + reset-id compaction, and the pre-physics half of
+// Fly.step (action scaling, DOF-target scatter, reset bookkeeping).
+//
+// Replaces reference fly.py:397-443, 446-480, 624-660, 676-681 and the two TorchScript functions
+// compute_fly_observations (771-805) / compute_fly_reward2 (685-768): ~385 aten launches per step in the
+// reference become one launch each side of the physics step.
+//
+// Data movement (HBM-bound; algorithmic bytes per env-step in DESIGN.md):
+//   * one CTA owns ENVS consecutive envs; every global access is a flat, coalesced sweep over the CTA's
+//     contiguous slab (root rows, actuated DOF pairs, action rows, obs rows) — rows are 52 / 292 bytes, so
+//     per-thread row access would be misaligned; slabs are staged in shared memory instead and obs rows
+//     leave as full 128-bit stores;
+//   * the 11 contact-force rows an env needs (5 abdomen + 6 leg tips out of 93 bodies) are gathered with a
+//     flat (env, row, component) index so that a warp touches ~11 sectors per request instead of 32;
+//   * reset ids are compacted in ascending order (== torch.nonzero) inside the same launch: warp ballot ->
+//     CTA prefix -> decoupled look-back across CTAs (ticketed, so forward progress never depends on
+//     residency); the count stays on the device — the reference's host sync at fly.py:447-450 is gone.
+#include "env_math.cuh"
+
+namespace flyb {
+
+constexpr int ENVS = 128;          // envs per CTA == threads per CTA
+
+// look-back status word: [63:32] flag (0 none, 1 aggregate, 2 inclusive prefix), [31:0] value
+struct ScanScratch {
+  unsigned int ticket;
+  unsigned int done;
+  unsigned long long status[1];
+};
+
+FLYB_D unsigned long long ld_status(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+FLYB_D void st_status(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(ENVS)
+post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restrict__ root,
+                    const float* __restrict__ dof_state, const float* __restrict__ force,
+                    const float* __restrict__ actions_scaled, float* __restrict__ potentials,
+                    float* __restrict__ prev_potentials, long long* __restrict__ progress,
+                    long long* __restrict__ reset, float* __restrict__ obs, float* __restrict__ reward,
+                    float* __restrict__ up_vec, float* __restrict__ heading_vec, int* __restrict__ reset_ids,
+                    int* __restrict__ reset_count, ScanScratch* __restrict__ scratch, float* __restrict__ obs_copy,
+                    float* __restrict__ reward_copy) {
+  extern __shared__ __align__(16) float smem[];
+  const int N = cfg.num_envs, D = cfg.num_dof, A = cfg.num_act, B = cfg.num_bodies;
+  const int O = 19 + 3 * A;
+  float* obs_s = smem;                        // [ENVS][O]      (O is odd -> conflict-free row access)
+  float* root_s = obs_s + ENVS * O;           // [ENVS][13]
+  float* force_s = root_s + ENVS * 13;        // [ENVS][33]
+  __shared__ int s_block;                     // ticket = logical CTA id
+  __shared__ int s_warp_cnt[ENVS / 32];
+  __shared__ int s_excl;
+
+  const int tid = threadIdx.x;
+  if (tid == 0) s_block = (int)atomicAdd(&scratch->ticket, 1u);
+  __syncthreads();
+  const int blk = s_block;
+  const int env0 = blk * ENVS;
+  const int nenv = min(ENVS, N - env0);
+
+  // ---- stage root slab (contiguous nenv*13 floats; slab base is 16B aligned since ENVS*52 % 16 == 0)
+  {
+    const float* src = root + (size_t)env0 * 13;
+    const int n = nenv * 13;
+    const int n4 = n >> 2;
+    const float4* src4 = reinterpret_cast<const float4*>(src);
+    for (int i = tid; i < n4; i += ENVS) reinterpret_cast<float4*>(root_s)[i] = ldg_stream4(src4 + i);
+    for (int i = (n4 << 2) + tid; i < n; i += ENVS) root_s[i] = __ldg(src + i);
+  }
+  // ---- contact-force gather: flat (env, row, comp)
+  {
+    const int n = nenv * FORCE_VALS;
+    for (int i = tid; i < n; i += ENVS) {
+      const int e = i / FORCE_VALS;
+      const int rc = i - e * FORCE_VALS;
+      const int r = rc / 3;
+      const int comp = rc - r * 3;
+      const int body = (r < FLYB_NUM_ABDOMEN) ? cfg.abdomen_local[r] : cfg.legtip_local[r - FLYB_NUM_ABDOMEN];
+      force_s[i] = __ldg(force + ((size_t)(env0 + e) * B + body) * 3 + comp);
+    }
+  }
+  // ---- actuated DOF (pos, vel) pairs -> obs[12 : 12+A], obs[12+A : 12+2A]   (fly.py:795, 801)
+  {
+    const float2* dof2 = reinterpret_cast<const float2*>(dof_state);
+    const int n = nenv * A;
+    for (int i = tid; i < n; i += ENVS) {
+      const int e = i / A;
+      const int k = i - e * A;
+      const int d = cfg.action_idx[k];
+      const float2 pv = __ldg(dof2 + (size_t)(env0 + e) * D + d);
+      obs_s[e * O + 12 + k] = unscale(pv.x, cfg.lower[d], cfg.upper[d]);
+      obs_s[e * O + 12 + A + k] = pv.y * cfg.dof_vel_scale;
+      obs_s[e * O + 12 + 2 * A + k] = __ldg(actions_scaled + (size_t)env0 * A + i);  // fly.py:802
+    }
+  }
+  __syncthreads();
+
+  // ---- per-env math: one thread per env
+  bool flag = false;
+  if (tid < nenv) {
+    const int env = env0 + tid;
+    float r[13];
+#pragma unroll
+    for (int j = 0; j < 13; ++j) r[j] = root_s[tid * 13 + j];
+    const EnvStepOut out = env_post_one(cfg, r, force_s + tid * FORCE_VALS, obs_s + tid * O, potentials[env],
+                                        progress[env], reset[env]);
+    potentials[env] = out.potential;
+    prev_potentials[env] = out.prev_potential;
+    progress[env] = out.progress;
+    reset[env] = out.reset;
+    reward[env] = out.reward;
+    if (reward_copy) reward_copy[env] = out.reward;
+    up_vec[env * 3 + 0] = out.up_vec.x; up_vec[env * 3 + 1] = out.up_vec.y; up_vec[env * 3 + 2] = out.up_vec.z;
+    heading_vec[env * 3 + 0] = out.heading_vec.x; heading_vec[env * 3 + 1] = out.heading_vec.y;
+    heading_vec[env * 3 + 2] = out.heading_vec.z;
+    flag = out.reset != 0;
+  }
+
+  // ---- reset-id compaction, ascending: ballot -> CTA prefix -> look-back across CTAs
+  const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+  const int lane = tid & 31, warp = tid >> 5;
+  if (lane == 0) s_warp_cnt[warp] = __popc(ballot);
+  __syncthreads();
+  int warp_off = 0, block_cnt = 0;
+#pragma unroll
+  for (int w = 0; w < ENVS / 32; ++w) {
+    if (w < warp) warp_off += s_warp_cnt[w];
+    block_cnt += s_warp_cnt[w];
+  }
+  if (warp == 0) {
+    unsigned long long* status = scratch->status;
+    int excl = 0;
+    if (blk == 0) {
+      if (lane == 0) st_status(status, (2ull << 32) | (unsigned)block_cnt);
+    } else {
+      if (lane == 0) st_status(status + blk, (1ull << 32) | (unsigned)block_cnt);
+      int look = blk - 1;  // lane l inspects CTA (look - l)
+      while (true) {
+        const int idx = look - lane;
+        unsigned long long st = 2ull << 32;  // lanes before CTA 0 act as a zero-valued inclusive prefix
+        if (idx >= 0) {
+          do { st = ld_status(status + idx); } while ((st >> 32) == 0ull);
+        }
+        const unsigned has_prefix = __ballot_sync(0xffffffffu, (st >> 32) == 2ull);
+        const int first = __ffs(has_prefix) - 1;  // nearest predecessor that already holds an inclusive prefix
+        int v = (first < 0 || lane <= first) ? (int)(unsigned)(st & 0xffffffffull) : 0;
+#pragma unroll
+        for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
+        excl += v;
+        if (first >= 0) break;
+        look -= 32;
+      }
+      if (lane == 0) st_status(status + blk, (2ull << 32) | (unsigned)(excl + block_cnt));
+    }
+    if (lane == 0) {
+      s_excl = excl;
+      if (env0 + ENVS >= N) *reset_count = excl + block_cnt;  // the CTA that owns the last env
+    }
+  }
+  __syncthreads();
+  if (flag) {
+    const int pos = s_excl + warp_off + __popc(ballot & ((1u << lane) - 1u));
+    reset_ids[pos] = env0 + tid;
+  }
+
+  // ---- obs slab out: full 128-bit stores (slab base 16B aligned: ENVS*O*4 % 16 == 0)
+  {
+    const int n = nenv * O;
+    const int n4 = n >> 2;
+    float4* dst4 = reinterpret_cast<float4*>(obs + (size_t)env0 * O);
+    float4* cpy4 = obs_copy ? reinterpret_cast<float4*>(obs_copy + (size_t)env0 * O) : nullptr;
+    for (int i = tid; i < n4; i += ENVS) {
+      const float4 v = reinterpret_cast<const float4*>(obs_s)[i];
+      dst4[i] = v;
+      if (cpy4) stg_stream4(cpy4 + i, v);
+    }
+    for (int i = (n4 << 2) + tid; i < n; i += ENVS) {
+      obs[(size_t)env0 * O + i] = obs_s[i];
+      if (obs_copy) obs_copy[(size_t)env0 * O + i] = obs_s[i];
+    }
+  }
+
+  // ---- self-cleaning scratch: the last CTA to finish re-arms ticket / status for the next launch
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    const unsigned nblk = gridDim.x;
+    const unsigned prev = atomicAdd(&scratch->done, 1u);
+    s_block = (prev == nblk - 1) ? 1 : 0;
+  }
+  __syncthreads();
+  if (s_block) {
+    for (int i = tid; i < (int)gridDim.x; i += ENVS) scratch->status[i] = 0ull;
+    if (tid == 0) {
+      scratch->ticket = 0u;
+      scratch->done = 0u;
+    }
+  }
+}
+
+// Pre-physics half of Fly.step (fly.py:626-660): one thread per (env, dof) element for the target vector,
+// reset bookkeeping by the threads that own an env's first DOF.
+__global__ void __launch_bounds__(256)
+pre_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restrict__ actions,
+                   float* __restrict__ actions_scaled, float* __restrict__ dof_targets,
+                   long long* __restrict__ reset, long long* __restrict__ progress, float* __restrict__ potentials,
+                   float* __restrict__ prev_potentials, float* __restrict__ root, float* __restrict__ dof_state) {
+  __shared__ int s_slot[FLYB_MAX_DOF];  // dof -> action slot or -1
+  const int D = cfg.num_dof, A = cfg.num_act;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    int slot = -1;
+    for (int k = 0; k < A; ++k)
+      if (cfg.action_idx[k] == d) slot = k;
+    s_slot[d] = slot;
+  }
+  __syncthreads();
+  const size_t total = (size_t)cfg.num_envs * D;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int env = (int)(i / D);
+    const int d = (int)(i - (size_t)env * D);
+    const int k = s_slot[d];
+    float tgt = cfg.initial_pos[d];                                  // fly.py:626
+    if (k >= 0) {
+      const float a = __ldg(actions + (size_t)env * A + k);
+      tgt = scale_action(a, cfg.lower[d], cfg.upper[d]);             // fly.py:629-630
+      actions_scaled[(size_t)env * A + k] = tgt;                     // fly.py:633-636
+    }
+    dof_targets[i] = tgt;                                            // fly.py:648-651
+    if (reset[env] != 0) {                                           // fly.py:446-480
+      reinterpret_cast<float2*>(dof_state)[i] = make_float2(cfg.initial_pos[d], cfg.initial_vel[d]);
+      if (d < 13) root[(size_t)env * 13 + d] = cfg.origin_root[d];
+      if (D < 13 && d == 0)
+        for (int j = D; j < 13; ++j) root[(size_t)env * 13 + j] = cfg.origin_root[j];
+    }
+  }
+  // the masks are cleared by pre_physics_finish_kernel: an env's DOF elements may span two CTAs, so the
+  // bookkeeping has to wait for a launch boundary
+}
+
+__global__ void __launch_bounds__(256)
+pre_physics_finish_kernel(const __grid_constant__ FlybEnvCfg cfg, long long* __restrict__ reset,
+                          long long* __restrict__ progress, float* __restrict__ potentials,
+                          float* __restrict__ prev_potentials) {
+  const int env = blockIdx.x * blockDim.x + threadIdx.x;
+  if (env >= cfg.num_envs) return;
+  if (reset[env] != 0) {
+    const float tx = cfg.target[0] - cfg.origin_root[0];
+    const float ty = cfg.target[1] - cfg.origin_root[1];
+    const float p = -sqrtf(tx * tx + ty * ty + 0.0f) / cfg.dt;       // fly.py:470-473
+    prev_potentials[env] = p;
+    potentials[env] = p;
+    reset[env] = 0;                                                  // fly.py:476-477
+    progress[env] = 0;
+  }
+}
+
+}  // namespace flyb
+
+using namespace flyb;
+
+extern "C" size_t flyb_env_scratch_bytes(int32_t num_envs) {
+  const size_t nblk = num_envs > 0 ? (size_t)(num_envs + ENVS - 1) / ENVS : 1;
+  return 16 + nblk * sizeof(unsigned long long);
+}
+
+static int validate_cfg(const FlybEnvCfg* cfg) {
+  FLYB_REQUIRE(cfg != nullptr, "cfg is NULL");
+  FLYB_REQUIRE(cfg->num_envs > 0, "num_envs must be > 0 (got %d)", cfg->num_envs);
+  FLYB_REQUIRE(cfg->num_dof > 0 && cfg->num_dof <= FLYB_MAX_DOF, "num_dof %d out of (0, %d]", cfg->num_dof, FLYB_MAX_DOF);
+  FLYB_REQUIRE(cfg->num_act > 0 && cfg->num_act <= cfg->num_dof, "num_act %d out of (0, num_dof]", cfg->num_act);
+  FLYB_REQUIRE(cfg->num_bodies > 0, "num_bodies must be > 0");
+  for (int k = 0; k < cfg->num_act; ++k) {
+    FLYB_REQUIRE(cfg->action_idx[k] >= 0 && cfg->action_idx[k] < cfg->num_dof, "action_idx[%d] out of range", k);
+    FLYB_REQUIRE(k == 0 || cfg->action_idx[k] > cfg->action_idx[k - 1], "action_idx must be strictly ascending");
+  }
+  for (int b = 0; b < FLYB_NUM_ABDOMEN; ++b)
+    FLYB_REQUIRE(cfg->abdomen_local[b] >= 0 && cfg->abdomen_local[b] < cfg->num_bodies, "abdomen_local[%d] out of range", b);
+  for (int b = 0; b < FLYB_NUM_LEGTIPS; ++b)
+    FLYB_REQUIRE(cfg->legtip_local[b] >= 0 && cfg->legtip_local[b] < cfg->num_bodies, "legtip_local[%d] out of range", b);
+  return FLYB_OK;
+}
+
+extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, const float* dof_state,
+                                     const float* force, const float* actions_scaled, float* potentials,
+                                     float* prev_potentials, int64_t* progress, int64_t* reset, float* obs,
+                                     float* reward, float* up_vec, float* heading_vec, int32_t* reset_ids,
+                                     int32_t* reset_count, void* scratch, float* obs_copy, float* reward_copy,
+                                     void* stream) {
+  int rc = validate_cfg(cfg);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(root && dof_state && force && actions_scaled && potentials && prev_potentials && progress && reset &&
+                   obs && reward && up_vec && heading_vec && reset_ids && reset_count && scratch,
+               "flyb_env_post_physics: NULL buffer");
+  FLYB_REQUIRE(aligned16(root) && aligned16(obs) && aligned16(dof_state) && (!obs_copy || aligned16(obs_copy)),
+               "flyb_env_post_physics: root/dof_state/obs must be 16-byte aligned");
+  const int O = 19 + 3 * cfg->num_act;
+  const size_t smem = (size_t)ENVS * (O + 13 + FORCE_VALS) * sizeof(float);
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    rc = check_cuda(cudaFuncSetAttribute(post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                    "cudaFuncSetAttribute(post_physics_kernel)");
+    if (rc != FLYB_OK) return rc;
+    smem_set = smem;
+  }
+  const int grid = (cfg->num_envs + ENVS - 1) / ENVS;
+  post_physics_kernel<<<grid, ENVS, smem, (cudaStream_t)stream>>>(
+      *cfg, root, dof_state, force, actions_scaled, potentials, prev_potentials, (long long*)progress,
+      (long long*)reset, obs, reward, up_vec, heading_vec, reset_ids, reset_count, (ScanScratch*)scratch, obs_copy,
+      reward_copy);
+  FLYB_LAUNCH_CHECK("post_physics_kernel");
+  return FLYB_OK;
+}
+
+extern "C" int flyb_env_pre_physics(const FlybEnvCfg* cfg, const float* actions, float* actions_scaled,
+                                    float* dof_targets, int64_t* reset, int64_t* progress, float* potentials,
+                                    float* prev_potentials, float* root, float* dof_state, void* stream) {
+  int rc = validate_cfg(cfg);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(actions && actions_scaled && dof_targets && reset && progress && potentials && prev_potentials &&
+                   root && dof_state,
+               "flyb_env_pre_physics: NULL buffer");
+  FLYB_REQUIRE((reinterpret_cast<uintptr_t>(dof_state) & 7u) == 0, "dof_state must be 8-byte aligned");
+  const size_t total = (size_t)cfg->num_envs * cfg->num_dof;
+  const int grid = (int)((total + 255) / 256);
+  pre_physics_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*cfg, actions, actions_scaled, dof_targets,
+                                                            (long long*)reset, (long long*)progress, potentials,
+                                                            prev_potentials, root, dof_state);
+  FLYB_LAUNCH_CHECK("pre_physics_kernel");
+  pre_physics_finish_kernel<<<(cfg->num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      *cfg, (long long*)reset, (long long*)progress, potentials, prev_potentials);
+  FLYB_LAUNCH_CHECK("pre_physics_finish_kernel");
+  return FLYB_OK;
+}

@@ -1,0 +1,173 @@
+/*
+ * flyb200 — C ABI of the B200-native fly_bProject hot path (libflyb200.so).
+ *
+ * The reference (petim0/fly_bProject) is pure Python: it has no plugin / FFI
+ * of its own.  Its boundary for this path is two duck-typed classes,
+ * `Fly` (reference fly.py:10-808) and `PPO` (reference ppo.py:105-279), whose
+ * tensor math the entry points below replace one-for-one.  Every entry point
+ * takes plain DEVICE pointers and sizes (no torch types), launches on the CUDA
+ * stream passed as `stream` (a cudaStream_t cast to void*; NULL = legacy default
+ * stream), never synchronises the host and allocates nothing: the caller owns
+ * every buffer, exactly as the reference's in-place `self.obs_buf[:] = ...`
+ * convention requires for Isaac Gym's wrapped views (fly.py:405, 418).
+ *
+ * Return value: 0 on success, a negative FLYB_E* code otherwise;
+ * flyb_last_error() gives the message (thread-local).  There is no CPU
+ * fallback: without a CUDA device every compute entry point fails.
+ *
+ * All floating tensors are fp32, masks/counters are int64 as in the
+ * reference API (fly.py:169-179), compacted env ids are int32 as the Isaac Gym
+ * `_indexed` setters take them (fly.py:457-468).
+ */
+#ifndef FLYB200_H_
+#define FLYB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLYB_ABI_VERSION 1
+#define FLYB_MAX_DOF 64      /* asset DOF count D: 18 (nmf_no_limits_limited_Dofs.urdf) or 42 (nmf_no_limits.urdf) */
+#define FLYB_NUM_ABDOMEN 5   /* reference fly.py:299 */
+#define FLYB_NUM_LEGTIPS 6   /* reference fly.py:300 */
+
+#define FLYB_OK 0
+#define FLYB_EINVAL (-1)     /* bad argument (null pointer, size, alignment) */
+#define FLYB_ECUDA (-2)      /* CUDA runtime error (no device, launch failure) */
+#define FLYB_EUNSUPPORTED (-3)
+
+/* Constants and index tables `Fly.__init__` derives (reference fly.py:16-51, 248-348).
+ * Per-env constant tensors of the reference (targets, inv_start_rot, basis vectors, origin root row,
+ * initial_dofs: fly.py:121-135, 318-348) hold the same row for every env and are passed as that row. */
+typedef struct FlybEnvCfg {
+  int32_t num_envs;                       /* N */
+  int32_t num_dof;                        /* D  = gym.get_asset_dof_count (fly.py:200) */
+  int32_t num_act;                        /* A  = len(names) (fly.py:31) */
+  int32_t num_bodies;                     /* B  = gym.get_asset_rigid_body_count (fly.py:201), 93 */
+  int32_t action_idx[FLYB_MAX_DOF];       /* sorted DOF ids of the actuated joints, `action_indexes_one` (fly.py:288-290) */
+  int32_t abdomen_local[FLYB_NUM_ABDOMEN];/* body ids of A1A2,A3..A6 inside one env, sorted (fly.py:303-314) */
+  int32_t legtip_local[FLYB_NUM_LEGTIPS]; /* body ids of the six Tarsus5 links inside one env, sorted */
+  float lower[FLYB_MAX_DOF];              /* dof_limits_lower (fly.py:258-267) */
+  float upper[FLYB_MAX_DOF];              /* dof_limits_upper */
+  float initial_pos[FLYB_MAX_DOF];        /* initial_dofs_one[:,0] (fly.py:318-336) */
+  float initial_vel[FLYB_MAX_DOF];        /* initial_dofs_one[:,1] */
+  float origin_root[13];                  /* origin_root_tensor row (fly.py:338-348) */
+  float target[3];                        /* targets row (fly.py:134) */
+  float inv_start_rot[4];                 /* fly.py:129 */
+  float basis0[3];                        /* heading_vec / basis_vec0 (fly.py:127,131) */
+  float basis1[3];                        /* up_vec / basis_vec1 (fly.py:125,132) */
+  float dt;                               /* fly.py:16 */
+  float dof_vel_scale;                    /* fly.py:43 */
+  float heading_weight;                   /* fly.py:44 */
+  float up_weight;                        /* fly.py:45 */
+  float actions_cost_scale;               /* fly.py:46 */
+  float energy_cost_scale;                /* fly.py:47 */
+  float joints_at_limit_cost_scale;       /* fly.py:48 */
+  float death_cost;                       /* fly.py:49 */
+  float termination_height;               /* fly.py:50 */
+  float termination_height_up;            /* fly.py:51 */
+  float max_episode_length;               /* fly.py:34 */
+  int32_t walking;                        /* 0: live standing total (fly.py:750); 1: walking total (fly.py:747-748 + leg term) */
+} FlybEnvCfg;
+
+/* Actor-critic net (reference ppo.py:10-38): trunk O->256->128, mean head 128->64->A (ELU after every layer,
+ * the last one included), value head 128->64->1.  Parameters live in ONE flat fp32 device buffer so that the
+ * gradient all-reduce, the global-norm clip and Adam see a single array.  Segment order is the reference's
+ * `state_dict` order; the first weight matrix is stored with its rows padded from O to `k0_pad` floats and
+ * every segment starts on a 16-byte boundary (padding holds zeros and receives zero gradient). */
+typedef struct FlybNetLayout {
+  int32_t num_obs;     /* O */
+  int32_t num_act;     /* A */
+  int32_t k0_pad;      /* O rounded up to a multiple of 16 */
+  int32_t total;       /* floats in the flat buffer (multiple of 4) */
+  int32_t off[12];     /* shared_net.0.{weight,bias}, shared_net.2.{..}, to_mean.0, to_mean.2, to_value.0, to_value.2 */
+} FlybNetLayout;
+
+/* PPO hyper-parameters (reference ppo.py:113-119, 155). */
+typedef struct FlybPpoCfg {
+  float clip;          /* 0.2 */
+  float lr;            /* 1e-3 */
+  float beta1, beta2;  /* 0.9, 0.999 */
+  float eps;           /* 1e-8 */
+  float max_grad_norm; /* 1.0 (ppo.py:198) */
+} FlybPpoCfg;
+
+int flyb_abi_version(void);
+const char* flyb_last_error(void);
+/* Number of CUDA devices visible, or a negative code. */
+int flyb_device_count(void);
+
+int flyb_net_layout(int32_t num_obs, int32_t num_act, FlybNetLayout* out);
+
+/* ---- env, kernel (a): reference Fly.get_obs + progress_buf += 1 + Fly.get_reward
+ *      (fly.py:397-443, 676-681 -> compute_fly_observations 771-805, compute_fly_reward2 685-768).
+ * In:  root (N,13), dof_state (N,D,2), force (N*B,3), actions_scaled (N,A) = `self.actions` (fly.py:636).
+ * In/out: potentials, prev_potentials (N), progress (N) i64, reset (N) i64.
+ * Out: obs (N,O), reward (N), up_vec/heading_vec (N,3), reset_ids (N) i32 = ascending ids of envs whose reset
+ *      mask is now set (what `reset_buf.nonzero()` yields at fly.py:447, compacted on the device),
+ *      reset_count (1) i32.  obs_copy / reward_copy (nullable) receive a second copy (rollout rows, ppo.py:228-229).
+ * scratch: flyb_env_scratch_bytes(N) bytes, zeroed once by the caller before first use. */
+size_t flyb_env_scratch_bytes(int32_t num_envs);
+int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, const float* dof_state, const float* force,
+                          const float* actions_scaled, float* potentials, float* prev_potentials, int64_t* progress,
+                          int64_t* reset, float* obs, float* reward, float* up_vec, float* heading_vec,
+                          int32_t* reset_ids, int32_t* reset_count, void* scratch, float* obs_copy,
+                          float* reward_copy, void* stream);
+
+/* ---- env: reference Fly.step up to simulate() (fly.py:626-660): scale policy actions to the joint range,
+ *      scatter into the DOF position-target vector, then Fly.reset() (fly.py:446-480) for envs whose mask is set.
+ * In:  actions (N,A) in [-1,1].  Out: actions_scaled (N,A), dof_targets (N*D).
+ * In/out (reset): reset, progress, potentials, prev_potentials, root (N,13), dof_state (N,D,2). */
+int flyb_env_pre_physics(const FlybEnvCfg* cfg, const float* actions, float* actions_scaled, float* dof_targets,
+                         int64_t* reset, int64_t* progress, float* potentials, float* prev_potentials, float* root,
+                         float* dof_state, void* stream);
+
+/* ---- agent, kernel (b): reference PPO.run act block (ppo.py:213-220): mu = Net.pi(obs); a = mu + sqrt(var)*eps;
+ *      logp = MVN(mu, diag(var)).log_prob(a); a = clip(a,-1,1) — optionally fused with flyb_env_pre_physics
+ *      (pass cfg != NULL and the env buffers) so that one launch covers act + Fly.step's pre-physics half.
+ * noise (rows,A) nullable: explicit eps (parity mode); NULL -> in-kernel Philox4x32-10 keyed by (seed, offset).
+ * Out: action (rows,A) clipped, logp (rows); mu_out, obs_store (rollout all_obs row, ppo.py:226) nullable. */
+int flyb_policy_act(const FlybNetLayout* net, const float* params, const float* obs, int64_t rows,
+                    const float* action_var, const float* noise, uint64_t seed, uint64_t offset, float* action,
+                    float* logp, float* mu_out, float* obs_store, const FlybEnvCfg* cfg, float* actions_scaled,
+                    float* dof_targets, int64_t* reset, int64_t* progress, float* potentials,
+                    float* prev_potentials, float* root, float* dof_state, void* stream);
+
+/* Net.pi / Net.v forward over `rows` observation rows (ppo.py:88-102). mu_out (rows,A) / value_out (rows) nullable. */
+int flyb_net_forward(const FlybNetLayout* net, const float* params, const float* obs, int64_t rows, float* mu_out,
+                     float* value_out, void* stream);
+
+/* ---- agent, kernel (c): reference PPO.make_data scan (ppo.py:160-169).
+ * values (T+1,N): values[t] = v(all_obs[t]) for t<T and values[T] = v(all_next_obs[T-1]); all_next_obs[t] is
+ * all_obs[t+1] for t<T-1 (ppo.py:210,228), so one value forward over T+1 rows serves both terms.
+ * reward (T,N); reset_last (N) i64 = env.reset_buf after the last step: done = 1 - reset (ppo.py:230 rebinds
+ * all_done to that single (N,1) mask, broadcast over T); no done mask inside the recursion.
+ * Out: target (T,N), advantage (T,N). */
+int flyb_gae(const float* reward, const float* values, const int64_t* reset_last, int32_t horizon, int32_t num_envs,
+             float gamma, float lmbda, float* target, float* advantage, void* stream);
+
+/* ---- agent, kernel (d): one optimiser step of reference PPO.update (ppo.py:183-199), split where a
+ *      data-parallel run all-reduces:  flyb_ppo_grad -> [all-reduce(grad)/world] -> flyb_ppo_apply.
+ * flyb_ppo_grad: forward, clipped-surrogate + SmoothL1 loss, backward.  obs (rows,O), action (rows,A),
+ *   old_logp/target/advantage (rows).  Out: grad (net->total) = d(loss.mean())/d(params) over THESE rows,
+ *   loss (1).  workspace: flyb_ppo_workspace_bytes(net, rows) bytes.
+ * flyb_ppo_apply: grad *= grad_scale; clip_grad_norm_(max_grad_norm) with torch's coefficient
+ *   min(1, max/(norm+1e-6)); Adam (torch defaults, no weight decay).  step (1) i64 device counter, incremented.
+ *   grad_norm_out (1) nullable. */
+size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t rows);
+int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const float* obs,
+                  const float* action, const float* old_logp, const float* target, const float* advantage,
+                  const float* action_var, int64_t rows, float* grad, float* loss, void* workspace, void* stream);
+int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad, float* exp_avg,
+                   float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out, void* stream);
+
+/* action_var <- max(floor, action_var - decay) (ppo.py:236-237), on the device so a captured graph can replay it. */
+int flyb_anneal_var(float* action_var, int32_t num_act, float decay, float floor, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLYB200_H_ */
