@@ -41,8 +41,8 @@ class NetLayout(C.Structure):
 
 
 class PpoCfg(C.Structure):
-    _fields_ = [("clip", C.c_float), ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
-                ("eps", C.c_float), ("max_grad_norm", C.c_float)]
+    _fields_ = [("clip", C.c_double), ("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double),
+                ("eps", C.c_double), ("max_grad_norm", C.c_double)]
 
 
 _P = C.c_void_p
@@ -53,16 +53,16 @@ SIGNATURES = {
     "flyb_device_count": (C.c_int, []),
     "flyb_net_layout": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(NetLayout)]),
     "flyb_env_scratch_bytes": (C.c_size_t, [C.c_int32]),
-    "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 18),
+    "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 19),
     "flyb_env_pre_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 10),
-    "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64,
+    "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64, _P,
                                   _P, _P, _P, _P, C.POINTER(EnvCfg)] + [_P] * 9),
     "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.c_int64, _P, _P, _P]),
     "flyb_gae": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, _P]),
     "flyb_ppo_workspace_bytes": (C.c_size_t, [C.POINTER(NetLayout), C.c_int64]),
     "flyb_ppo_grad": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 7 + [C.c_int64] + [_P] * 4),
-    "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5 + [C.c_float, _P, _P]),
-    "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P]),
+    "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5 + [C.c_float, _P, _P, _P]),
+    "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P, _P]),
 }
 
 _lib = None

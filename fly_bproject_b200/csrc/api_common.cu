@@ -21,6 +21,24 @@ int check_cuda(cudaError_t err, const char* what) {
   return FLYB_ECUDA;
 }
 
+int ensure_smem(const void* kernel, size_t smem) {
+  struct Entry { const void* k; size_t granted; };
+  static Entry table[64];
+  static int used = 0;
+  for (int i = 0; i < used; ++i)
+    if (table[i].k == kernel) {
+      if (smem <= table[i].granted) return FLYB_OK;
+      int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                          "cudaFuncSetAttribute(max dynamic smem)");
+      if (rc == FLYB_OK) table[i].granted = smem;
+      return rc;
+    }
+  int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                      "cudaFuncSetAttribute(max dynamic smem)");
+  if (rc == FLYB_OK && used < 64) table[used++] = Entry{kernel, smem};
+  return rc;
+}
+
 }  // namespace flyb
 
 extern "C" int flyb_abi_version(void) { return FLYB_ABI_VERSION; }

@@ -45,7 +45,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
                     long long* __restrict__ reset, float* __restrict__ obs, float* __restrict__ reward,
                     float* __restrict__ up_vec, float* __restrict__ heading_vec, int* __restrict__ reset_ids,
                     int* __restrict__ reset_count, ScanScratch* __restrict__ scratch, float* __restrict__ obs_copy,
-                    float* __restrict__ reward_copy) {
+                    float* __restrict__ reward_copy, float* __restrict__ reward_sum) {
   extern __shared__ __align__(16) float smem[];
   const int N = cfg.num_envs, D = cfg.num_dof, A = cfg.num_act, B = cfg.num_bodies;
   const int O = 19 + 3 * A;
@@ -102,6 +102,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
 
   // ---- per-env math: one thread per env
   bool flag = false;
+  float my_reward = 0.0f;
   if (tid < nenv) {
     const int env = env0 + tid;
     float r[13];
@@ -115,6 +116,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     reset[env] = out.reset;
     reward[env] = out.reward;
     if (reward_copy) reward_copy[env] = out.reward;
+    my_reward = out.reward;
     up_vec[env * 3 + 0] = out.up_vec.x; up_vec[env * 3 + 1] = out.up_vec.y; up_vec[env * 3 + 2] = out.up_vec.z;
     heading_vec[env * 3 + 0] = out.heading_vec.x; heading_vec[env * 3 + 1] = out.heading_vec.y;
     heading_vec[env * 3 + 2] = out.heading_vec.z;
@@ -125,6 +127,10 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   const unsigned ballot = __ballot_sync(0xffffffffu, flag);
   const int lane = tid & 31, warp = tid >> 5;
   if (lane == 0) s_warp_cnt[warp] = __popc(ballot);
+  if (reward_sum) {   // score accumulator (ppo.py:233), one atomic per warp
+    const float ws = warp_sum(my_reward);
+    if (lane == 0) atomicAdd(reward_sum, ws);
+  }
   __syncthreads();
   int warp_off = 0, block_cnt = 0;
 #pragma unroll
@@ -290,7 +296,7 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
                                      float* prev_potentials, int64_t* progress, int64_t* reset, float* obs,
                                      float* reward, float* up_vec, float* heading_vec, int32_t* reset_ids,
                                      int32_t* reset_count, void* scratch, float* obs_copy, float* reward_copy,
-                                     void* stream) {
+                                     float* reward_sum, void* stream) {
   int rc = validate_cfg(cfg);
   if (rc != FLYB_OK) return rc;
   FLYB_REQUIRE(root && dof_state && force && actions_scaled && potentials && prev_potentials && progress && reset &&
@@ -300,18 +306,13 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
                "flyb_env_post_physics: root/dof_state/obs must be 16-byte aligned");
   const int O = 19 + 3 * cfg->num_act;
   const size_t smem = (size_t)ENVS * (O + 13 + FORCE_VALS) * sizeof(float);
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    rc = check_cuda(cudaFuncSetAttribute(post_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-                    "cudaFuncSetAttribute(post_physics_kernel)");
-    if (rc != FLYB_OK) return rc;
-    smem_set = smem;
-  }
+  rc = ensure_smem(reinterpret_cast<const void*>(post_physics_kernel), smem);
+  if (rc != FLYB_OK) return rc;
   const int grid = (cfg->num_envs + ENVS - 1) / ENVS;
   post_physics_kernel<<<grid, ENVS, smem, (cudaStream_t)stream>>>(
       *cfg, root, dof_state, force, actions_scaled, potentials, prev_potentials, (long long*)progress,
       (long long*)reset, obs, reward, up_vec, heading_vec, reset_ids, reset_count, (ScanScratch*)scratch, obs_copy,
-      reward_copy);
+      reward_copy, reward_sum);
   FLYB_LAUNCH_CHECK("post_physics_kernel");
   return FLYB_OK;
 }

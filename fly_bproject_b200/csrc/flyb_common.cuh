@@ -13,6 +13,8 @@ namespace flyb {
 
 void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t err, const char* what);
+// opt a kernel in to `smem` bytes of dynamic shared memory (> 48 KB needs it); cached per kernel ADDRESS
+int ensure_smem(const void* kernel, size_t smem);
 
 #define FLYB_REQUIRE(cond, ...)      \
   do {                               \

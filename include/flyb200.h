@@ -88,11 +88,11 @@ typedef struct FlybNetLayout {
 
 /* PPO hyper-parameters (reference ppo.py:113-119, 155). */
 typedef struct FlybPpoCfg {
-  float clip;          /* 0.2 */
-  float lr;            /* 1e-3 */
-  float beta1, beta2;  /* 0.9, 0.999 */
-  float eps;           /* 1e-8 */
-  float max_grad_norm; /* 1.0 (ppo.py:198) */
+  double clip;          /* 0.2   (doubles: the reference holds these as Python floats; torch rounds them to   */
+  double lr;            /* 1e-3   fp32 only where they meet a tensor, e.g. 1 - beta1 is formed in double)     */
+  double beta1, beta2;  /* 0.9, 0.999 */
+  double eps;           /* 1e-8 */
+  double max_grad_norm; /* 1.0 (ppo.py:198) */
 } FlybPpoCfg;
 
 int flyb_abi_version(void);
@@ -108,14 +108,15 @@ int flyb_net_layout(int32_t num_obs, int32_t num_act, FlybNetLayout* out);
  * In/out: potentials, prev_potentials (N), progress (N) i64, reset (N) i64.
  * Out: obs (N,O), reward (N), up_vec/heading_vec (N,3), reset_ids (N) i32 = ascending ids of envs whose reset
  *      mask is now set (what `reset_buf.nonzero()` yields at fly.py:447, compacted on the device),
- *      reset_count (1) i32.  obs_copy / reward_copy (nullable) receive a second copy (rollout rows, ppo.py:228-229).
+ *      reset_count (1) i32.  obs_copy / reward_copy (nullable) receive a second copy (rollout rows, ppo.py:228-229);
+ *      reward_sum (1, nullable) += sum(reward) — the device-side accumulator behind the score log (ppo.py:233).
  * scratch: flyb_env_scratch_bytes(N) bytes, zeroed once by the caller before first use. */
 size_t flyb_env_scratch_bytes(int32_t num_envs);
 int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, const float* dof_state, const float* force,
                           const float* actions_scaled, float* potentials, float* prev_potentials, int64_t* progress,
                           int64_t* reset, float* obs, float* reward, float* up_vec, float* heading_vec,
                           int32_t* reset_ids, int32_t* reset_count, void* scratch, float* obs_copy,
-                          float* reward_copy, void* stream);
+                          float* reward_copy, float* reward_sum, void* stream);
 
 /* ---- env: reference Fly.step up to simulate() (fly.py:626-660): scale policy actions to the joint range,
  *      scatter into the DOF position-target vector, then Fly.reset() (fly.py:446-480) for envs whose mask is set.
@@ -128,10 +129,13 @@ int flyb_env_pre_physics(const FlybEnvCfg* cfg, const float* actions, float* act
 /* ---- agent, kernel (b): reference PPO.run act block (ppo.py:213-220): mu = Net.pi(obs); a = mu + sqrt(var)*eps;
  *      logp = MVN(mu, diag(var)).log_prob(a); a = clip(a,-1,1) — optionally fused with flyb_env_pre_physics
  *      (pass cfg != NULL and the env buffers) so that one launch covers act + Fly.step's pre-physics half.
- * noise (rows,A) nullable: explicit eps (parity mode); NULL -> in-kernel Philox4x32-10 keyed by (seed, offset).
+ * noise (rows,A) nullable: explicit eps (parity mode); NULL -> in-kernel Philox4x32-10 keyed by
+ *   (seed, offset + *offset_dev); offset_dev (nullable) is a device counter flyb_anneal_var advances once per
+ *   step, so that a captured CUDA graph draws fresh noise at every replay.
  * Out: action (rows,A) clipped, logp (rows); mu_out, obs_store (rollout all_obs row, ppo.py:226) nullable. */
 int flyb_policy_act(const FlybNetLayout* net, const float* params, const float* obs, int64_t rows,
-                    const float* action_var, const float* noise, uint64_t seed, uint64_t offset, float* action,
+                    const float* action_var, const float* noise, uint64_t seed, uint64_t offset,
+                    const uint64_t* offset_dev, float* action,
                     float* logp, float* mu_out, float* obs_store, const FlybEnvCfg* cfg, float* actions_scaled,
                     float* dof_targets, int64_t* reset, int64_t* progress, float* potentials,
                     float* prev_potentials, float* root, float* dof_state, void* stream);
@@ -156,16 +160,19 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  *   loss (1).  workspace: flyb_ppo_workspace_bytes(net, rows) bytes.
  * flyb_ppo_apply: grad *= grad_scale; clip_grad_norm_(max_grad_norm) with torch's coefficient
  *   min(1, max/(norm+1e-6)); Adam (torch defaults, no weight decay).  step (1) i64 device counter, incremented.
- *   grad_norm_out (1) nullable. */
+ *   grad_norm_out (1) nullable.  workspace: the flyb_ppo_grad workspace (only its first 256 bytes are used). */
 size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t rows);
 int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const float* obs,
                   const float* action, const float* old_logp, const float* target, const float* advantage,
                   const float* action_var, int64_t rows, float* grad, float* loss, void* workspace, void* stream);
 int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad, float* exp_avg,
-                   float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out, void* stream);
+                   float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out, void* workspace,
+                   void* stream);
 
-/* action_var <- max(floor, action_var - decay) (ppo.py:236-237), on the device so a captured graph can replay it. */
-int flyb_anneal_var(float* action_var, int32_t num_act, float decay, float floor, void* stream);
+/* action_var <- max(floor, action_var - decay) (ppo.py:236-237), on the device so a captured graph can replay it;
+ * step_counter (1, nullable) u64 += 1 (the Philox draw number of flyb_policy_act). */
+int flyb_anneal_var(float* action_var, int32_t num_act, float decay, float floor, uint64_t* step_counter,
+                    void* stream);
 
 #ifdef __cplusplus
 }

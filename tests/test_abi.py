@@ -1,0 +1,84 @@
+"""CPU: libflyb200.so builds for sm_100a, loads, and exports every symbol include/flyb200.h declares (no compute)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+from tests.helpers import ROOT
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "flyb200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(flyb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported_and_bound(built_lib):
+    from fly_bproject_b200 import _lib
+    syms = declared_symbols()
+    assert len(syms) >= 14
+    handle = C.CDLL(built_lib)
+    for s in syms:
+        assert hasattr(handle, s), f"{s} declared in include/flyb200.h but not exported"
+        assert s in _lib.SIGNATURES, f"{s} has no ctypes signature in fly_bproject_b200/_lib.py"
+    assert sorted(_lib.SIGNATURES) == syms
+    lib = _lib.lib()
+    assert lib.flyb_abi_version() == 1
+
+
+def test_library_is_sm100a_only(built_lib):
+    out = subprocess.run(["cuobjdump", "-lelf", built_lib], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_struct_sizes_match_header(built_lib, tmp_path):
+    """ctypes mirrors of the ABI structs must have the C compiler's sizes."""
+    from fly_bproject_b200 import _lib
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include "flyb200.h"\nint main(){printf("%zu %zu %zu\\n", '
+                   'sizeof(FlybEnvCfg), sizeof(FlybNetLayout), sizeof(FlybPpoCfg));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
+    assert sizes == [C.sizeof(_lib.EnvCfg), C.sizeof(_lib.NetLayout), C.sizeof(_lib.PpoCfg)]
+
+
+def test_net_layout_and_argument_errors(built_lib):
+    from fly_bproject_b200 import _lib
+    lib = _lib.lib()
+    lay = _lib.NetLayout()
+    assert lib.flyb_net_layout(73, 18, C.byref(lay)) == 0
+    assert lay.k0_pad == 80 and lay.total % 4 == 0
+    assert list(lay.off)[:3] == [0, 256 * 80, 256 * 80 + 256]
+    real = 256 * 73 + 256 + 128 * 256 + 128 + 64 * 128 + 64 + 18 * 64 + 18 + 64 * 128 + 64 + 64 + 1
+    assert real == 69587                                   # 69 587 parameters at O=73, A=18
+    assert lay.total >= real
+    assert lib.flyb_net_layout(0, 18, C.byref(lay)) == -1
+    assert b"num_obs" in lib.flyb_last_error()
+    # compute entry points reject NULL buffers before touching CUDA
+    cfg = _lib.EnvCfg()
+    assert lib.flyb_env_pre_physics(C.byref(cfg), *([None] * 10)) == -1
+
+
+def test_product_path_fails_loudly_without_cuda(built_lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    import fly_bproject_b200 as fb
+    with pytest.raises(fb.FlybError):
+        fb.Fly(fb.make_args(num_envs=8, sim_device="cpu"))
+    with pytest.raises(fb.FlybError):
+        fb._lib.ptr(torch.zeros(4))
+
+
+def test_package_never_imports_oracle():
+    pkg = os.path.join(ROOT, "fly_bproject_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+                assert "/root/reference" not in text, f

@@ -1,0 +1,344 @@
+"""GPU parity, agent half: Net forward, act, GAE and the PPO minibatch step through the C ABI against the golden
+vectors frozen from the executed reference (ppo.py) and against the CPU oracle.
+Bar (north_star): GAE within 1e-5 relative; one PPO minibatch update within 1e-4 relative on loss and parameters."""
+import ctypes as C
+import math
+
+import pytest
+import torch
+
+import fly_bproject_b200 as fb
+from fly_bproject_b200 import _lib
+from oracle import fly_oracle as fo
+from tests.helpers import RTOL_PPO, load_golden, oracle_tables
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def golden_net(g, tag="w0"):
+    net = fb.Net(73, 18, DEV, init=False)
+    net.load_state_dict({k: g[f"{tag}/{k}"] for k in fo.PARAM_ORDER})
+    return net
+
+
+def test_net_forward_matches_reference_golden():
+    g = load_golden("ppo_n64_t32.npz")
+    net = golden_net(g)
+    x = g["net_x"].to(DEV)
+    torch.testing.assert_close(net.pi(x).cpu(), g["net_pi"], rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(net.v(x).cpu(), g["net_v"], rtol=1e-5, atol=2e-5)
+    # checkpoint round trip in the reference's state_dict format (ppo.py:266-273)
+    sd = net.state_dict()
+    assert list(sd) == fo.PARAM_ORDER and sd["shared_net.0.weight"].shape == (256, 73)
+    for k in fo.PARAM_ORDER:
+        assert torch.equal(sd[k].cpu(), g["w0/" + k])
+
+
+@pytest.mark.parametrize("o,a,rows", [(73, 18, 1), (73, 18, 16384 + 17), (145, 42, 3001)])
+def test_net_forward_matches_oracle_random_weights(o, a, rows):
+    p = fo.init_params(o, a, seed=o)
+    net = fb.Net(o, a, DEV, init=False)
+    net.load_state_dict(p)
+    x = torch.randn(rows, o, generator=torch.Generator().manual_seed(rows)) * 1.5
+    mu, val = net._forward(x.to(DEV), True, True)
+    torch.testing.assert_close(mu.cpu(), fo.pi(p, x), rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(val.cpu(), fo.v(p, x), rtol=1e-5, atol=1e-5)
+
+
+def _act(net, obs, var, noise, env=None, seed=0):
+    rows = obs.shape[0]
+    action = torch.empty(rows, net.num_act, device=DEV)
+    logp = torch.empty(rows, device=DEV)
+    mu = torch.empty(rows, net.num_act, device=DEV)
+    p = _lib.ptr
+    envargs = [None] * 9
+    if env is not None:
+        st = env.state
+        envargs = [C.byref(env.cfg), p(env._actions_scaled), p(env.dof_targets), p(env.reset_buf), p(env.progress_buf),
+                   p(env.potentials), p(env.prev_potentials), p(st.root), p(st.dof_state)]
+    _lib.check(net.lib.flyb_policy_act(C.byref(net.layout), p(net.flat), p(obs), rows, p(var), p(noise), seed, 0, None,
+                                       p(action), p(logp), p(mu), None, *envargs, _lib.current_stream()))
+    return action, logp, mu
+
+
+def test_act_matches_reference_golden():
+    g = load_golden("ppo_n64_t32.npz")
+    net = golden_net(g)
+    a, logp, _ = _act(net, g["act_obs"].to(DEV), g["act_var"].to(DEV), g["act_noise"].to(DEV))
+    torch.testing.assert_close(a.cpu(), g["act_action"], rtol=1e-5, atol=2e-6)      # clipped action (ppo.py:220)
+    torch.testing.assert_close(logp.cpu(), g["act_logp"], rtol=1e-5, atol=1e-5)     # of the UNclipped sample
+    assert float(a.abs().max()) <= 1.0
+
+
+def test_fused_act_pre_physics_equals_separate_kernels():
+    n = 5000
+    t = oracle_tables("full_42", n, False)
+    st = fo.synth_state(t, seed=11)
+    mk = lambda: fb.Fly(fb.make_args(num_envs=n, sim_device=DEV, asset="full_42", full_actions=False),
+                        state_source=fb.TensorStateSource(st["root"].to(DEV), st["dof_states"].to(DEV),
+                                                          st["force"].to(DEV)))
+    e1, e2 = mk(), mk()
+    mask = (torch.rand(n, generator=torch.Generator().manual_seed(1)) < 0.3).long().to(DEV)
+    for e in (e1, e2):
+        e.reset_buf.copy_(mask)
+        e.progress_buf.fill_(7)
+    net = fb.Net(73, 18, DEV)
+    obs = torch.randn(n, 73, device=DEV)
+    var = torch.full((18,), 0.2, device=DEV)
+    noise = torch.randn(n, 18, device=DEV)
+    a1, l1, _ = _act(net, obs, var, noise, env=e1)
+    a2, l2, _ = _act(net, obs, var, noise)
+    e2.pre_physics(a2)
+    assert torch.equal(a1, a2) and torch.equal(l1, l2)
+    for name in ["_actions_scaled", "dof_targets", "reset_buf", "progress_buf", "potentials", "prev_potentials"]:
+        assert torch.equal(getattr(e1, name), getattr(e2, name)), name
+    assert torch.equal(e1.state.root, e2.state.root) and torch.equal(e1.state.dof_state, e2.state.dof_state)
+    # and against the oracle's scaling (fly.py:626-651)
+    scaled, targets = fo.scale_actions(t, a1.cpu())
+    torch.testing.assert_close(e1._actions_scaled.cpu(), scaled.view(n, -1), rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(e1.dof_targets.cpu(), targets, rtol=1e-6, atol=1e-6)
+
+
+def test_philox_noise_is_standard_normal_and_keyed():
+    net = fb.Net(73, 18, DEV)
+    n = 20000
+    obs = torch.randn(n, 73, device=DEV)
+    var = torch.full((18,), 0.04, device=DEV)
+    a0, l0, mu0 = _act(net, obs, var, None, seed=5)
+    a1, l1, _ = _act(net, obs, var, None, seed=5)
+    a2, _, _ = _act(net, obs, var, None, seed=6)
+    assert torch.equal(a0, a1) and torch.equal(l0, l1) and not torch.equal(a0, a2)
+    inside = a0.abs() < 1.0
+    eps = ((a0 - mu0) / 0.2)[inside]
+    assert abs(float(eps.mean())) < 0.01 and abs(float(eps.std()) - 1.0) < 0.01
+    # log-prob identity on rows where nothing was clipped
+    rows = inside.all(dim=1)
+    want = fo.gaussian_logp(mu0[rows].cpu(), a0[rows].cpu(), var.cpu())
+    torch.testing.assert_close(l0[rows].cpu(), want, rtol=1e-4, atol=1e-3)
+
+
+def _gae(reward, values, reset_last, gamma=0.99, lmbda=0.95):
+    t, n = reward.shape[0], reward.shape[1]
+    target = torch.empty(t, n, device=DEV)
+    adv = torch.empty(t, n, device=DEV)
+    p = _lib.ptr
+    _lib.check(_lib.lib().flyb_gae(p(reward), p(values), p(reset_last), t, n, gamma, lmbda, p(target), p(adv),
+                                   _lib.current_stream()))
+    return target, adv
+
+
+def test_gae_matches_reference_golden():
+    g = load_golden("ppo_n64_t32.npz")
+    net = golden_net(g)
+    ring = torch.cat([g["roll_obs"], g["roll_next"][-1:]], dim=0).to(DEV)      # (T+1, N, O)
+    values = net.v(ring).squeeze(-1).contiguous()
+    reset_last = (1 - g["roll_done"].squeeze(-1)).to(DEV)
+    target, adv = _gae(g["roll_rew"].squeeze(-1).contiguous().to(DEV), values, reset_last)
+    torch.testing.assert_close(target.cpu(), g["roll_target"].squeeze(-1), rtol=1e-5, atol=2e-5)
+    torch.testing.assert_close(adv.cpu(), g["roll_adv"].squeeze(-1), rtol=1e-5, atol=5e-5)
+
+
+@pytest.mark.parametrize("t,n", [(32, 16384), (1, 33), (7, 1000), (128, 4097)])
+def test_gae_scan_bit_exact_vs_oracle_recursion_and_linear(t, n):
+    gen = torch.Generator().manual_seed(t * n)
+    reward = torch.randn(t, n, generator=gen)
+    values = torch.randn(t + 1, n, generator=gen) * 3
+    reset_last = (torch.rand(n, generator=gen) < 0.3).long()
+    done = (1 - reset_last).float()
+    # oracle recursion on the same values (ppo.py:160-169)
+    target = reward + 0.99 * values[1:] * done
+    delta = target - values[:-1]
+    adv = torch.zeros_like(delta)
+    run = torch.zeros(n)
+    gl = torch.tensor(0.99 * 0.95, dtype=torch.float32)
+    for i in range(t - 1, -1, -1):
+        run = gl * run + delta[i]
+        adv[i] = run
+    tg, ad = _gae(reward.to(DEV), values.to(DEV), reset_last.to(DEV))
+    assert torch.equal(tg.cpu(), target)
+    torch.testing.assert_close(ad.cpu(), adv, rtol=1e-6, atol=1e-6)
+    # size-independent property: the scan is linear in (reward, values)
+    tg2, ad2 = _gae((2 * reward).to(DEV), (2 * values).to(DEV), reset_last.to(DEV))
+    torch.testing.assert_close(ad2, 2 * ad, rtol=1e-5, atol=1e-5)
+
+
+def _grad_step(net, g, k, j, var):
+    """One flyb_ppo_grad on golden rollout rows [k:j]; returns (grad views, loss)."""
+    n = g["roll_obs"].shape[1]
+    rows = (j - k) * n
+    lib, p = _lib.lib(), _lib.ptr
+    cfg = _lib.PpoCfg(0.2, 1e-3, 0.9, 0.999, 1e-8, 1.0)
+    ws = torch.zeros(lib.flyb_ppo_workspace_bytes(C.byref(net.layout), rows) + 256, dtype=torch.uint8, device=DEV)
+    wsp = (ws.data_ptr() + 255) // 256 * 256
+    grad = torch.zeros_like(net.flat)
+    loss = torch.zeros(1, device=DEV)
+    # keep the device copies alive until the launch has finished
+    dv = [x.contiguous().to(DEV) for x in (g["roll_obs"][k:j], g["roll_acts"][k:j], g["roll_logp"][k:j],
+                                           g["roll_target"][k:j], g["roll_adv"][k:j], var)]
+    _lib.check(lib.flyb_ppo_grad(C.byref(net.layout), C.byref(cfg), p(net.flat), p(dv[0]), p(dv[1]), p(dv[2]),
+                                 p(dv[3]), p(dv[4]), p(dv[5]), rows, p(grad), p(loss), wsp, _lib.current_stream()))
+    torch.cuda.synchronize()
+    return grad, loss, ws, wsp, cfg
+
+
+def test_ppo_minibatch_step_matches_reference_golden():
+    g = load_golden("ppo_n64_t32.npz")
+    n, t_roll, mc = [int(x) for x in g["meta"]]
+    net = golden_net(g)
+    grad, loss, ws, wsp, cfg = _grad_step(net, g, 0, mc, g["roll_var"])
+    torch.testing.assert_close(loss.cpu().squeeze(), g["loss0"], rtol=RTOL_PPO, atol=1e-6)
+    # unclipped gradient against the oracle's autograd on the same rows
+    p0 = {k: g["w0/" + k].clone() for k in fo.PARAM_ORDER}
+    _, norm, grads = fo.minibatch_step(p0, fo.AdamState(p0), g["roll_obs"][0:mc], g["roll_acts"][0:mc],
+                                       g["roll_logp"][0:mc], g["roll_target"][0:mc], g["roll_adv"][0:mc], g["roll_var"])
+    gv = net.make_views(grad)
+    for k in fo.PARAM_ORDER:
+        scale = float(grads[k].abs().max()) + 1e-12
+        torch.testing.assert_close(gv[k].cpu(), grads[k], rtol=RTOL_PPO, atol=RTOL_PPO * scale, msg="grad " + k)
+    # padding of the flat layout carries exactly zero gradient
+    assert float(grad.abs().sum()) == pytest.approx(float(sum(gv[k].abs().sum() for k in fo.PARAM_ORDER)), rel=1e-6)
+    # clip + Adam against the golden parameters / moments after optimiser step 1 (ppo.py:198-199)
+    lib, p = _lib.lib(), _lib.ptr
+    m, v = torch.zeros_like(net.flat), torch.zeros_like(net.flat)
+    step = torch.zeros(1, dtype=torch.int64, device=DEV)
+    gn = torch.zeros(1, device=DEV)
+    _lib.check(lib.flyb_ppo_apply(C.byref(net.layout), C.byref(cfg), p(net.flat), p(grad), p(m), p(v), p(step), 1.0,
+                                  p(gn), wsp, _lib.current_stream()))
+    torch.cuda.synchronize()
+    assert int(step.item()) == 1
+    assert float(gn) == pytest.approx(norm, rel=1e-4)
+    sd, mv, vv, gc = net.state_dict(), net.make_views(m), net.make_views(v), net.make_views(grad)
+    ill = 0
+    for k in fo.PARAM_ORDER:
+        # Adam's first step is lr * g / (|g| + eps) = +-lr wherever |g| >> eps: it is discontinuous in g at 0, so an
+        # element whose gradient is below the gradient tolerance band (1e-4 of the tensor's largest gradient — i.e.
+        # rounding noise of the reduction over rows) may legitimately land anywhere within +-lr of the reference.
+        gref = g["g0/" + k]
+        band = RTOL_PPO * float(gref.abs().max())
+        well = gref.abs() > band
+        got, want = sd[k].cpu(), g["w1/" + k]
+        err = (got - want).abs()
+        tol = 1e-6 + RTOL_PPO * want.abs()
+        bad = (err > tol) & well
+        assert not bad.any(), f"param {k}: {int(bad.sum())} well-conditioned elements off, worst {float(err[well].max()):.3e}"
+        assert float(err[~well].max() if (~well).any() else 0.0) <= 2.0 * 1e-3 + 1e-6, "param " + k
+        ill += int(((err > tol) & ~well).sum())
+        torch.testing.assert_close(gc[k].cpu(), g["g0/" + k], rtol=RTOL_PPO,
+                                   atol=RTOL_PPO * float(g["g0/" + k].abs().max()), msg="clipped grad " + k)
+        torch.testing.assert_close(mv[k].cpu(), g["m1/" + k], rtol=RTOL_PPO,
+                                   atol=RTOL_PPO * float(g["m1/" + k].abs().max()), msg="exp_avg " + k)
+        torch.testing.assert_close(vv[k].cpu(), g["v1/" + k], rtol=2 * RTOL_PPO,
+                                   atol=2 * RTOL_PPO * float(g["v1/" + k].abs().max()), msg="exp_avg_sq " + k)
+    assert ill <= 0.005 * 69587, f"{ill} near-zero-gradient elements moved differently"
+
+
+class _ReplayEnv:
+    """Foreign env behind the reference's duck-typed surface: replays the golden rollout."""
+
+    def __init__(self, g):
+        self.g, self.i = g, 0
+        self.num_act, self.num_obs, self.end = 18, 73, False
+        self.obs_buf = g["roll_obs"][0].to(DEV)
+        self.reward_buf = torch.zeros(64, device=DEV)
+        self.reset_buf = torch.ones(64, dtype=torch.long, device=DEV)
+
+    def step(self, a):
+        g, i = self.g, self.i
+        self.obs_buf = g["roll_next"][i].to(DEV)
+        self.reward_buf = g["roll_rew"][i].squeeze(-1).to(DEV)
+        self.reset_buf = (1 - g["roll_done"].squeeze(-1)).to(DEV) if i == g["roll_obs"].shape[0] - 1 else \
+            torch.zeros(64, dtype=torch.long, device=DEV)
+        self.i += 1
+
+
+def test_full_update_matches_reference_golden_75_steps():
+    """PPO.update through the drop-in class on the golden rollout: 5 epochs x 15 minibatches (log.txt:49)."""
+    g = load_golden("ppo_n64_t32.npz")
+    n, t_roll, mc = [int(x) for x in g["meta"]]
+    args = fb.make_args(num_envs=n, sim_device=DEV, horizon=t_roll, verbose=False)
+    agent = fb.PPO(args, env=_ReplayEnv(g))
+    assert agent.mini_chunk_size == mc and agent.rollout_size == t_roll
+    agent.net.load_state_dict({k: g["w0/" + k] for k in fo.PARAM_ORDER})
+    agent._obs_ring[:t_roll].copy_(g["roll_obs"])
+    agent._obs_ring[t_roll].copy_(g["roll_next"][-1])
+    agent.all_acts.copy_(g["roll_acts"])
+    agent.all_reward.copy_(g["roll_rew"])
+    agent.all_log_prob.copy_(g["roll_logp"])
+    agent.action_var.copy_(g["roll_var"])
+    agent.env.reset_buf = (1 - g["roll_done"].squeeze(-1)).to(DEV)
+    assert agent.all_done.shape == (n, 1) and agent.all_done.dtype == torch.int64       # ppo.py:230 quirk
+    obs, acts, logp, target, adv = agent.make_data()
+    torch.testing.assert_close(target.cpu(), g["roll_target"], rtol=1e-5, atol=2e-5)
+    torch.testing.assert_close(adv.cpu(), g["roll_adv"], rtol=1e-5, atol=5e-5)
+    agent.update()
+    assert agent.optim_step == 75 and int(agent.adam_step.item()) == 75
+    sd = agent.net.state_dict()
+    for k in fo.PARAM_ORDER:
+        torch.testing.assert_close(sd[k].cpu(), g["w3/" + k] if False else g["w75/" + k], rtol=2e-3, atol=2e-4,
+                                   msg="param " + k)
+
+
+@pytest.mark.parametrize("o,a,rows", [(145, 42, 1000), (73, 18, 32768), (73, 18, 100)])
+def test_ppo_grad_matches_oracle_autograd_other_shapes(o, a, rows):
+    gen = torch.Generator().manual_seed(rows + o)
+    p0 = fo.init_params(o, a, seed=3)
+    net = fb.Net(o, a, DEV, init=False)
+    net.load_state_dict(p0)
+    obs = torch.randn(rows, o, generator=gen)
+    var = torch.full((a,), 0.15)
+    with torch.no_grad():
+        mu = fo.pi(p0, obs)
+    act = (mu + 0.4 * torch.randn(rows, a, generator=gen)).clip(-1, 1)
+    old_logp = fo.gaussian_logp(mu, act, var) + 0.3 * torch.randn(rows, generator=gen)   # ratios in and out of the clip
+    target = torch.randn(rows, 1, generator=gen) * 2
+    adv = torch.randn(rows, 1, generator=gen)
+    g = {"roll_obs": obs.view(1, rows, o), "roll_acts": act.view(1, rows, a), "roll_logp": old_logp.view(1, rows),
+         "roll_target": target.view(1, rows, 1), "roll_adv": adv.view(1, rows, 1)}
+    grad, loss, *_ = _grad_step(net, g, 0, 1, var)
+    leaf = {k: x.clone().requires_grad_(True) for k, x in p0.items()}
+    want = fo.minibatch_loss(leaf, obs, act, old_logp, target, adv, var)
+    want.backward()
+    torch.testing.assert_close(loss.cpu().squeeze(), want.detach(), rtol=RTOL_PPO, atol=1e-6)
+    gv = net.make_views(grad)
+    for k in fo.PARAM_ORDER:
+        scale = float(leaf[k].grad.abs().max()) + 1e-12
+        torch.testing.assert_close(gv[k].cpu(), leaf[k].grad, rtol=RTOL_PPO, atol=RTOL_PPO * scale, msg="grad " + k)
+
+
+def test_run_loop_matches_oracle_rollout_and_update():
+    """Integration: the drop-in PPO + Fly driven like trainer.py, against the oracle driven the same way, with
+    explicit noise; two env steps then compare rollout rows."""
+    n = 512
+    t = oracle_tables("limited_18", n, True)
+    args = fb.make_args(num_envs=n, sim_device=DEV, horizon=16, verbose=False, state_pool=2, seed=77)
+    agent = fb.PPO(args)
+    env = agent.env
+    p0 = {k: v.cpu() for k, v in agent.net.state_dict().items()}
+    # oracle env on the same synthetic pool
+    s = fo.EnvState(t)
+    pool = [{k: v.cpu().clone() for k, v in e.items()} for e in env.state.pool]
+    var = torch.full((18,), 0.2)
+    idx = 0
+    s.root, s.dof_states, s.force = pool[0]["root"], pool[0]["dof_state"], pool[0]["force"]
+    gen = torch.Generator().manual_seed(0)
+    for i in range(3):
+        noise = torch.randn(n, 18, generator=gen)
+        obs_before = s.obs_buf.clone()
+        a, logp, _ = fo.act(p0, obs_before, var, noise)
+        scaled, targets = fo.scale_actions(t, a)
+        s.actions = scaled
+        fo.apply_reset(t, s)
+        idx = (idx + 1) % 2
+        s.root, s.dof_states, s.force = pool[idx]["root"], pool[idx]["dof_state"], pool[idx]["force"]
+        fo.post_physics(t, s)
+        var = fo.anneal_var(var)
+        agent.run(noise=noise.to(DEV))
+        torch.cuda.synchronize()
+        torch.testing.assert_close(agent.all_acts[i].cpu(), a, rtol=1e-5, atol=2e-6)
+        torch.testing.assert_close(agent.all_log_prob[i].cpu(), logp, rtol=1e-5, atol=1e-4)
+        torch.testing.assert_close(agent.all_obs[i].cpu(), obs_before, rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(agent.all_reward[i].squeeze(-1).cpu(), s.reward_buf, rtol=1e-5, atol=1e-5)
+        assert torch.equal(env.reset_buf.cpu(), s.reset_buf)
+        torch.testing.assert_close(agent.action_var.cpu(), var, rtol=1e-6, atol=0)
+    assert agent.mini_batch_number == 3 and agent.run_step == 3

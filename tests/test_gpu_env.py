@@ -1,0 +1,146 @@
+"""GPU parity, env half: the CUDA kernels called through the C ABI (via the `Fly` drop-in) against
+(1) golden vectors frozen from the executed reference and (2) the CPU oracle on seeded synthetic states.
+Bar (north_star): reset masks / ids / counters bit-exact; obs and reward within 1e-5 relative."""
+import pytest
+import torch
+
+import fly_bproject_b200 as fb
+from oracle import fly_oracle as fo
+from tests.helpers import ATOL_ENV, ENV_CASES, RTOL_ENV, assert_obs_close, load_golden, oracle_tables
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def make_env(n, asset, full, root, dof, force, walking=False):
+    src = fb.TensorStateSource(root.to(DEV).contiguous(), dof.to(DEV).contiguous(), force.to(DEV).contiguous())
+    args = fb.make_args(num_envs=n, sim_device=DEV, asset=asset, full_actions=full, walking=walking)
+    return fb.Fly(args, state_source=src)
+
+
+@pytest.mark.parametrize("name,asset,n,full", ENV_CASES)
+def test_env_kernels_match_reference_golden(name, asset, n, full):
+    g = load_golden(name)
+    env = make_env(n, asset, full, g["root"], g["dof_states"], g["force"])
+    # pre-physics with no env flagged: scaling + DOF-target scatter only (fly.py:626-657)
+    env.reset_buf.zero_()
+    env.pre_physics(g["actions_in"].to(DEV))
+    torch.testing.assert_close(env._actions_scaled.cpu(), g["actions_scaled"], rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(env.dof_targets.cpu(), g["dof_targets"], rtol=1e-6, atol=1e-6)
+    assert env.actions.shape == (n * env.num_act, 1)
+    # post-physics with the fixture's previous mask / counters / potentials
+    env.reset_buf.copy_(g["reset_in"])
+    env.progress_buf.copy_(g["progress_in"])
+    env.potentials.copy_(g["potentials_in"])
+    env.post_physics()
+    torch.cuda.synchronize()
+    assert torch.equal(env.reset_buf.cpu(), g["reset"])                       # bit-exact
+    assert torch.equal(env.progress_buf.cpu(), g["progress"])
+    assert env.reset_buf.dtype == torch.int64 and env.progress_buf.dtype == torch.int64
+    assert_obs_close(env.obs_buf.cpu(), g["obs"], env.num_act)
+    torch.testing.assert_close(env.reward_buf.cpu(), g["reward"], rtol=RTOL_ENV, atol=ATOL_ENV)
+    torch.testing.assert_close(env.potentials.cpu(), g["potentials"], rtol=1e-6, atol=0)
+    assert torch.equal(env.prev_potentials.cpu(), g["prev_potentials"])
+    torch.testing.assert_close(env.up_vec.cpu(), g["up_vec"], rtol=RTOL_ENV, atol=ATOL_ENV)
+    torch.testing.assert_close(env.heading_vec.cpu(), g["heading_vec"], rtol=RTOL_ENV, atol=ATOL_ENV)
+    # compacted ids == reset_buf.nonzero() (fly.py:447), ascending, int32; count on the device
+    want_ids = g["reset"].nonzero().squeeze(-1).to(torch.int32)
+    cnt = int(env.reset_count.item())
+    assert cnt == want_ids.numel()
+    assert torch.equal(env.reset_ids[:cnt].cpu(), want_ids)
+    torch.testing.assert_close(env.reward_sum.cpu(), g["reward"].sum().view(1), rtol=1e-4, atol=1e-3)
+
+
+@pytest.mark.parametrize("n,asset,full,walking", [(16384, "limited_18", True, False), (100003, "limited_18", True, True),
+                                                   (4099, "full_42", True, False), (1000, "full_42", False, True),
+                                                   (1, "limited_18", True, False), (127, "limited_18", True, False)])
+def test_env_step_matches_oracle(n, asset, full, walking):
+    t = oracle_tables(asset, n, full)
+    st = fo.synth_state(t, seed=n + 5)
+    s = fo.EnvState(t)
+    s.root, s.dof_states, s.force = st["root"].clone(), st["dof_states"].clone(), st["force"].clone()
+    s.progress_buf = st["progress"].clone()
+    g = torch.Generator().manual_seed(n)
+    s.reset_buf = (torch.rand(n, generator=g) < 0.25).long()           # some envs flagged from the previous step
+    s.potentials = -torch.rand(n, generator=g) * 60000.0
+    env = make_env(n, asset, full, st["root"], st["dof_states"], st["force"], walking)
+    env.progress_buf.copy_(s.progress_buf)
+    env.reset_buf.copy_(s.reset_buf)
+    env.potentials.copy_(s.potentials)
+    env.prev_potentials.copy_(s.prev_potentials)
+
+    # oracle: Fly.step order (fly.py:624-681) with no physics in between
+    scaled, targets = fo.scale_actions(t, st["actions"])
+    s.actions = scaled
+    ids = fo.apply_reset(t, s)
+    fo.post_physics(t, s, walking=walking)
+
+    env.pre_physics(st["actions"].to(DEV))
+    # reset bookkeeping of the flagged envs (fly.py:446-480)
+    assert int(env.reset_buf.sum().item()) == 0
+    torch.testing.assert_close(env.state.root.cpu(), s.root, rtol=0, atol=0)
+    torch.testing.assert_close(env.state.dof_state.cpu(), s.dof_states, rtol=1e-6, atol=1e-7)
+    env.simulate()
+    env.post_physics()
+    torch.cuda.synchronize()
+    assert torch.equal(env.reset_buf.cpu(), s.reset_buf)
+    assert torch.equal(env.progress_buf.cpu(), s.progress_buf)
+    assert_obs_close(env.obs_buf.cpu(), s.obs_buf, env.num_act)
+    # walking total holds 2*(pot - prev_pot), a difference of O(6e4) potentials: one ulp of the potential (2^-8) is
+    # 0.0078 in the reward; the potentials themselves are held to 1e-6 relative just below
+    torch.testing.assert_close(env.reward_buf.cpu(), s.reward_buf, rtol=RTOL_ENV, atol=0.016 if walking else ATOL_ENV)
+    torch.testing.assert_close(env.potentials.cpu(), s.potentials, rtol=1e-6, atol=0)
+    torch.testing.assert_close(env.prev_potentials.cpu(), s.prev_potentials, rtol=1e-6, atol=0)
+    torch.testing.assert_close(env.dof_targets.cpu(), targets, rtol=1e-6, atol=1e-6)
+    want_ids = s.reset_buf.nonzero().squeeze(-1).to(torch.int32)
+    cnt = int(env.reset_count.item())
+    assert cnt == want_ids.numel()
+    assert torch.equal(env.reset_ids[:cnt].cpu(), want_ids)
+    assert torch.equal(env.reset_ids[:cnt].cpu(), torch.sort(env.reset_ids[:cnt].cpu()).values)
+    assert ids.dtype == torch.int32
+
+
+def test_compaction_is_stable_over_repeated_launches():
+    """The look-back scratch re-arms itself: many launches, all-set / none-set / ragged masks."""
+    n = 50000
+    t = oracle_tables("limited_18", n, True)
+    st = fo.synth_state(t, seed=3)
+    env = make_env(n, "limited_18", True, st["root"], st["dof_states"], st["force"])
+    env._actions_scaled.copy_(st["actions"])
+    for it in range(12):
+        env.reset_buf.zero_()
+        if it % 3 == 1:
+            env.reset_buf.fill_(1)                      # every env flagged (the reference's first step, fly.py:175)
+        env.progress_buf.zero_()
+        env.post_physics()
+        want = env.reset_buf.nonzero().squeeze(-1).to(torch.int32)
+        cnt = int(env.reset_count.item())
+        assert cnt == want.numel()
+        assert torch.equal(env.reset_ids[:cnt], want)
+    # a healthy, upright fly never resets: count 0 and ids untouched
+    root = torch.zeros(n, 13)
+    root[:, 2], root[:, 6] = 2.0, 1.0
+    env2 = make_env(n, "limited_18", True, root, st["dof_states"], torch.zeros_like(st["force"]))
+    env2.reset_buf.zero_()
+    env2._actions_scaled.copy_(((t.lower + t.upper) / 2).repeat(n, 1))      # mid-range commands: no limit cost
+    env2.post_physics()
+    assert int(env2.reset_count.item()) == 0
+    assert int(env2.reset_buf.sum().item()) == 0
+    # closed forms: identity quaternion => up_proj = heading_proj = 1, roll = pitch = yaw = 0
+    o = env2.obs_buf[0].cpu()
+    assert o[10] == 1.0 and o[11] == 1.0 and o[7] == 0.0 and o[8] == 0.0 and o[12 + 54] == 0.0
+    assert float(env2.reward_buf[0]) == pytest.approx(0.5)     # alive only: up 0 (1.4 < h < 2.1), no legs down
+
+
+def test_step_api_and_errors():
+    env = fb.Fly(fb.make_args(num_envs=300, sim_device=DEV))
+    assert env.reset_buf.dtype == torch.int64 and int(env.reset_buf.sum()) == 300      # init ones (fly.py:175)
+    a = torch.zeros(300, 18, device=DEV)
+    env.step(a)
+    assert int(env.progress_buf.min()) == 1
+    with pytest.raises(fb.FlybError):
+        env.step(torch.zeros(300, 17, device=DEV))
+    with pytest.raises(fb.FlybError):
+        env.step(torch.zeros(300, 18))                  # CPU tensor: no fallback
+    assert env.dof_pos.shape == (300, 18) and env.root_tensor.shape == (300, 13)
+    assert env.force_tensor.shape == (300 * 93, 3)
