@@ -279,7 +279,8 @@ def run_own(args):
         st = env.state
         env.simulate()
         _lib.check(agent.lib.flyb_policy_act(
-            C.byref(agent.net.layout), p(agent.net.flat), p(env.obs_buf), NUM_ENVS, p(agent.action_var), None, 1, i,
+            C.byref(agent.net.layout), p(agent.net.flat), p(agent.net.wpack), p(env.obs_buf), NUM_ENVS,
+            p(agent.action_var), None, 1, i,
             None, p(agent.all_acts[i % HORIZON]), p(agent.all_log_prob[i % HORIZON]), None, None, C.byref(env.cfg),
             p(env._actions_scaled), p(env.dof_targets), p(env.reset_buf), p(env.progress_buf), p(env.potentials),
             p(env.prev_potentials), p(st.root), p(st.dof_state), _lib.current_stream()))
@@ -289,7 +290,8 @@ def run_own(args):
                                       0.95, p(agent._target), p(agent.all_advantage), _lib.current_stream()))
 
     def k_vfwd(i):
-        _lib.check(agent.lib.flyb_net_forward(C.byref(agent.net.layout), p(agent.net.flat), p(agent._obs_ring),
+        _lib.check(agent.lib.flyb_net_forward(C.byref(agent.net.layout), p(agent.net.flat), p(agent.net.wpack),
+                                              p(agent._obs_ring),
                                               (HORIZON + 1) * NUM_ENVS, None, p(agent._values), _lib.current_stream()))
 
     def k_grad(i):

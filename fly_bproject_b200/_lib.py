@@ -52,16 +52,18 @@ SIGNATURES = {
     "flyb_last_error": (C.c_char_p, []),
     "flyb_device_count": (C.c_int, []),
     "flyb_net_layout": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(NetLayout)]),
+    "flyb_wpack_bytes": (C.c_size_t, [C.POINTER(NetLayout)]),
+    "flyb_pack_weights": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P]),
     "flyb_env_scratch_bytes": (C.c_size_t, [C.c_int32]),
     "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 19),
     "flyb_env_pre_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 10),
-    "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64, _P,
+    "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64, _P,
                                   _P, _P, _P, _P, C.POINTER(EnvCfg)] + [_P] * 9),
-    "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.c_int64, _P, _P, _P]),
+    "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, _P]),
     "flyb_gae": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, _P]),
     "flyb_ppo_workspace_bytes": (C.c_size_t, [C.POINTER(NetLayout), C.c_int64]),
     "flyb_ppo_grad": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 7 + [C.c_int64] + [_P] * 4),
-    "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5 + [C.c_float, _P, _P, _P]),
+    "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5 + [C.c_float, _P, _P, _P, _P]),
     "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P, _P]),
 }
 
@@ -81,7 +83,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)  # AttributeError if the .so does not export it
             fn.restype = restype
             fn.argtypes = argtypes
-        if handle.flyb_abi_version() != 1:
+        if handle.flyb_abi_version() != 2:
             raise FlybError("libflyb200.so ABI version mismatch")
         _lib = handle
     return _lib

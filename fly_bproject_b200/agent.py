@@ -34,7 +34,9 @@ class Net:
     ppo.py:266-273): the 12 tensors of ``nn.Sequential`` names above, so the 95 live-architecture ``.pth`` files load.
     """
 
-    def __init__(self, num_obs: int, num_act: int, device="cuda:0", init: bool = True):
+    def __init__(self, num_obs: int, num_act: int, device="cuda:0", init: bool = True, tensor_cores: bool = True):
+        """`tensor_cores`: run the GEMMs as 3xTF32 products on tcgen05 (where the shape is covered: num_obs <= 80,
+        num_act <= 32); False = the exact-fp32 CUDA-core kernels."""
         self.lib = _lib.lib()
         self.device = torch.device(device)
         self.layout = _lib.NetLayout()
@@ -42,6 +44,8 @@ class Net:
         self.num_obs, self.num_act = num_obs, num_act
         self.flat = torch.zeros(self.layout.total, dtype=torch.float32, device=self.device)
         self._views = self.make_views(self.flat)
+        wbytes = self.lib.flyb_wpack_bytes(C.byref(self.layout)) if tensor_cores else 0
+        self.wpack = torch.zeros(wbytes, dtype=torch.uint8, device=self.device) if wbytes else None
         if init:
             self.reset_parameters()
 
@@ -88,7 +92,14 @@ class Net:
                 if tuple(src.shape) != tuple(v.shape):
                     raise RuntimeError(f"size mismatch for {k}: checkpoint {tuple(src.shape)} vs model {tuple(v.shape)}")
                 v.copy_(src.to(device=self.device, dtype=torch.float32))
+        self.repack()
         return "<All keys matched successfully>"
+
+    def repack(self) -> None:
+        """Refresh the tensor-core weight stream after `flat` changed (flyb_ppo_apply does it in-kernel order)."""
+        if self.wpack is not None:
+            _lib.check(self.lib.flyb_pack_weights(C.byref(self.layout), _lib.ptr(self.flat), _lib.ptr(self.wpack),
+                                                  _lib.current_stream()), "flyb_pack_weights")
 
     def parameters(self):
         return list(self._views.values())
@@ -106,7 +117,8 @@ class Net:
         rows = x2.shape[0]
         mu = torch.empty((rows, self.num_act), dtype=torch.float32, device=self.device) if want_pi else None
         val = torch.empty(rows, dtype=torch.float32, device=self.device) if want_v else None
-        _lib.check(self.lib.flyb_net_forward(C.byref(self.layout), _lib.ptr(self.flat), _lib.ptr(x2), rows,
+        _lib.check(self.lib.flyb_net_forward(C.byref(self.layout), _lib.ptr(self.flat), _lib.ptr(self.wpack),
+                                             _lib.ptr(x2), rows,
                                              _lib.ptr(mu), _lib.ptr(val), _lib.current_stream()), "flyb_net_forward")
         return (mu.view(*lead, self.num_act) if want_pi else None, val.view(*lead, 1) if want_v else None)
 
@@ -170,7 +182,7 @@ class PPO:
         self.run_step = 0
         self.optim_step = 0
 
-        self.net = Net(o, a, dev)
+        self.net = Net(o, a, dev, tensor_cores=bool(_get(args, "tensor_cores", True)))
         if _get(args, "load", False):
             if self.verbose:
                 print("loaded from: ", str(args.load_path))
@@ -202,6 +214,7 @@ class PPO:
         if torch.distributed.is_available() and torch.distributed.is_initialized():
             self.world_size = torch.distributed.get_world_size()
             torch.distributed.broadcast(self.net.flat, src=0)
+            self.net.repack()
 
     # ------------------------------------------------------------------ reference-compatible views
     @property
@@ -225,7 +238,7 @@ class PPO:
         if self._fused_env:
             st = env.state
             _lib.check(self.lib.flyb_policy_act(
-                lay, p(self.net.flat), p(env.obs_buf), self.num_envs, p(self.action_var), p(noise), self.seed, 0,
+                lay, p(self.net.flat), p(self.net.wpack), p(env.obs_buf), self.num_envs, p(self.action_var), p(noise), self.seed, 0,
                 p(self._rng_counter), p(self.all_acts[i]), p(self.all_log_prob[i]), None,
                 p(self._obs_ring[0]) if i == 0 else None, C.byref(env.cfg), p(env._actions_scaled),
                 p(env.dof_targets), p(env.reset_buf), p(env.progress_buf), p(env.potentials),
@@ -238,7 +251,7 @@ class PPO:
         else:   # foreign env object behind the reference's duck-typed surface (ppo.py:210-229)
             obs = env.obs_buf.contiguous()
             _lib.check(self.lib.flyb_policy_act(
-                lay, p(self.net.flat), p(obs), self.num_envs, p(self.action_var), p(noise), self.seed, 0,
+                lay, p(self.net.flat), p(self.net.wpack), p(obs), self.num_envs, p(self.action_var), p(noise), self.seed, 0,
                 p(self._rng_counter), p(self.all_acts[i]), p(self.all_log_prob[i]), None, p(self._obs_ring[i]),
                 None, None, None, None, None, None, None, None, None, stream), "flyb_policy_act")
             env.step(self.all_acts[i])
@@ -311,7 +324,8 @@ class PPO:
     def make_data(self):
         t, n = self.rollout_size, self.num_envs
         p, stream = _lib.ptr, _lib.current_stream()
-        _lib.check(self.lib.flyb_net_forward(C.byref(self.net.layout), p(self.net.flat), p(self._obs_ring),
+        _lib.check(self.lib.flyb_net_forward(C.byref(self.net.layout), p(self.net.flat), p(self.net.wpack),
+                                             p(self._obs_ring),
                                              (t + 1) * n, None, p(self._values), stream), "flyb_net_forward")
         _lib.check(self.lib.flyb_gae(p(self.all_reward), p(self._values), p(self.env.reset_buf), t, n, self.gamma,
                                      self.lmbda, p(self._target), p(self.all_advantage), stream), "flyb_gae")
@@ -330,7 +344,8 @@ class PPO:
             torch.distributed.all_reduce(self.grad)          # SUM over ranks; the mean is taken by grad_scale
         _lib.check(self.lib.flyb_ppo_apply(
             lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.grad), p(self.exp_avg), p(self.exp_avg_sq),
-            p(self.adam_step), 1.0 / self.world_size, p(self.grad_norm), self._ws_ptr, stream), "flyb_ppo_apply")
+            p(self.adam_step), 1.0 / self.world_size, p(self.grad_norm), self._ws_ptr, p(self.net.wpack), stream),
+            "flyb_ppo_apply")
 
     def _update_body(self) -> int:
         self.make_data()

@@ -9,32 +9,9 @@
 
 #include "env_math.cuh"
 #include "mlp_simt.cuh"
+#include "philox.cuh"
 
 namespace flyb {
-
-// ---- Philox4x32-10 (Salmon et al. 2011), counter-based: one call yields four 32-bit words
-FLYB_D uint4 philox4x32_10(uint4 ctr, uint2 key) {
-  const unsigned M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-#pragma unroll
-  for (int i = 0; i < 10; ++i) {
-    const unsigned hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
-    const unsigned hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
-    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
-    key.x += W0;
-    key.y += W1;
-  }
-  return ctr;
-}
-
-// standard normal for element `idx` of draw number `offset` under `seed` (Box-Muller on two of the four words)
-FLYB_D float philox_normal(unsigned long long seed, unsigned long long offset, unsigned long long idx) {
-  const uint4 r = philox4x32_10(make_uint4((unsigned)idx, (unsigned)(idx >> 32), (unsigned)offset,
-                                           (unsigned)(offset >> 32)),
-                                make_uint2((unsigned)seed, (unsigned)(seed >> 32)));
-  const float u1 = ((float)r.x + 1.0f) * 2.3283064365386963e-10f;  // (0, 1]
-  const float u2 = (float)r.y * 2.3283064365386963e-10f;           // [0, 1)
-  return sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
-}
 
 struct ActArgs {
   const float* obs;
@@ -218,11 +195,35 @@ int validate_net(const FlybNetLayout* net, const float* params) {
   return FLYB_OK;
 }
 
+// tensor-core path (policy_kernels_tc.cu)
+bool tc_supported(const FlybNetLayout* net);
+bool tc_act_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg);
+size_t tc_wpack_bytes(const FlybNetLayout* net);
+int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st);
+int tc_launch_forward(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs,
+                      long long rows, float* mu_out, float* value_out, cudaStream_t st);
+int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs, long long rows,
+                  const float* action_var, const float* noise, uint64_t seed, uint64_t offset,
+                  const uint64_t* offset_dev, float* action, float* logp, float* mu_out, float* obs_store,
+                  const FlybEnvCfg* cfg, float* actions_scaled, float* dof_targets, int64_t* reset, int64_t* progress,
+                  float* potentials, float* prev_potentials, float* root, float* dof_state, cudaStream_t st);
+
 }  // namespace flyb
 
 using namespace flyb;
 
-extern "C" int flyb_policy_act(const FlybNetLayout* net, const float* params, const float* obs, int64_t rows,
+extern "C" size_t flyb_wpack_bytes(const FlybNetLayout* net) { return net ? tc_wpack_bytes(net) : 0; }
+
+extern "C" int flyb_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, void* stream) {
+  int rc = validate_net(net, params);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(wpack != nullptr && aligned16(wpack), "flyb_pack_weights: wpack must be a 16-byte aligned buffer");
+  FLYB_REQUIRE(tc_supported(net), "flyb_pack_weights: the tensor-core path needs num_obs <= 80 and num_act <= 32");
+  return tc_pack_weights(net, params, wpack, (cudaStream_t)stream);
+}
+
+extern "C" int flyb_policy_act(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs,
+                               int64_t rows,
                                const float* action_var, const float* noise, uint64_t seed, uint64_t offset,
                                const uint64_t* offset_dev, float* action, float* logp, float* mu_out, float* obs_store, const FlybEnvCfg* cfg,
                                float* actions_scaled, float* dof_targets, int64_t* reset, int64_t* progress,
@@ -249,6 +250,14 @@ extern "C" int flyb_policy_act(const FlybNetLayout* net, const float* params, co
     a.actions_scaled = actions_scaled; a.dof_targets = dof_targets; a.reset = (long long*)reset;
     a.progress = (long long*)progress; a.potentials = potentials; a.prev_potentials = prev_potentials;
     a.root = root; a.dof_state = dof_state;
+  }
+  if (wpack) {   // tensor-core path (3xTF32 on tcgen05, policy_kernels_tc.cu)
+    FLYB_REQUIRE(tc_act_supported(net, cfg), "flyb_policy_act: wpack given but the tensor-core path does not cover "
+                 "this shape (needs num_obs <= 80, num_act <= 32)");
+    FLYB_REQUIRE(aligned16(wpack), "wpack must be 16-byte aligned");
+    return tc_launch_act(net, params, wpack, obs, rows, action_var, noise, seed, offset, offset_dev, action, logp,
+                         mu_out, obs_store, cfg, actions_scaled, dof_targets, reset, progress, potentials,
+                         prev_potentials, root, dof_state, (cudaStream_t)stream);
   }
   const size_t smem = mlp_smem_bytes(net->k0_pad);
   const long long ntiles = (rows + MLP_TM - 1) / MLP_TM;
@@ -281,11 +290,16 @@ static int launch_forward(const FlybNetLayout* net, const float* params, const F
   return FLYB_OK;
 }
 
-extern "C" int flyb_net_forward(const FlybNetLayout* net, const float* params, const float* obs, int64_t rows,
-                                float* mu_out, float* value_out, void* stream) {
+extern "C" int flyb_net_forward(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs,
+                                int64_t rows, float* mu_out, float* value_out, void* stream) {
   int rc = validate_net(net, params);
   if (rc != FLYB_OK) return rc;
   FLYB_REQUIRE(obs && rows > 0 && (mu_out || value_out), "flyb_net_forward: NULL buffer or rows <= 0");
+  if (wpack) {
+    FLYB_REQUIRE(tc_supported(net) && aligned16(wpack), "flyb_net_forward: wpack given but the tensor-core path "
+                 "does not cover this shape (needs num_obs <= 80, num_act <= 32) or wpack is misaligned");
+    return tc_launch_forward(net, params, wpack, obs, rows, mu_out, value_out, (cudaStream_t)stream);
+  }
   FwdArgs a{obs, rows, mu_out, value_out};
   const size_t smem = mlp_smem_bytes(net->k0_pad);
   const long long ntiles = (rows + MLP_TM - 1) / MLP_TM;

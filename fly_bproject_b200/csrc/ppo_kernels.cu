@@ -19,6 +19,8 @@ namespace flyb {
 
 int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
+bool tc_supported(const FlybNetLayout* net);
+int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st);
 
 constexpr int DW_SPLITS_MAX = 64;
 constexpr int NORM_BLOCKS = 64;
@@ -484,7 +486,7 @@ extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, co
 
 extern "C" int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad,
                               float* exp_avg, float* exp_avg_sq, int64_t* step, float grad_scale,
-                              float* grad_norm_out, void* workspace, void* stream) {
+                              float* grad_norm_out, void* workspace, void* wpack, void* stream) {
   int rc = validate_net(net, params);
   if (rc != FLYB_OK) return rc;
   FLYB_REQUIRE(cfg && grad && exp_avg && exp_avg_sq && step && workspace, "flyb_ppo_apply: NULL argument");
@@ -497,5 +499,9 @@ extern "C" int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, f
   ppo_adam_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(params, grad, exp_avg, exp_avg_sq, net->total, norm_part,
                                                             (const long long*)step, a, grad_norm_out);
   FLYB_LAUNCH_CHECK("ppo_adam_kernel");
+  if (wpack) {   // keep the tensor-core weight stream in step with the parameters
+    FLYB_REQUIRE(tc_supported(net), "flyb_ppo_apply: wpack given but the tensor-core path does not cover this shape");
+    return tc_pack_weights(net, params, wpack, st);
+  }
   return FLYB_OK;
 }

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FLYB_ABI_VERSION 1
+#define FLYB_ABI_VERSION 2
 #define FLYB_MAX_DOF 64      /* asset DOF count D: 18 (nmf_no_limits_limited_Dofs.urdf) or 42 (nmf_no_limits.urdf) */
 #define FLYB_NUM_ABDOMEN 5   /* reference fly.py:299 */
 #define FLYB_NUM_LEGTIPS 6   /* reference fly.py:300 */
@@ -102,6 +102,16 @@ int flyb_device_count(void);
 
 int flyb_net_layout(int32_t num_obs, int32_t num_act, FlybNetLayout* out);
 
+/* ---- tensor-core weight stream.  The GEMMs of Net.pi / Net.v (reference ppo.py:88-102) run on tcgen05 tensor
+ *      cores as 3xTF32 products (fp32 accumulate; within ~1e-6 of an fp32 evaluation) when the caller passes
+ *      `wpack`: the parameters re-laid as hi/lo TF32 operand slabs in the order the kernel's TMA producer
+ *      consumes them.  flyb_wpack_bytes: size of that buffer, 0 when the shape is outside the tensor-core path
+ *      (it covers num_obs <= 80 and num_act <= 32; the 42-DOF joint set uses the CUDA-core fp32 path).
+ *      flyb_pack_weights must be re-run whenever `params` changes (flyb_ppo_apply does it when given wpack).
+ *      Every entry point below that takes `wpack` accepts NULL = exact-fp32 CUDA-core path. */
+size_t flyb_wpack_bytes(const FlybNetLayout* net);
+int flyb_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, void* stream);
+
 /* ---- env, kernel (a): reference Fly.get_obs + progress_buf += 1 + Fly.get_reward
  *      (fly.py:397-443, 676-681 -> compute_fly_observations 771-805, compute_fly_reward2 685-768).
  * In:  root (N,13), dof_state (N,D,2), force (N*B,3), actions_scaled (N,A) = `self.actions` (fly.py:636).
@@ -133,7 +143,7 @@ int flyb_env_pre_physics(const FlybEnvCfg* cfg, const float* actions, float* act
  *   (seed, offset + *offset_dev); offset_dev (nullable) is a device counter flyb_anneal_var advances once per
  *   step, so that a captured CUDA graph draws fresh noise at every replay.
  * Out: action (rows,A) clipped, logp (rows); mu_out, obs_store (rollout all_obs row, ppo.py:226) nullable. */
-int flyb_policy_act(const FlybNetLayout* net, const float* params, const float* obs, int64_t rows,
+int flyb_policy_act(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs, int64_t rows,
                     const float* action_var, const float* noise, uint64_t seed, uint64_t offset,
                     const uint64_t* offset_dev, float* action,
                     float* logp, float* mu_out, float* obs_store, const FlybEnvCfg* cfg, float* actions_scaled,
@@ -141,8 +151,8 @@ int flyb_policy_act(const FlybNetLayout* net, const float* params, const float* 
                     float* prev_potentials, float* root, float* dof_state, void* stream);
 
 /* Net.pi / Net.v forward over `rows` observation rows (ppo.py:88-102). mu_out (rows,A) / value_out (rows) nullable. */
-int flyb_net_forward(const FlybNetLayout* net, const float* params, const float* obs, int64_t rows, float* mu_out,
-                     float* value_out, void* stream);
+int flyb_net_forward(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs, int64_t rows,
+                     float* mu_out, float* value_out, void* stream);
 
 /* ---- agent, kernel (c): reference PPO.make_data scan (ppo.py:160-169).
  * values (T+1,N): values[t] = v(all_obs[t]) for t<T and values[T] = v(all_next_obs[T-1]); all_next_obs[t] is
@@ -160,14 +170,15 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  *   loss (1).  workspace: flyb_ppo_workspace_bytes(net, rows) bytes.
  * flyb_ppo_apply: grad *= grad_scale; clip_grad_norm_(max_grad_norm) with torch's coefficient
  *   min(1, max/(norm+1e-6)); Adam (torch defaults, no weight decay).  step (1) i64 device counter, incremented.
- *   grad_norm_out (1) nullable.  workspace: the flyb_ppo_grad workspace (only its first 256 bytes are used). */
+ *   grad_norm_out (1) nullable.  workspace: the flyb_ppo_grad workspace (only its first 256 bytes are used).
+ *   wpack (nullable): re-packed from the updated parameters in the same call. */
 size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t rows);
 int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const float* obs,
                   const float* action, const float* old_logp, const float* target, const float* advantage,
                   const float* action_var, int64_t rows, float* grad, float* loss, void* workspace, void* stream);
 int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad, float* exp_avg,
                    float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out, void* workspace,
-                   void* stream);
+                   void* wpack, void* stream);
 
 /* action_var <- max(floor, action_var - decay) (ppo.py:236-237), on the device so a captured graph can replay it;
  * step_counter (1, nullable) u64 += 1 (the Philox draw number of flyb_policy_act). */

@@ -14,10 +14,29 @@ from tests.helpers import RTOL_PPO, load_golden, oracle_tables
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
+TC = True
+
+
+@pytest.fixture(params=["tcgen05_3xtf32", "cuda_core_fp32"], autouse=True)
+def gemm_path(request):
+    """Every test runs on both GEMM paths: tensor cores (3xTF32, wpack given) and the exact-fp32 CUDA-core kernels."""
+    global TC
+    TC = request.param == "tcgen05_3xtf32"
+    yield
+
+
+def vclose(got, want, rtol, atol):
+    """Value-head comparisons.  CUDA-core fp32 path: elementwise (rtol, atol).  Tensor-core path: a 3xTF32 product
+    carries ~4e-7 * sum|a_k b_k| (hi/lo rounding; measured by tests/tc_probe), so outputs that are small next to
+    their own intermediate sums — the reference checkpoint's value head reaches +-40 — are held to 1e-5 of the
+    tensor's scale instead of 1e-5 of each element."""
+    if TC:
+        atol = max(atol, 1e-5 * float(want.abs().max()))
+    torch.testing.assert_close(got, want, rtol=rtol, atol=atol)
 
 
 def golden_net(g, tag="w0"):
-    net = fb.Net(73, 18, DEV, init=False)
+    net = fb.Net(73, 18, DEV, init=False, tensor_cores=TC)
     net.load_state_dict({k: g[f"{tag}/{k}"] for k in fo.PARAM_ORDER})
     return net
 
@@ -27,7 +46,7 @@ def test_net_forward_matches_reference_golden():
     net = golden_net(g)
     x = g["net_x"].to(DEV)
     torch.testing.assert_close(net.pi(x).cpu(), g["net_pi"], rtol=1e-5, atol=1e-5)
-    torch.testing.assert_close(net.v(x).cpu(), g["net_v"], rtol=1e-5, atol=2e-5)
+    vclose(net.v(x).cpu(), g["net_v"], rtol=1e-5, atol=2e-5)
     # checkpoint round trip in the reference's state_dict format (ppo.py:266-273)
     sd = net.state_dict()
     assert list(sd) == fo.PARAM_ORDER and sd["shared_net.0.weight"].shape == (256, 73)
@@ -38,7 +57,7 @@ def test_net_forward_matches_reference_golden():
 @pytest.mark.parametrize("o,a,rows", [(73, 18, 1), (73, 18, 16384 + 17), (145, 42, 3001)])
 def test_net_forward_matches_oracle_random_weights(o, a, rows):
     p = fo.init_params(o, a, seed=o)
-    net = fb.Net(o, a, DEV, init=False)
+    net = fb.Net(o, a, DEV, init=False, tensor_cores=TC)
     net.load_state_dict(p)
     x = torch.randn(rows, o, generator=torch.Generator().manual_seed(rows)) * 1.5
     mu, val = net._forward(x.to(DEV), True, True)
@@ -57,7 +76,7 @@ def _act(net, obs, var, noise, env=None, seed=0):
         st = env.state
         envargs = [C.byref(env.cfg), p(env._actions_scaled), p(env.dof_targets), p(env.reset_buf), p(env.progress_buf),
                    p(env.potentials), p(env.prev_potentials), p(st.root), p(st.dof_state)]
-    _lib.check(net.lib.flyb_policy_act(C.byref(net.layout), p(net.flat), p(obs), rows, p(var), p(noise), seed, 0, None,
+    _lib.check(net.lib.flyb_policy_act(C.byref(net.layout), p(net.flat), p(net.wpack), p(obs), rows, p(var), p(noise), seed, 0, None,
                                        p(action), p(logp), p(mu), None, *envargs, _lib.current_stream()))
     return action, logp, mu
 
@@ -83,7 +102,7 @@ def test_fused_act_pre_physics_equals_separate_kernels():
     for e in (e1, e2):
         e.reset_buf.copy_(mask)
         e.progress_buf.fill_(7)
-    net = fb.Net(73, 18, DEV)
+    net = fb.Net(73, 18, DEV, tensor_cores=TC)
     obs = torch.randn(n, 73, device=DEV)
     var = torch.full((18,), 0.2, device=DEV)
     noise = torch.randn(n, 18, device=DEV)
@@ -101,7 +120,7 @@ def test_fused_act_pre_physics_equals_separate_kernels():
 
 
 def test_philox_noise_is_standard_normal_and_keyed():
-    net = fb.Net(73, 18, DEV)
+    net = fb.Net(73, 18, DEV, tensor_cores=TC)
     n = 20000
     obs = torch.randn(n, 73, device=DEV)
     var = torch.full((18,), 0.04, device=DEV)
@@ -135,8 +154,8 @@ def test_gae_matches_reference_golden():
     values = net.v(ring).squeeze(-1).contiguous()
     reset_last = (1 - g["roll_done"].squeeze(-1)).to(DEV)
     target, adv = _gae(g["roll_rew"].squeeze(-1).contiguous().to(DEV), values, reset_last)
-    torch.testing.assert_close(target.cpu(), g["roll_target"].squeeze(-1), rtol=1e-5, atol=2e-5)
-    torch.testing.assert_close(adv.cpu(), g["roll_adv"].squeeze(-1), rtol=1e-5, atol=5e-5)
+    vclose(target.cpu(), g["roll_target"].squeeze(-1), rtol=1e-5, atol=2e-5)
+    vclose(adv.cpu(), g["roll_adv"].squeeze(-1), rtol=1e-5, atol=5e-5)
 
 
 @pytest.mark.parametrize("t,n", [(32, 16384), (1, 33), (7, 1000), (128, 4097)])
@@ -204,7 +223,7 @@ def test_ppo_minibatch_step_matches_reference_golden():
     step = torch.zeros(1, dtype=torch.int64, device=DEV)
     gn = torch.zeros(1, device=DEV)
     _lib.check(lib.flyb_ppo_apply(C.byref(net.layout), C.byref(cfg), p(net.flat), p(grad), p(m), p(v), p(step), 1.0,
-                                  p(gn), wsp, _lib.current_stream()))
+                                  p(gn), wsp, p(net.wpack), _lib.current_stream()))
     torch.cuda.synchronize()
     assert int(step.item()) == 1
     assert float(gn) == pytest.approx(norm, rel=1e-4)
@@ -256,7 +275,7 @@ def test_full_update_matches_reference_golden_75_steps():
     """PPO.update through the drop-in class on the golden rollout: 5 epochs x 15 minibatches (log.txt:49)."""
     g = load_golden("ppo_n64_t32.npz")
     n, t_roll, mc = [int(x) for x in g["meta"]]
-    args = fb.make_args(num_envs=n, sim_device=DEV, horizon=t_roll, verbose=False)
+    args = fb.make_args(num_envs=n, sim_device=DEV, horizon=t_roll, verbose=False, tensor_cores=TC)
     agent = fb.PPO(args, env=_ReplayEnv(g))
     assert agent.mini_chunk_size == mc and agent.rollout_size == t_roll
     agent.net.load_state_dict({k: g["w0/" + k] for k in fo.PARAM_ORDER})
@@ -269,8 +288,8 @@ def test_full_update_matches_reference_golden_75_steps():
     agent.env.reset_buf = (1 - g["roll_done"].squeeze(-1)).to(DEV)
     assert agent.all_done.shape == (n, 1) and agent.all_done.dtype == torch.int64       # ppo.py:230 quirk
     obs, acts, logp, target, adv = agent.make_data()
-    torch.testing.assert_close(target.cpu(), g["roll_target"], rtol=1e-5, atol=2e-5)
-    torch.testing.assert_close(adv.cpu(), g["roll_adv"], rtol=1e-5, atol=5e-5)
+    vclose(target.cpu(), g["roll_target"], rtol=1e-5, atol=2e-5)
+    vclose(adv.cpu(), g["roll_adv"], rtol=1e-5, atol=5e-5)
     agent.update()
     assert agent.optim_step == 75 and int(agent.adam_step.item()) == 75
     sd = agent.net.state_dict()
@@ -283,7 +302,7 @@ def test_full_update_matches_reference_golden_75_steps():
 def test_ppo_grad_matches_oracle_autograd_other_shapes(o, a, rows):
     gen = torch.Generator().manual_seed(rows + o)
     p0 = fo.init_params(o, a, seed=3)
-    net = fb.Net(o, a, DEV, init=False)
+    net = fb.Net(o, a, DEV, init=False, tensor_cores=TC)
     net.load_state_dict(p0)
     obs = torch.randn(rows, o, generator=gen)
     var = torch.full((a,), 0.15)
@@ -311,7 +330,7 @@ def test_run_loop_matches_oracle_rollout_and_update():
     explicit noise; two env steps then compare rollout rows."""
     n = 512
     t = oracle_tables("limited_18", n, True)
-    args = fb.make_args(num_envs=n, sim_device=DEV, horizon=16, verbose=False, state_pool=2, seed=77)
+    args = fb.make_args(num_envs=n, sim_device=DEV, horizon=16, verbose=False, state_pool=2, seed=77, tensor_cores=TC)
     agent = fb.PPO(args)
     env = agent.env
     p0 = {k: v.cpu() for k, v in agent.net.state_dict().items()}
