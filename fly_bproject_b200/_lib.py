@@ -52,6 +52,7 @@ SIGNATURES = {
     "flyb_last_error": (C.c_char_p, []),
     "flyb_device_count": (C.c_int, []),
     "flyb_net_layout": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(NetLayout)]),
+    "flyb_debug_set_trace": (C.c_int, [_P]),
     "flyb_wpack_bytes": (C.c_size_t, [C.POINTER(NetLayout)]),
     "flyb_pack_weights": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P]),
     "flyb_env_scratch_bytes": (C.c_size_t, [C.c_int32]),

@@ -1,27 +1,30 @@
 // Tensor-core forward of the actor-critic MLP (reference ppo.py:10-38, 88-102) on 128-row tiles:
 // tcgen05.mma kind::tf32 (3xTF32, fp32 accumulate in tensor memory), weights streamed L2 -> shared memory by
-// 1-D bulk TMA copies through a 32-stage mbarrier ring, activations kept in TENSOR MEMORY between layers
-// (the A operand of every GEMM is read from TMEM, "TS" mode), so that an observation row never leaves the SM
-// between the first layer and the action / value it produces.
+// 1-D bulk TMA copies through an 8-stage (64 KB) mbarrier ring.  The observation tile is the only activation that lives
+// in shared memory (hi/lo split, UMMA K-major layout: the A operand of layer 1); every later activation stays
+// in TENSOR MEMORY and is fed back as the A operand of the next GEMM ("TS" mode), so a row never leaves the SM
+// between the observation and the action / value it produces.
 //
 // One CTA = 10 warps:  warps 0-7  epilogue (TMEM -> registers -> bias + ELU -> hi/lo split -> TMEM),
-//                      warp  8    TMA producer (one lane): observation tiles + the packed weight stream,
-//                      warp  9    MMA issuer (one lane).
+//                      warp  8    TMA producer: observation tiles + the packed weight stream,
+//                      warp  9    MMA issuer (warp-uniform code, one elected lane issues).
 // Epilogue warp w owns TMEM lanes 32*(w%4)..+31 (row r of the tile = lane r) and column half w/4.
 //
 // Layer schedule of one tile (K0 = 80 padded obs, trunk 256 -> 128, heads 64 -> {A<=32, 1}):
-//   the 256-wide first layer is produced in 8 chunks of 32 columns; chunk c is  D1[c&1] = A1 * W1[c]^T  (N = 32),
+//   the 256-wide first layer is produced in 4 chunks of 64 columns; chunk c is  D1[c&1] = X * W1[c]^T  (N = 64),
 //   its epilogue writes ELU(D1 + b1) as the K-chunk A2[c&1] of the second layer, and  D2 += A2[c&1] * W2[:, c]^T
-//   (N = 128) consumes it.  D1 / A2 are double buffered: the epilogue of chunk c overlaps the MMAs of chunks
-//   c-1 (layer 2) and c+1 (layer 1).  Then  A3 = ELU(D2 + b2),  D3 = A3 * W3^T (mean and/or value head, N = 64
-//   each),  A4 = ELU(D3pi + b3),  D4 = A4 * W4^T (N = 32); the 64 -> 1 value output is a register dot product.
+//   (N = 128) consumes it.  D1 / A2 are double buffered and the MMA warp issues  W1[0], W1[1], (W2[c], W1[c+2])...
+//   so the epilogue of chunk c overlaps the layer-2 MMAs of chunk c-1 and the layer-1 MMAs of chunk c+1.
+//   Then  A3 = ELU(D2 + b2),  D3 = A3 * W3^T (mean and/or value head, N = 64 each),  A4 = ELU(D3pi + b3),
+//   D4 = A4 * W4^T (N = 32); the 64 -> 1 value output is a register dot product.
 //
-// TMEM columns (512 allocated):   A1 hi|lo [0,160)   D1[2] [160,224)   A2[2] hi|lo [224,352)   D2 [352,480)
-//   after the trunk:              A3 hi|lo [0,256)   D3 pi|v [256,384) A4 hi|lo [384,512)      D4 [0,32)
+// TMEM columns (512 allocated):   D1[2] [0,128)      A2[2] hi|lo [128,384)     D2 [384,512)
+//   after the trunk:              A3 hi|lo [0,256)   D3 pi|v [256,384)         A4 hi|lo [384,512)    D4 [0,32)
 //
-// Packed weight stream (flyb_pack_weights): 4 KB stages in consumption order, each k-step (8 k) of an N-row
+// Packed weight stream (flyb_pack_weights): 8 KB stages in consumption order, each k-step (8 k) of an N-row
 // operand stored as [hi slab | lo slab], slab = N x 32 bytes in the no-swizzle K-major core-matrix layout
-// (tc_common.cuh).  Trunk = 8 x (W1 chunk: 5 stages, W2 K-chunk: 8 stages), then W3pi (16), W3v (16), W4 (4).
+// (tc_common.cuh).  Trunk = W1[0], W1[1], W2[0], W1[2], W2[1], W1[3], W2[2], W2[3]  (W1 chunk: 5 stages,
+// W2 K-chunk: 8 stages), then W3pi (8), W3v (8), W4 (2).
 #pragma once
 #include "tc_common.cuh"
 
@@ -31,33 +34,37 @@ namespace tcm {
 constexpr int TM = 128;
 constexpr int K0 = 80;
 constexpr int H1 = 256, H2 = 128, H3 = 64, APAD = 32;
-constexpr int CH = 32, NCH = H1 / CH;
-constexpr int STAGE = 4096;
-constexpr int NST = 32;                        // ring stages (128 KB)
+constexpr int CH = 64, NCH = H1 / CH;
+constexpr int STAGE = 8192;
+constexpr int NST = 8, LOG_NST = 3;            // ring stages (64 KB)
 constexpr int EPI_WARPS = 8, EPI_THREADS = EPI_WARPS * 32;
 constexpr int PRODUCER_WARP = 8, MMA_WARP = 9;
 constexpr int THREADS = 320;
 
 constexpr int W1C_STAGES = (K0 / 8) * 2 * (CH * 32) / STAGE;   // 5
 constexpr int W2C_STAGES = (CH / 8) * 2 * (H2 * 32) / STAGE;   // 8
-constexpr int TRUNK_STAGES = NCH * (W1C_STAGES + W2C_STAGES);  // 104
-constexpr int W3_STAGES = (H2 / 8) * 2 * (H3 * 32) / STAGE;    // 16
-constexpr int W4_STAGES = (H3 / 8) * 2 * (APAD * 32) / STAGE;  // 4
+constexpr int TRUNK_STAGES = NCH * (W1C_STAGES + W2C_STAGES);  // 52
+constexpr int W3_STAGES = (H2 / 8) * 2 * (H3 * 32) / STAGE;    // 8
+constexpr int W4_STAGES = (H3 / 8) * 2 * (APAD * 32) / STAGE;  // 2
 constexpr int OFF_W3PI = TRUNK_STAGES, OFF_W3V = OFF_W3PI + W3_STAGES, OFF_W4 = OFF_W3V + W3_STAGES;
-constexpr int FWD_STAGES = OFF_W4 + W4_STAGES;                 // 140 stages = 560 KB
+constexpr int FWD_STAGES = OFF_W4 + W4_STAGES;                 // 70 stages = 560 KB
 
 // TMEM column map
-constexpr uint32_t C_A1H = 0, C_A1L = K0, C_D1 = 160, C_A2 = 224, C_D2 = 352;
+constexpr uint32_t C_D1 = 0, C_A2 = 128, C_D2 = 384;
 constexpr uint32_t C_A3H = 0, C_A3L = H2, C_D3 = 256, C_A4H = 384, C_A4L = 448, C_D4 = 0;
 
 // bias block in shared memory (floats)
 constexpr int B_B1 = 0, B_B2 = 256, B_B3PI = 384, B_B3V = 448, B_B4 = 512, B_W4V = 544, B_B4V = 608, B_TOTAL = 640;
 
-constexpr size_t OBS_STAGE_BYTES = (size_t)TM * K0 * 4;   // 40960: room for any O <= 80
+__host__ __device__ inline size_t obs_stage_bytes(int O) { return ((size_t)TM * O * 4 + 127) / 128 * 128; }
+constexpr size_t X_PLANE_BYTES = (size_t)TM * K0 * 4;     // 40960: one of the hi / lo planes of the A operand
+constexpr uint32_t X_LBO = TM * 16, X_SBO = 128;          // K-major no-swizzle: [k/4][row][4 floats]
 
 struct Smem {
   unsigned char* ring;
-  float* obs;
+  float* xhi;            // layer-1 A operand, hi plane (UMMA layout)
+  float* xlo;
+  float* obs;            // raw observation tile (row-major, O floats per row)
   float* out;
   float* bias;
   float* vpart;
@@ -65,18 +72,22 @@ struct Smem {
   uint32_t* tmem_slot;
 };
 
-__host__ __device__ inline size_t smem_bytes(size_t out_bytes) {
-  return 1024 + (size_t)NST * STAGE + OBS_STAGE_BYTES + ((out_bytes + 127) / 128 * 128) + B_TOTAL * 4 + TM * 4 +
-         (2 * NST + 6) * 8 + 16;
+__host__ __device__ inline size_t smem_bytes(int O, size_t out_bytes) {
+  return 1024 + (size_t)NST * STAGE + 2 * X_PLANE_BYTES + obs_stage_bytes(O) + ((out_bytes + 127) / 128 * 128) +
+         B_TOTAL * 4 + TM * 4 + (2 * NST + 6) * 8 + 16;
 }
 
-FLYB_D Smem carve(unsigned char* raw, size_t out_bytes) {
+FLYB_D Smem carve(unsigned char* raw, int O, size_t out_bytes) {
   Smem s;
   uintptr_t p = (reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023;
   s.ring = reinterpret_cast<unsigned char*>(p);
   p += (size_t)NST * STAGE;
+  s.xhi = reinterpret_cast<float*>(p);
+  p += X_PLANE_BYTES;
+  s.xlo = reinterpret_cast<float*>(p);
+  p += X_PLANE_BYTES;
   s.obs = reinterpret_cast<float*>(p);
-  p += OBS_STAGE_BYTES;
+  p += obs_stage_bytes(O);
   s.out = reinterpret_cast<float*>(p);
   p += (out_bytes + 127) / 128 * 128;
   s.bias = reinterpret_cast<float*>(p);
@@ -96,61 +107,128 @@ FLYB_D Smem carve(unsigned char* raw, size_t out_bytes) {
 FLYB_D void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------- MMA issuer
+// The MMA warp runs warp-uniform code (all 32 lanes wait on the barriers and compute the descriptors, which keeps
+// them in uniform registers); `leader` (elect.sync) predicates the tcgen05 instructions themselves.
+FLYB_D void umma_ts_if(uint32_t leader, uint32_t d, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc), "r"(leader)
+      : "memory");
+}
+FLYB_D void umma_ss_if(uint32_t leader, uint32_t d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc), "r"(leader)
+      : "memory");
+}
+FLYB_D void umma_commit_if(uint32_t leader, uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(tc::smem_u32(bar)),
+      "r"(leader)
+      : "memory");
+}
+
 struct MmaState {
-  uint32_t tb, ring;
+  uint32_t leader;
+  uint32_t ring;       // shared-memory byte address of the weight ring
   uint64_t *full, *empty;
-  uint32_t g;          // stages consumed so far (running over tiles)
-  uint32_t acquired;   // stages whose full barrier has been waited for
+  uint32_t stage;      // stages consumed so far (running over tiles)
 };
 
-// One GEMM segment: D[128 x N] (+)= A[128 x 8*ksteps] * B^T, A hi/lo in TMEM, B = the next 2*ksteps slabs of the ring.
-template <int N>
-FLYB_D void mma_segment(MmaState& m, uint32_t a_hi, uint32_t a_lo, uint32_t d, int ksteps, bool accumulate) {
+// One GEMM segment: D[128 x N] (+)= A[128 x 8*KSTEPS] * B^T with B = the next 2*KSTEPS slabs of the ring.
+// A_SMEM = false: a_hi / a_lo are TMEM addresses (8 columns per k-step);
+// A_SMEM = true:  a_hi / a_lo are shared-memory byte addresses of the X planes (2 * X_LBO bytes per k-step).
+template <int N, int KSTEPS, bool A_SMEM>
+FLYB_D void mma_segment(MmaState& m, uint32_t a_hi, uint32_t a_lo, uint32_t d, bool accumulate) {
   constexpr uint32_t SLAB = N * 32;
-  constexpr uint32_t SPS = STAGE / SLAB;
   const uint32_t idesc = tc::umma_idesc_tf32(N);
-  for (int ks = 0; ks < ksteps; ++ks) {
-    const uint32_t slab_hi = 2 * ks, slab_lo = 2 * ks + 1;
-    const uint32_t st_hi = m.g + slab_hi / SPS, st_lo = m.g + slab_lo / SPS;
-    if (m.acquired <= st_lo) {
-      while (m.acquired <= st_lo) {
-        tc::mbar_wait(&m.full[m.acquired % NST], (m.acquired / NST) & 1u);
-        ++m.acquired;
-      }
-      tc::tc_fence_after();
+  auto issue3 = [&](int ks, uint32_t hi_addr, uint32_t lo_addr) {
+    const uint64_t b_hi = tc::umma_smem_desc(hi_addr, N * 16, 128);
+    const uint64_t b_lo = tc::umma_smem_desc(lo_addr, N * 16, 128);
+    const uint32_t acc0 = (accumulate || ks > 0) ? 1u : 0u;
+    if constexpr (A_SMEM) {
+      const uint64_t xa_hi = tc::umma_smem_desc(a_hi + (uint32_t)ks * 2u * X_LBO, X_LBO, X_SBO);
+      const uint64_t xa_lo = tc::umma_smem_desc(a_lo + (uint32_t)ks * 2u * X_LBO, X_LBO, X_SBO);
+      umma_ss_if(m.leader, d, xa_lo, b_hi, idesc, acc0);
+      umma_ss_if(m.leader, d, xa_hi, b_lo, idesc, 1u);
+      umma_ss_if(m.leader, d, xa_hi, b_hi, idesc, 1u);
+    } else {
+      umma_ts_if(m.leader, d, a_lo + 8 * ks, b_hi, idesc, acc0);
+      umma_ts_if(m.leader, d, a_hi + 8 * ks, b_lo, idesc, 1u);
+      umma_ts_if(m.leader, d, a_hi + 8 * ks, b_hi, idesc, 1u);
     }
-    const uint32_t addr_hi = m.ring + (st_hi % NST) * STAGE + (slab_hi % SPS) * SLAB;
-    const uint32_t addr_lo = m.ring + (st_lo % NST) * STAGE + (slab_lo % SPS) * SLAB;
-    const uint64_t b_hi = tc::umma_smem_desc(addr_hi, N * 16, 128);
-    const uint64_t b_lo = tc::umma_smem_desc(addr_lo, N * 16, 128);
-    tc::umma_tf32_ts(d, a_lo + 8 * ks, b_hi, idesc, accumulate || ks > 0);
-    tc::umma_tf32_ts(d, a_hi + 8 * ks, b_lo, idesc, true);
-    tc::umma_tf32_ts(d, a_hi + 8 * ks, b_hi, idesc, true);
-    if (SPS == 1) {
-      tc::umma_commit(&m.empty[st_hi % NST]);
-      tc::umma_commit(&m.empty[st_lo % NST]);
-    } else if (slab_lo % SPS == SPS - 1) {
-      tc::umma_commit(&m.empty[st_lo % NST]);
+  };
+  static_assert(2 * SLAB <= STAGE, "a k-step (hi + lo slab) must fit one stage");
+  constexpr int KPS = STAGE / (2 * SLAB);   // k-steps per stage
+  static_assert(KSTEPS % KPS == 0, "segment must end on a stage boundary");
+  uint32_t base = 0, slot = 0;
+#pragma unroll
+  for (int ks = 0; ks < KSTEPS; ++ks) {
+    if (ks % KPS == 0) {
+      slot = m.stage & (NST - 1);
+      tc::mbar_wait(&m.full[slot], (m.stage >> LOG_NST) & 1u);
+      tc::tc_fence_after();
+      base = m.ring + slot * STAGE;
+    }
+    const uint32_t hi_addr = base + (uint32_t)(ks % KPS) * 2u * SLAB;
+    issue3(ks, hi_addr, hi_addr + SLAB);
+    if (ks % KPS == KPS - 1) {
+      umma_commit_if(m.leader, &m.empty[slot]);
+      ++m.stage;
     }
   }
-  m.g += (uint32_t)(2 * ksteps) / SPS;
 }
 
 // ---------------------------------------------------------------------------------------------- epilogue helpers
-// y = ELU(acc + bias) for 16 consecutive accumulator columns, split to hi/lo and stored as the next A operand
-FLYB_D void epi_elu16(uint32_t tb, uint32_t lane_base, uint32_t d_col, uint32_t ah_col, uint32_t al_col,
-                      const float* bias, float* keep) {
-  uint32_t v[16], hi[16], lo[16];
-  tc::tmem_ld16(tc::tmem_addr(tb, lane_base, d_col), v);
+// ELU of the tensor-core path: exp through ex2.approx (|error| <= ~2.4e-7 absolute), x > 0 ? x : exp(x) - 1
+FLYB_D float elu_fast(float y) {
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(y * 1.4426950408889634f));
+  return y > 0.0f ? y : e - 1.0f;
+}
+// hi = rna_tf32(y); lo = y - hi (exact; the tensor core reads its upper 19 bits)
+FLYB_D void split_fast(float y, uint32_t& hi, uint32_t& lo) {
+  hi = tc::tf32_rna_bits(y);
+  lo = __float_as_uint(y - __uint_as_float(hi));
+}
+
+// y = ELU(acc + bias) for 32 consecutive accumulator columns, split to hi/lo and stored as the next A operand
+FLYB_D void epi_elu32(uint32_t tb, uint32_t lane_base, uint32_t d_col, uint32_t ah_col, uint32_t al_col,
+                      const float* bias) {
+  uint32_t v0[16], v1[16];
+  tc::tmem_ld16(tc::tmem_addr(tb, lane_base, d_col), v0);
+  tc::tmem_ld16(tc::tmem_addr(tb, lane_base, d_col + 16), v1);
   tc::tmem_wait_ld();
+  const float4* b4 = reinterpret_cast<const float4*>(bias);
+  {
+    uint32_t hi[16], lo[16];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const float y = elu(__uint_as_float(v[j]) + bias[j]);
-    if (keep) keep[j] = y;
-    tc::split_tf32(y, hi[j], lo[j]);
+    for (int q = 0; q < 4; ++q) {
+      const float4 b = b4[q];
+      split_fast(elu_fast(__uint_as_float(v0[4 * q + 0]) + b.x), hi[4 * q + 0], lo[4 * q + 0]);
+      split_fast(elu_fast(__uint_as_float(v0[4 * q + 1]) + b.y), hi[4 * q + 1], lo[4 * q + 1]);
+      split_fast(elu_fast(__uint_as_float(v0[4 * q + 2]) + b.z), hi[4 * q + 2], lo[4 * q + 2]);
+      split_fast(elu_fast(__uint_as_float(v0[4 * q + 3]) + b.w), hi[4 * q + 3], lo[4 * q + 3]);
+    }
+    tc::tmem_st16(tc::tmem_addr(tb, lane_base, ah_col), hi);
+    tc::tmem_st16(tc::tmem_addr(tb, lane_base, al_col), lo);
   }
-  tc::tmem_st16(tc::tmem_addr(tb, lane_base, ah_col), hi);
-  tc::tmem_st16(tc::tmem_addr(tb, lane_base, al_col), lo);
+  {
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 b = b4[4 + q];
+      split_fast(elu_fast(__uint_as_float(v1[4 * q + 0]) + b.x), hi[4 * q + 0], lo[4 * q + 0]);
+      split_fast(elu_fast(__uint_as_float(v1[4 * q + 1]) + b.y), hi[4 * q + 1], lo[4 * q + 1]);
+      split_fast(elu_fast(__uint_as_float(v1[4 * q + 2]) + b.z), hi[4 * q + 2], lo[4 * q + 2]);
+      split_fast(elu_fast(__uint_as_float(v1[4 * q + 3]) + b.w), hi[4 * q + 3], lo[4 * q + 3]);
+    }
+    tc::tmem_st16(tc::tmem_addr(tb, lane_base, ah_col + 16), hi);
+    tc::tmem_st16(tc::tmem_addr(tb, lane_base, al_col + 16), lo);
+  }
 }
 
 struct FwdArgs {
@@ -160,17 +238,25 @@ struct FwdArgs {
   long long rows;
   int O, A;
   size_t out_bytes;
+  unsigned long long* trace;   // debug: clock64 timeline of CTA 0 (nullable; flyb_debug_set_trace)
 };
 
-// Per-tile consumer of the results; called by the 256 epilogue threads.
-//   begin_tile(...)                      after the observation tile is staged in shared memory (obs_s, row-major)
-//   pi(row_in_tile, half, mu[32], ...)   both column halves call it with the full mu row (ELU applied)
-//   value(row_in_tile, v)                half 0 only
-// See policy_kernels_tc.cu for the implementations.
+// trace slots: [0,64) MMA warp, [64,128) epilogue warp 0 lane 0
+FLYB_D void trace_mark(unsigned long long* trace, int& idx, int limit) {
+  if (trace != nullptr && blockIdx.x == 0 && idx < limit) trace[idx++] = clock64();
+}
 
+// Per-tile consumer of the results (`Final`), called by the 256 epilogue threads:
+//   begin_tile(s, row0, r, nrows)          after the raw observation tile is in shared memory (s.obs, row-major)
+//   obs_consumed(s)                        after the A operand of layer 1 was built; must arrive on s.obs_empty
+//   pre_pi(s, row0, r, h, nrows)           before the last accumulator is waited for (mu-independent work)
+//   pi(s, row0, r, h, nrows, mu[32])       both column halves call it with the full mu row (ELU applied)
+//   value(row0, r, nrows, v)               half 0 only
+//   finish(s)                              once, after the last tile
+// Implementations: policy_kernels_tc.cu.
 template <bool WANT_PI, bool WANT_V, class Final>
 FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final& fin, unsigned char* smem_raw) {
-  const Smem s = carve(smem_raw, a.out_bytes);
+  const Smem s = carve(smem_raw, a.O, a.out_bytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int O = a.O;
   const long long ntiles = (a.rows + TM - 1) / TM;
@@ -210,71 +296,82 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
   const uint32_t tb = *s.tmem_slot;
 
   if (warp == PRODUCER_WARP) {
-    // =========================================================================== TMA producer
-    if (lane == 0) {
-      uint32_t gs = 0, obs_phase = 0;
-      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const long long row0 = tile * TM;
-        const int nrows = (int)min((long long)TM, a.rows - row0);
-        const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
-        const float* src = a.obs + (size_t)row0 * O;
-        tc::mbar_wait(s.obs_empty, obs_phase ^ 1u);   // the epilogue warps are done with the previous tile's rows
-        obs_phase ^= 1u;
-        if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
-          tc::mbar_arrive_expect_tx(s.obs_full, bytes);
-          tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
-        }
-        auto stream = [&](int first, int count) {
-          for (int i = 0; i < count; ++i, ++gs) {
-            const uint32_t slot = gs % NST;
-            tc::mbar_wait(&s.empty[slot], ((gs / NST) & 1u) ^ 1u);
-            tc::mbar_arrive_expect_tx(&s.full[slot], STAGE);
-            tc::tma_load_1d(s.ring + (size_t)slot * STAGE, a.wpack + (size_t)(first + i) * STAGE, STAGE, &s.full[slot]);
-          }
-        };
-        stream(0, TRUNK_STAGES);
-        if (WANT_PI) stream(OFF_W3PI, W3_STAGES);
-        if (WANT_V) stream(OFF_W3V, W3_STAGES);
-        if (WANT_PI) stream(OFF_W4, W4_STAGES);
+    // =========================================================================== TMA producer (warp-uniform)
+    const uint32_t leader = tc::elect_one() ? 1u : 0u;
+    const uint32_t ring = tc::smem_u32(s.ring);
+    uint32_t gs = 0, obs_phase = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long row0 = tile * TM;
+      const int nrows = (int)min((long long)TM, a.rows - row0);
+      const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
+      const float* src = a.obs + (size_t)row0 * O;
+      tc::mbar_wait(s.obs_empty, obs_phase ^ 1u);   // the epilogue warps are done with the previous tile's rows
+      obs_phase ^= 1u;
+      if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
+        tc::mbar_arrive_expect_tx(s.obs_full, bytes);
+        tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
       }
+      auto stream = [&](int first, int count) {
+        const unsigned char* g = a.wpack + (size_t)first * STAGE;
+        for (int i = 0; i < count; ++i, ++gs, g += STAGE) {
+          const uint32_t slot = gs & (NST - 1);
+          tc::mbar_wait(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
+          const uint32_t bar = tc::smem_u32(&s.full[slot]);
+          asm volatile(
+              "{\n\t.reg .pred q;\n\t.reg .b64 st;\n\tsetp.ne.b32 q, %4, 0;\n\t"
+              "@q mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %3;\n\t"
+              "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2], %3, [%0];\n\t}" ::"r"(bar),
+              "r"(ring + slot * STAGE), "l"(g), "r"((uint32_t)STAGE), "r"(leader)
+              : "memory");
+        }
+      };
+      stream(0, TRUNK_STAGES);
+      if (WANT_PI) stream(OFF_W3PI, W3_STAGES);
+      if (WANT_V) stream(OFF_W3V, W3_STAGES);
+      if (WANT_PI) stream(OFF_W4, W4_STAGES);
     }
   } else if (warp == MMA_WARP) {
-    // =========================================================================== MMA issuer
-    if (lane == 0) {
-      MmaState m{tb, tc::smem_u32(s.ring), s.full, s.empty, 0u, 0u};
-      uint32_t pa[2] = {0u, 0u};
-      auto wait_a = [&](int b) {
-        tc::mbar_wait(&s.bar_a[b], pa[b]);
-        pa[b] ^= 1u;
-        tc::tc_fence_after();
-      };
-      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        wait_a(0);   // A1 staged
-        // issue order (== packed stream order): W1[0], W1[1], then (W2[c], W1[c+2]) for c = 0..7, so that the
-        // epilogue of chunk c overlaps the layer-2 MMAs of chunk c-1 and the layer-1 MMAs of chunk c+1
-        mma_segment<CH>(m, tb + C_A1H, tb + C_A1L, tb + C_D1, K0 / 8, false);
-        tc::umma_commit(&s.bar_d[0]);
-        mma_segment<CH>(m, tb + C_A1H, tb + C_A1L, tb + C_D1 + 32, K0 / 8, false);
-        tc::umma_commit(&s.bar_d[1]);
-        for (int c = 0; c < NCH; ++c) {
-          const int b = c & 1;
-          wait_a(b);   // A2[b] = ELU(D1[b] + b1) written, D1[b] drained
-          mma_segment<H2>(m, tb + C_A2 + 64 * b, tb + C_A2 + 64 * b + 32, tb + C_D2, CH / 8, c > 0);
-          if (c + 2 < NCH) {
-            mma_segment<CH>(m, tb + C_A1H, tb + C_A1L, tb + C_D1 + 32 * b, K0 / 8, false);
-            tc::umma_commit(&s.bar_d[b]);
-          }
+    // =========================================================================== MMA issuer (warp-uniform)
+    MmaState m{tc::elect_one() ? 1u : 0u, tc::smem_u32(s.ring), s.full, s.empty, 0u};
+    const uint32_t xh = tc::smem_u32(s.xhi), xl = tc::smem_u32(s.xlo);
+    uint32_t pa0 = 0u, pa1 = 0u;
+    int ti = 0;
+    unsigned long long* mtrace = (lane == 0) ? a.trace : nullptr;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      trace_mark(mtrace, ti, 64);
+      tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; tc::tc_fence_after();   // X staged
+      trace_mark(mtrace, ti, 64);
+      mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);
+      mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1 + CH, false);
+      umma_commit_if(m.leader, &s.bar_d[1]);
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        const int b = c & 1;
+        if (b == 0) { tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; }
+        else        { tc::mbar_wait(&s.bar_a[1], pa1); pa1 ^= 1u; }
+        tc::tc_fence_after();           // A2[b] = ELU(D1[b] + b1) written, D1[b] drained
+        trace_mark(mtrace, ti, 64);
+        mma_segment<H2, CH / 8, false>(m, tb + C_A2 + 128 * b, tb + C_A2 + 128 * b + CH, tb + C_D2, c > 0);
+        if (c + 2 < NCH) {
+          mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1 + CH * b, false);
+          umma_commit_if(m.leader, &s.bar_d[b]);
         }
-        tc::umma_commit(&s.bar_d[0]);   // D2 complete
-        wait_a(0);                      // A3
-        if (WANT_PI) mma_segment<H3>(m, tb + C_A3H, tb + C_A3L, tb + C_D3, H2 / 8, false);
-        if (WANT_V) mma_segment<H3>(m, tb + C_A3H, tb + C_A3L, tb + C_D3 + 64, H2 / 8, false);
-        tc::umma_commit(&s.bar_d[0]);   // D3
-        if (WANT_PI) {
-          wait_a(0);                    // A4
-          mma_segment<APAD>(m, tb + C_A4H, tb + C_A4L, tb + C_D4, H3 / 8, false);
-          tc::umma_commit(&s.bar_d[0]); // D4
-        }
+      }
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D2 complete
+      trace_mark(mtrace, ti, 64);
+      tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; tc::tc_fence_after();   // A3
+      trace_mark(mtrace, ti, 64);
+      if (WANT_PI) mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3, false);
+      if (WANT_V) mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3 + H3, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D3
+      if (WANT_PI) {
+        trace_mark(mtrace, ti, 64);
+        tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; tc::tc_fence_after(); // A4
+        trace_mark(mtrace, ti, 64);
+        mma_segment<APAD, H3 / 8, false>(m, tb + C_A4H, tb + C_A4L, tb + C_D4, false);
+        umma_commit_if(m.leader, &s.bar_d[0]); // D4
+        trace_mark(mtrace, ti, 64);
       }
     }
   } else {
@@ -282,13 +379,9 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
     const int q = warp & 3, h = warp >> 2;
     const uint32_t lane_base = (uint32_t)q * 32u;
     const int r = q * 32 + lane;   // row inside the tile
-    uint32_t pd[2] = {0u, 0u};
-    uint32_t obs_phase = 0;
-    auto wait_d = [&](int b) {
-      tc::mbar_wait(&s.bar_d[b], pd[b]);
-      pd[b] ^= 1u;
-      tc::tc_fence_after();
-    };
+    uint32_t pd0 = 0u, pd1 = 0u, obs_phase = 0u;
+    int ti = 64;
+    unsigned long long* etrace = (threadIdx.x == 0) ? a.trace : nullptr;
     auto arrive_a = [&](int b) {
       tc::tmem_wait_st();
       tc::tc_fence_before();
@@ -309,84 +402,98 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
         tc::fence_proxy_async();
         epi_bar_sync();
       }
-      fin.begin_tile(s, row0, nrows, by_tma);
+      trace_mark(etrace, ti, 128);
+      fin.begin_tile(s, row0, r, nrows);
 
-      // ---- A1 = split(obs row), zero padded to K0 columns; rows beyond nrows are zero
+      // ---- X = split(obs row) in the UMMA K-major layout, zero padded to K0 columns and TM rows
       {
         const float* xr = s.obs + r * O;
+        const bool live = r < nrows;
+        float x[K0 / 2];
 #pragma unroll
-        for (int gI = 0; gI < K0 / 16; ++gI) {
-          const int c0 = h * (K0 / 2) + gI * 8;
-          uint32_t hi[8], lo[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int c = c0 + j;
-            const float x = (r < nrows && c < O) ? xr[c] : 0.0f;
-            tc::split_tf32(x, hi[j], lo[j]);
-          }
-          tc::tmem_st8(tc::tmem_addr(tb, lane_base, C_A1H + c0), hi);
-          tc::tmem_st8(tc::tmem_addr(tb, lane_base, C_A1L + c0), lo);
+        for (int j = 0; j < K0 / 2; ++j) {
+          const int c = h * (K0 / 2) + j;
+          x[j] = (live && c < O) ? xr[c] : 0.0f;
         }
+#pragma unroll
+        for (int g = 0; g < K0 / 8; ++g) {
+          const int kc = h * (K0 / 8) + g;   // 16-byte K chunk
+          uint32_t hi[4], lo[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) split_fast(x[g * 4 + j], hi[j], lo[j]);
+          reinterpret_cast<uint4*>(s.xhi)[kc * TM + r] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          reinterpret_cast<uint4*>(s.xlo)[kc * TM + r] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+        tc::fence_proxy_async();   // generic-proxy writes -> visible to the tensor core's shared-memory reads
       }
-      fin.obs_consumed(s, by_tma);   // releases the staging buffer (arrives on obs_empty when the tile came by TMA)
+      trace_mark(etrace, ti, 128);
+      fin.obs_consumed(s);
       arrive_a(0);
 
-      // ---- trunk: 8 chunks of layer 1 -> layer-2 K-chunks
+      // ---- trunk: 4 chunks of layer 1 -> layer-2 K-chunks (32 columns per thread)
+#pragma unroll
       for (int c = 0; c < NCH; ++c) {
         const int b = c & 1;
-        wait_d(b);
-        epi_elu16(tb, lane_base, C_D1 + 32 * b + 16 * h, C_A2 + 64 * b + 16 * h, C_A2 + 64 * b + 32 + 16 * h,
-                  s.bias + B_B1 + c * CH + 16 * h, nullptr);
+        if (b == 0) { tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; }
+        else        { tc::mbar_wait(&s.bar_d[1], pd1); pd1 ^= 1u; }
+        tc::tc_fence_after();
+        trace_mark(etrace, ti, 128);
+        epi_elu32(tb, lane_base, C_D1 + CH * b + 32 * h, C_A2 + 128 * b + 32 * h, C_A2 + 128 * b + CH + 32 * h,
+                  s.bias + B_B1 + c * CH + 32 * h);
         arrive_a(b);
+        trace_mark(etrace, ti, 128);
       }
       // ---- A3 = ELU(D2 + b2): 64 columns per thread
-      wait_d(0);
+      tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; tc::tc_fence_after();
+      trace_mark(etrace, ti, 128);
 #pragma unroll
-      for (int gI = 0; gI < 4; ++gI) {
-        const int c0 = h * 64 + gI * 16;
-        epi_elu16(tb, lane_base, C_D2 + c0, C_A3H + c0, C_A3L + c0, s.bias + B_B2 + c0, nullptr);
+      for (int g = 0; g < 2; ++g) {
+        const int c0 = h * 64 + g * 32;
+        epi_elu32(tb, lane_base, C_D2 + c0, C_A3H + c0, C_A3L + c0, s.bias + B_B2 + c0);
       }
       arrive_a(0);
+      trace_mark(etrace, ti, 128);
       // ---- heads, first layer
-      wait_d(0);
+      tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; tc::tc_fence_after();
+      trace_mark(etrace, ti, 128);
       if (WANT_PI) {   // A4 = ELU(D3pi + b3pi): 32 columns per thread
-#pragma unroll
-        for (int gI = 0; gI < 2; ++gI) {
-          const int c0 = h * 32 + gI * 16;
-          epi_elu16(tb, lane_base, C_D3 + c0, C_A4H + c0, C_A4L + c0, s.bias + B_B3PI + c0, nullptr);
-        }
+        epi_elu32(tb, lane_base, C_D3 + 32 * h, C_A4H + 32 * h, C_A4L + 32 * h, s.bias + B_B3PI + 32 * h);
         arrive_a(0);
       }
       if (WANT_V) {    // value = ELU(D3v + b3v) . w + b : each half sums 32 columns, half 0 finishes
         float part = 0.0f;
 #pragma unroll
-        for (int gI = 0; gI < 2; ++gI) {
-          const int c0 = h * 32 + gI * 16;
+        for (int g = 0; g < 2; ++g) {
+          const int c0 = h * 32 + g * 16;
           uint32_t v[16];
-          tc::tmem_ld16(tc::tmem_addr(tb, lane_base, C_D3 + 64 + c0), v);
+          tc::tmem_ld16(tc::tmem_addr(tb, lane_base, C_D3 + H3 + c0), v);
           tc::tmem_wait_ld();
 #pragma unroll
           for (int j = 0; j < 16; ++j)
-            part = fmaf(elu(__uint_as_float(v[j]) + s.bias[B_B3V + c0 + j]), s.bias[B_W4V + c0 + j], part);
+            part = fmaf(elu_fast(__uint_as_float(v[j]) + s.bias[B_B3V + c0 + j]), s.bias[B_W4V + c0 + j], part);
         }
         if (h == 1) s.vpart[r] = part;
+        tc::tc_fence_before();
         epi_bar_sync();
         if (h == 0) fin.value(row0, r, nrows, part + s.vpart[r] + s.bias[B_B4V]);
-        if (!WANT_PI) tc::tc_fence_before();   // D3 reads done before the next tile's MMAs overwrite the region
       }
       if (WANT_PI) {
-        wait_d(0);
+        trace_mark(etrace, ti, 128);
+        fin.pre_pi(s, row0, r, h, nrows);   // work that does not depend on mu, done while the last MMAs run
+        tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; tc::tc_fence_after();
+        trace_mark(etrace, ti, 128);
         float mu[APAD];
 #pragma unroll
-        for (int gI = 0; gI < 2; ++gI) {
+        for (int g = 0; g < 2; ++g) {
           uint32_t v[16];
-          tc::tmem_ld16(tc::tmem_addr(tb, lane_base, C_D4 + gI * 16), v);
+          tc::tmem_ld16(tc::tmem_addr(tb, lane_base, C_D4 + g * 16), v);
           tc::tmem_wait_ld();
 #pragma unroll
-          for (int j = 0; j < 16; ++j) mu[gI * 16 + j] = elu(__uint_as_float(v[j]) + s.bias[B_B4 + gI * 16 + j]);
+          for (int j = 0; j < 16; ++j) mu[g * 16 + j] = elu_fast(__uint_as_float(v[j]) + s.bias[B_B4 + g * 16 + j]);
         }
         tc::tc_fence_before();
         fin.pi(s, row0, r, h, nrows, mu);
+        trace_mark(etrace, ti, 128);
       }
       if (WANT_V && !WANT_PI) epi_bar_sync();   // vpart is rewritten by the next tile
     }

@@ -19,14 +19,28 @@ FLYB_D uint4 philox4x32_10(uint4 ctr, uint2 key) {
   return ctr;
 }
 
-// standard normal for element `idx` of draw number `offset` under `seed` (Box-Muller on two of the four words)
-FLYB_D float philox_normal(unsigned long long seed, unsigned long long offset, unsigned long long idx) {
-  const uint4 r = philox4x32_10(make_uint4((unsigned)idx, (unsigned)(idx >> 32), (unsigned)offset,
+// Two standard normals (Box-Muller, cos and sin branch) from Philox counter `pair` of draw number `offset` under
+// `seed`.  Fast-math log / sin / cos: this is sampling noise, not part of the parity contract (parity tests pass
+// their noise explicitly).
+FLYB_D void philox_normal_pair(unsigned long long seed, unsigned long long offset, unsigned long long pair,
+                               float& n_even, float& n_odd) {
+  const uint4 r = philox4x32_10(make_uint4((unsigned)pair, (unsigned)(pair >> 32), (unsigned)offset,
                                            (unsigned)(offset >> 32)),
                                 make_uint2((unsigned)seed, (unsigned)(seed >> 32)));
   const float u1 = ((float)r.x + 1.0f) * 2.3283064365386963e-10f;  // (0, 1]
   const float u2 = (float)r.y * 2.3283064365386963e-10f;           // [0, 1)
-  return sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2);
+  const float rad = sqrtf(-2.0f * __logf(u1));
+  float sn, cs;
+  __sincosf(6.283185307179586f * u2, &sn, &cs);
+  n_even = rad * cs;
+  n_odd = rad * sn;
+}
+
+// standard normal for element `idx` of the draw: element 2j takes the cos branch of pair j, 2j+1 the sin branch
+FLYB_D float philox_normal(unsigned long long seed, unsigned long long offset, unsigned long long idx) {
+  float a, b;
+  philox_normal_pair(seed, offset, idx >> 1, a, b);
+  return (idx & 1ull) ? b : a;
 }
 
 }  // namespace flyb

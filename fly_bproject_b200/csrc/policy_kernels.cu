@@ -212,6 +212,14 @@ int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpa
 
 using namespace flyb;
 
+// Debug aid (not part of the reference-facing surface): device buffer of >= 160 u64 that CTA 0 of the tensor-core
+// kernels fills with clock64() marks; NULL switches it off.
+namespace flyb { void tc_set_trace(void* p); }
+extern "C" int flyb_debug_set_trace(void* dev_buffer) {
+  flyb::tc_set_trace(dev_buffer);
+  return FLYB_OK;
+}
+
 extern "C" size_t flyb_wpack_bytes(const FlybNetLayout* net) { return net ? tc_wpack_bytes(net) : 0; }
 
 extern "C" int flyb_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, void* stream) {

@@ -101,17 +101,19 @@ struct FwdFinal {
   float* mu_out;
   float* value_out;
   int A;
-  FLYB_D void begin_tile(const tcm::Smem&, long long, int, bool) {}
-  FLYB_D void obs_consumed(const tcm::Smem& s, bool) {
+  FLYB_D void begin_tile(const tcm::Smem&, long long, int, int) {}
+  FLYB_D void obs_consumed(const tcm::Smem& s) {
     __syncwarp();
     if ((threadIdx.x & 31) == 0) tc::mbar_arrive(s.obs_empty);
   }
   FLYB_D void value(long long row0, int r, int nrows, float v) {
     if (r < nrows) value_out[row0 + r] = v;
   }
-  FLYB_D void pi(const tcm::Smem& s, long long row0, int r, int h, int nrows, const float (&mu)[tcm::APAD]) {
-    if (threadIdx.x == 0) tc::tma_store_wait_read<0>();
+  FLYB_D void pre_pi(const tcm::Smem&, long long, int, int, int) {
+    if (threadIdx.x == 0) tc::tma_store_wait_read<0>();   // previous tile's bulk store has drained the staging
     tcm::epi_bar_sync();
+  }
+  FLYB_D void pi(const tcm::Smem& s, long long row0, int r, int h, int nrows, const float (&mu)[tcm::APAD]) {
     if (h == 0) {
 #pragma unroll
       for (int k = 0; k < tcm::APAD; ++k)
@@ -127,18 +129,27 @@ struct FwdFinal {
   }
 };
 
+// per-kernel tables the act finaliser reads from shared memory
+struct ActTables {
+  float std[FLYB_MAX_DOF];      // sqrt(action_var[k])
+  float lo[FLYB_MAX_DOF];       // lower limit of the DOF action k drives
+  float hi[FLYB_MAX_DOF];
+  float init_pos[FLYB_MAX_DOF]; // per DOF
+  float init_vel[FLYB_MAX_DOF];
+  int slot[FLYB_MAX_DOF];       // dof -> action slot or -1
+  float half_log_det;
+};
+
 struct ActFinal {
-  // act
-  const float* action_var;
   const float* noise;
   unsigned long long seed, draw;
   float* action;
   float* logp;
   float* mu_out;
   float* obs_store;
-  int A, O;
+  int A, O, D;
   // fused pre-physics
-  const FlybEnvCfg* cfg;   // points at the kernel's __grid_constant__ copy
+  const FlybEnvCfg* cfg;   // the kernel's __grid_constant__ copy
   int has_env;
   float* actions_scaled;
   float* dof_targets;
@@ -148,76 +159,97 @@ struct ActFinal {
   float* prev_potentials;
   float* root;
   float* dof_state;
-  // shared scratch owned by the kernel
-  const float* s_std;      // [A]
-  const int* s_slot;       // [D] dof -> action slot or -1
-  float half_log_det;
+  const ActTables* t;      // shared memory
+  long long rst_raw;       // this row's reset flag, fetched at the start of the tile (consumed at its end)
 
-  FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int nrows, bool) {
+  FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {
+    rst_raw = (has_env && r < nrows) ? reset[row0 + r] : 0;
     if (obs_store) {   // rollout row all_obs[i] = obs (ppo.py:226)
-      tc::fence_proxy_async();
       store_tile(obs_store + (size_t)row0 * O, s.obs, nrows * O);
       if (threadIdx.x == 0) tc::tma_store_commit();
     }
   }
-  FLYB_D void obs_consumed(const tcm::Smem& s, bool) {
+  FLYB_D void obs_consumed(const tcm::Smem& s) {
     if (obs_store && threadIdx.x == 0) tc::tma_store_wait_read<0>();   // the bulk store has read the staging buffer
     __syncwarp();
     if ((threadIdx.x & 31) == 0) tc::mbar_arrive(s.obs_empty);
   }
   FLYB_D void value(long long, int, int, float) {}
 
+  // the two column halves of a row share its A actions: [0, half) and [half, A), half even so that the Philox
+  // pairs (2j, 2j+1) of a row stay inside one thread when A is even
+  FLYB_D void k_range(int h, int& k_lo, int& k_hi) const {
+    const int half = min((((A + 1) >> 1) + 1) & ~1, A);
+    k_lo = h ? half : 0;
+    k_hi = h ? A : half;
+  }
+  // eps for this thread's share of the row -> staging (scaled_s slots, overwritten by the scaled action later)
+  FLYB_D void pre_pi(const tcm::Smem& s, long long row0, int r, int h, int nrows) {
+    float* scaled_s = s.out + tcm::TM * A;
+    if (threadIdx.x == 0) tc::tma_store_wait_read<0>();   // previous tile's bulk stores have drained the staging
+    tcm::epi_bar_sync();
+    if (r >= nrows) return;
+    const long long row = row0 + r;
+    int k_lo, k_hi;
+    k_range(h, k_lo, k_hi);
+    unsigned long long cached = ~0ull;
+    float n_even = 0.0f, n_odd = 0.0f;
+    for (int k = k_lo; k < k_hi; ++k) {
+      float eps;
+      if (noise) {
+        eps = __ldg(noise + (size_t)row * A + k);
+      } else {
+        const unsigned long long idx = (unsigned long long)row * A + k;
+        if ((idx >> 1) != cached) {
+          cached = idx >> 1;
+          philox_normal_pair(seed, draw, cached, n_even, n_odd);
+        }
+        eps = (idx & 1ull) ? n_odd : n_even;
+      }
+      scaled_s[r * A + k] = eps;
+    }
+  }
   FLYB_D void pi(const tcm::Smem& s, long long row0, int r, int h, int nrows, const float (&mu)[tcm::APAD]) {
-    const int D = has_env ? cfg->num_dof : 0;
-    float* act_s = s.out;                 // [TM][A]  mu, then the clipped action
+    float* act_s = s.out;                   // [TM][A]  mu, then the clipped action
     float* scaled_s = act_s + tcm::TM * A;  // [TM][A]
     float* tgt_s = scaled_s + tcm::TM * A;  // [TM][D]
     const long long row = row0 + r;
     const bool valid = r < nrows;
-    if (threadIdx.x == 0) tc::tma_store_wait_read<0>();   // previous tile's bulk stores have drained the staging
-    tcm::epi_bar_sync();
-    if (h == 0) {
+    const bool rst = rst_raw != 0;
+    int k_lo, k_hi;
+    k_range(h, k_lo, k_hi);
 #pragma unroll
-      for (int k = 0; k < tcm::APAD; ++k)
-        if (k < A) act_s[r * A + k] = mu[k];
-    }
-    tcm::epi_bar_sync();
-    // both column halves sample their share of the A actions of the row
-    const int half = (A + 1) >> 1;
-    const int k_lo = h ? half : 0, k_hi = h ? A : half;
+    for (int k = 0; k < tcm::APAD; ++k)
+      if (k >= k_lo && k < k_hi) act_s[r * A + k] = mu[k];   // own range only: read back below by the same thread
     float m = 0.0f;
     if (valid) {
       for (int k = k_lo; k < k_hi; ++k) {
         const float mu_k = act_s[r * A + k];
-        const float eps = noise ? __ldg(noise + (size_t)row * A + k)
-                                : philox_normal(seed, draw, (unsigned long long)row * A + k);
-        const float sample = mu_k + s_std[k] * eps;                 // MultivariateNormal.sample (ppo.py:218)
-        const float diff = (sample - mu_k) / s_std[k];
+        const float eps = scaled_s[r * A + k];   // staged by pre_pi
+        const float sd = t->std[k];
+        const float sample = mu_k + sd * eps;                       // MultivariateNormal.sample (ppo.py:218)
+        const float diff = (sample - mu_k) / sd;
         m += diff * diff;
         const float clipped = fminf(fmaxf(sample, -1.0f), 1.0f);    // ppo.py:220 (after log_prob)
         act_s[r * A + k] = clipped;
         if (mu_out) mu_out[(size_t)row * A + k] = mu_k;
-        if (has_env) {
-          const int d = cfg->action_idx[k];
-          scaled_s[r * A + k] = scale_action(clipped, cfg->lower[d], cfg->upper[d]);   // fly.py:629-630
-        }
+        if (has_env) scaled_s[r * A + k] = scale_action(clipped, t->lo[k], t->hi[k]);   // fly.py:629-630
       }
     }
     if (h == 1) s.vpart[r] = m;
     tcm::epi_bar_sync();
     if (h == 0 && valid) {
       const float a_log_2pi = (float)((double)A * 1.8378770664093453);
-      logp[row] = -0.5f * (a_log_2pi + (m + s.vpart[r])) - half_log_det;               // ppo.py:219
+      logp[row] = -0.5f * (a_log_2pi + (m + s.vpart[r])) - t->half_log_det;             // ppo.py:219
     }
     if (has_env && valid) {
-      const bool rst = reset[row] != 0;
       const int dh = (D + 1) >> 1;
       const int d_lo = h ? dh : 0, d_hi = h ? D : dh;
       for (int d = d_lo; d < d_hi; ++d) {
-        const int k = s_slot[d];
-        tgt_s[r * D + d] = (k >= 0) ? scaled_s[r * A + k] : cfg->initial_pos[d];       // fly.py:626, 648-651
+        const int k = t->slot[d];
+        tgt_s[r * D + d] = (k >= 0) ? scaled_s[r * A + k] : t->init_pos[d];             // fly.py:626, 648-651
         if (rst)                                                                        // fly.py:454-455
-          reinterpret_cast<float2*>(dof_state)[(size_t)row * D + d] = make_float2(cfg->initial_pos[d], cfg->initial_vel[d]);
+          reinterpret_cast<float2*>(dof_state)[(size_t)row * D + d] = make_float2(t->init_pos[d], t->init_vel[d]);
       }
       if (rst) {                                                                        // fly.py:459-477
         if (h == 1) {
@@ -230,16 +262,15 @@ struct ActFinal {
           prev_potentials[row] = p;
           potentials[row] = p;
           progress[row] = 0;
+          reset[row] = 0;
         }
       }
     }
     tc::fence_proxy_async();
     tcm::epi_bar_sync();
-    // the reset mask is cleared only after both halves of the row have read it
-    if (has_env && valid && h == 0 && reset[row] != 0) reset[row] = 0;
     store_tile(action + (size_t)row0 * A, act_s, nrows * A);
     if (has_env) {
-      store_tile(actions_scaled + (size_t)row0 * A, scaled_s, nrows * A);              // fly.py:633-636
+      store_tile(actions_scaled + (size_t)row0 * A, scaled_s, nrows * A);               // fly.py:633-636
       store_tile(dof_targets + (size_t)row0 * D, tgt_s, nrows * D);
     }
     if (threadIdx.x == 0) tc::tma_store_commit();
@@ -283,38 +314,47 @@ __global__ void __launch_bounds__(tcm::THREADS, 1)
 policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_constant__ tcm::FwdArgs a,
                      const __grid_constant__ ActTcArgs x, const __grid_constant__ FlybEnvCfg cfg) {
   extern __shared__ unsigned char smem_raw[];
-  __shared__ float s_std[FLYB_MAX_DOF];
-  __shared__ int s_slot[FLYB_MAX_DOF];
-  __shared__ float s_half_log_det;
+  __shared__ ActTables tab;
   const int A = net.num_act;
-  if (threadIdx.x < A) s_std[threadIdx.x] = sqrtf(__ldg(x.action_var + threadIdx.x));
+  for (int k = threadIdx.x; k < A; k += tcm::THREADS) {
+    tab.std[k] = sqrtf(__ldg(x.action_var + k));
+    if (x.has_env) {
+      const int d = cfg.action_idx[k];
+      tab.lo[k] = cfg.lower[d];
+      tab.hi[k] = cfg.upper[d];
+    }
+  }
   if (x.has_env)
     for (int d = threadIdx.x; d < cfg.num_dof; d += tcm::THREADS) {
       int slot = -1;
       for (int k = 0; k < A; ++k)
         if (cfg.action_idx[k] == d) slot = k;
-      s_slot[d] = slot;
+      tab.slot[d] = slot;
+      tab.init_pos[d] = cfg.initial_pos[d];
+      tab.init_vel[d] = cfg.initial_vel[d];
     }
   __syncthreads();
   if (threadIdx.x == 0) {
     float hl = 0.0f;
-    for (int k = 0; k < A; ++k) hl += logf(s_std[k]);
-    s_half_log_det = hl;
+    for (int k = 0; k < A; ++k) hl += logf(tab.std[k]);
+    tab.half_log_det = hl;
   }
   __syncthreads();
   ActFinal fin;
-  fin.action_var = x.action_var; fin.noise = x.noise; fin.seed = x.seed;
+  fin.noise = x.noise; fin.seed = x.seed;
   fin.draw = x.offset + (x.offset_dev ? __ldg(x.offset_dev) : 0ull);
   fin.action = x.action; fin.logp = x.logp; fin.mu_out = x.mu_out; fin.obs_store = x.obs_store;
-  fin.A = A; fin.O = net.num_obs;
+  fin.A = A; fin.O = net.num_obs; fin.D = x.has_env ? cfg.num_dof : 0;
   fin.cfg = &cfg; fin.has_env = x.has_env;
   fin.actions_scaled = x.actions_scaled; fin.dof_targets = x.dof_targets; fin.reset = x.reset; fin.progress = x.progress;
   fin.potentials = x.potentials; fin.prev_potentials = x.prev_potentials; fin.root = x.root; fin.dof_state = x.dof_state;
-  fin.s_std = s_std; fin.s_slot = s_slot; fin.half_log_det = s_half_log_det;
+  fin.t = &tab; fin.rst_raw = 0;
   tcm::forward_persistent<true, false>(net, a, fin, smem_raw);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
+static unsigned long long* g_trace = nullptr;   // debug timeline buffer (flyb_debug_set_trace), normally NULL
+void tc_set_trace(void* p) { g_trace = (unsigned long long*)p; }
 bool tc_supported(const FlybNetLayout* net) { return net->k0_pad == tcm::K0 && net->num_act <= tcm::APAD; }
 
 size_t tc_wpack_bytes(const FlybNetLayout* net) {
@@ -338,8 +378,8 @@ static int prepare(K kernel, size_t smem) {
 int tc_launch_forward(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs,
                       long long rows, float* mu_out, float* value_out, cudaStream_t st) {
   tcm::FwdArgs a{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act,
-                 mu_out ? (size_t)tcm::TM * net->num_act * 4 : 0};
-  const size_t smem = tcm::smem_bytes(a.out_bytes);
+                 mu_out ? (size_t)tcm::TM * net->num_act * 4 : 0, g_trace};
+  const size_t smem = tcm::smem_bytes(net->num_obs, a.out_bytes);
   const long long ntiles = (rows + tcm::TM - 1) / tcm::TM;
   const int grid = (int)std::min<long long>(ntiles, (long long)num_sms());
   int rc;
@@ -361,7 +401,7 @@ int tc_launch_forward(const FlybNetLayout* net, const float* params, const void*
 bool tc_act_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg) {
   if (!tc_supported(net)) return false;
   const size_t out = (size_t)tcm::TM * (2 * net->num_act + (cfg ? cfg->num_dof : 0)) * 4;
-  return tcm::smem_bytes(out) <= 227u * 1024u;
+  return tcm::smem_bytes(net->num_obs, out) <= 227u * 1024u;
 }
 
 int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs, long long rows,
@@ -370,7 +410,7 @@ int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpa
                   const FlybEnvCfg* cfg, float* actions_scaled, float* dof_targets, int64_t* reset, int64_t* progress,
                   float* potentials, float* prev_potentials, float* root, float* dof_state, cudaStream_t st) {
   const size_t out = (size_t)tcm::TM * (2 * net->num_act + (cfg ? cfg->num_dof : 0)) * 4;
-  tcm::FwdArgs a{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, out};
+  tcm::FwdArgs a{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, out, g_trace};
   ActTcArgs x{};
   x.action_var = action_var; x.noise = noise; x.seed = seed; x.offset = offset;
   x.offset_dev = (const unsigned long long*)offset_dev;
@@ -383,7 +423,7 @@ int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpa
     x.progress = (long long*)progress; x.potentials = potentials; x.prev_potentials = prev_potentials;
     x.root = root; x.dof_state = dof_state;
   }
-  const size_t smem = tcm::smem_bytes(out);
+  const size_t smem = tcm::smem_bytes(net->num_obs, out);
   const long long ntiles = (rows + tcm::TM - 1) / tcm::TM;
   const int grid = (int)std::min<long long>(ntiles, (long long)num_sms());
   int rc;

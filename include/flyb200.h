@@ -101,6 +101,9 @@ const char* flyb_last_error(void);
 int flyb_device_count(void);
 
 int flyb_net_layout(int32_t num_obs, int32_t num_act, FlybNetLayout* out);
+/* Debug aid: device buffer (>= 160 uint64) that CTA 0 of the tensor-core kernels fills with clock64() marks of its
+ * MMA / epilogue hand-offs; NULL (default) switches tracing off. */
+int flyb_debug_set_trace(void* dev_buffer);
 
 /* ---- tensor-core weight stream.  The GEMMs of Net.pi / Net.v (reference ppo.py:88-102) run on tcgen05 tensor
  *      cores as 3xTF32 products (fp32 accumulate; within ~1e-6 of an fp32 evaluation) when the caller passes
