@@ -77,10 +77,13 @@ __host__ __device__ inline size_t smem_bytes(int O, size_t out_bytes) {
          B_TOTAL * 4 + TM * 4 + (2 * NST + 6) * 8 + 16;
 }
 
+// `raw` must be the kernel's `extern __shared__` array itself: every pointer below is derived from it by plain
+// pointer arithmetic, so that the compiler keeps the shared state space (LDS / STS instead of generic LD / ST).
 FLYB_D Smem carve(unsigned char* raw, int O, size_t out_bytes) {
   Smem s;
-  uintptr_t p = (reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023;
-  s.ring = reinterpret_cast<unsigned char*>(p);
+  const uint32_t pad = (1024u - (tc::smem_u32(raw) & 1023u)) & 1023u;
+  unsigned char* p = raw + pad;
+  s.ring = p;
   p += (size_t)NST * STAGE;
   s.xhi = reinterpret_cast<float*>(p);
   p += X_PLANE_BYTES;
@@ -164,21 +167,21 @@ FLYB_D void mma_segment(MmaState& m, uint32_t a_hi, uint32_t a_lo, uint32_t d, b
   static_assert(2 * SLAB <= STAGE, "a k-step (hi + lo slab) must fit one stage");
   constexpr int KPS = STAGE / (2 * SLAB);   // k-steps per stage
   static_assert(KSTEPS % KPS == 0, "segment must end on a stage boundary");
-  uint32_t base = 0, slot = 0;
+  // rolled over stages (the whole kernel runs once per tile: straight-line code would only miss in the
+  // instruction cache), unrolled over the KPS k-steps of a stage
+#pragma unroll 1
+  for (int ks0 = 0; ks0 < KSTEPS; ks0 += KPS) {
+    const uint32_t slot = m.stage & (NST - 1);
+    tc::mbar_wait(&m.full[slot], (m.stage >> LOG_NST) & 1u);
+    tc::tc_fence_after();
+    const uint32_t base = m.ring + slot * STAGE;
 #pragma unroll
-  for (int ks = 0; ks < KSTEPS; ++ks) {
-    if (ks % KPS == 0) {
-      slot = m.stage & (NST - 1);
-      tc::mbar_wait(&m.full[slot], (m.stage >> LOG_NST) & 1u);
-      tc::tc_fence_after();
-      base = m.ring + slot * STAGE;
+    for (int j = 0; j < KPS; ++j) {
+      const uint32_t hi_addr = base + (uint32_t)j * 2u * SLAB;
+      issue3(ks0 + j, hi_addr, hi_addr + SLAB);
     }
-    const uint32_t hi_addr = base + (uint32_t)(ks % KPS) * 2u * SLAB;
-    issue3(ks, hi_addr, hi_addr + SLAB);
-    if (ks % KPS == KPS - 1) {
-      umma_commit_if(m.leader, &m.empty[slot]);
-      ++m.stage;
-    }
+    umma_commit_if(m.leader, &m.empty[slot]);
+    ++m.stage;
   }
 }
 
@@ -195,40 +198,36 @@ FLYB_D void split_fast(float y, uint32_t& hi, uint32_t& lo) {
   lo = __float_as_uint(y - __uint_as_float(hi));
 }
 
-// y = ELU(acc + bias) for 32 consecutive accumulator columns, split to hi/lo and stored as the next A operand
-FLYB_D void epi_elu32(uint32_t tb, uint32_t lane_base, uint32_t d_col, uint32_t ah_col, uint32_t al_col,
-                      const float* bias) {
+// y = ELU(acc + bias) for 32 consecutive accumulator columns (two independent 16-column groups in flight),
+// split to hi/lo and stored as the next A operand
+FLYB_D void epi_elu32(uint32_t d_addr, uint32_t ah_addr, uint32_t al_addr, const float* bias) {
   uint32_t v0[16], v1[16];
-  tc::tmem_ld16(tc::tmem_addr(tb, lane_base, d_col), v0);
-  tc::tmem_ld16(tc::tmem_addr(tb, lane_base, d_col + 16), v1);
+  tc::tmem_ld16(d_addr, v0);
+  tc::tmem_ld16(d_addr + 16, v1);
   tc::tmem_wait_ld();
   const float4* b4 = reinterpret_cast<const float4*>(bias);
-  {
+#pragma unroll
+  for (int g = 0; g < 2; ++g) {
     uint32_t hi[16], lo[16];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const float4 b = b4[q];
-      split_fast(elu_fast(__uint_as_float(v0[4 * q + 0]) + b.x), hi[4 * q + 0], lo[4 * q + 0]);
-      split_fast(elu_fast(__uint_as_float(v0[4 * q + 1]) + b.y), hi[4 * q + 1], lo[4 * q + 1]);
-      split_fast(elu_fast(__uint_as_float(v0[4 * q + 2]) + b.z), hi[4 * q + 2], lo[4 * q + 2]);
-      split_fast(elu_fast(__uint_as_float(v0[4 * q + 3]) + b.w), hi[4 * q + 3], lo[4 * q + 3]);
+      const float4 b = b4[4 * g + q];
+      const uint32_t* v = g ? v1 : v0;
+      split_fast(elu_fast(__uint_as_float(v[4 * q + 0]) + b.x), hi[4 * q + 0], lo[4 * q + 0]);
+      split_fast(elu_fast(__uint_as_float(v[4 * q + 1]) + b.y), hi[4 * q + 1], lo[4 * q + 1]);
+      split_fast(elu_fast(__uint_as_float(v[4 * q + 2]) + b.z), hi[4 * q + 2], lo[4 * q + 2]);
+      split_fast(elu_fast(__uint_as_float(v[4 * q + 3]) + b.w), hi[4 * q + 3], lo[4 * q + 3]);
     }
-    tc::tmem_st16(tc::tmem_addr(tb, lane_base, ah_col), hi);
-    tc::tmem_st16(tc::tmem_addr(tb, lane_base, al_col), lo);
+    tc::tmem_st16(ah_addr + 16 * g, hi);
+    tc::tmem_st16(al_addr + 16 * g, lo);
   }
-  {
-    uint32_t hi[16], lo[16];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float4 b = b4[4 + q];
-      split_fast(elu_fast(__uint_as_float(v1[4 * q + 0]) + b.x), hi[4 * q + 0], lo[4 * q + 0]);
-      split_fast(elu_fast(__uint_as_float(v1[4 * q + 1]) + b.y), hi[4 * q + 1], lo[4 * q + 1]);
-      split_fast(elu_fast(__uint_as_float(v1[4 * q + 2]) + b.z), hi[4 * q + 2], lo[4 * q + 2]);
-      split_fast(elu_fast(__uint_as_float(v1[4 * q + 3]) + b.w), hi[4 * q + 3], lo[4 * q + 3]);
-    }
-    tc::tmem_st16(tc::tmem_addr(tb, lane_base, ah_col + 16), hi);
-    tc::tmem_st16(tc::tmem_addr(tb, lane_base, al_col + 16), lo);
-  }
+}
+// `ncols` (multiple of 32) columns starting at d_col -> hi at ah_col, lo at al_col
+FLYB_D void epi_elu(uint32_t tb, uint32_t lane_base, uint32_t d_col, uint32_t ah_col, uint32_t al_col,
+                    const float* bias, int ncols) {
+  const uint32_t t0 = tc::tmem_addr(tb, lane_base, 0);
+#pragma unroll 1
+  for (int c = 0; c < ncols; c += 32) epi_elu32(t0 + d_col + c, t0 + ah_col + c, t0 + al_col + c, bias + c);
 }
 
 struct FwdArgs {
@@ -249,13 +248,15 @@ FLYB_D void trace_mark(unsigned long long* trace, int& idx, int limit) {
 // Per-tile consumer of the results (`Final`), called by the 256 epilogue threads:
 //   begin_tile(s, row0, r, nrows)          after the raw observation tile is in shared memory (s.obs, row-major)
 //   obs_consumed(s)                        after the A operand of layer 1 was built; must arrive on s.obs_empty
+//   early(s, row0, nrows)                  right after the layer-1 operand was handed to the MMA warp
 //   pre_pi(s, row0, r, h, nrows)           before the last accumulator is waited for (mu-independent work)
 //   pi(s, row0, r, h, nrows, mu[32])       both column halves call it with the full mu row (ELU applied)
 //   value(row0, r, nrows, v)               half 0 only
 //   finish(s)                              once, after the last tile
 // Implementations: policy_kernels_tc.cu.
 template <bool WANT_PI, bool WANT_V, class Final>
-FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final& fin, unsigned char* smem_raw) {
+FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final& fin) {
+  extern __shared__ unsigned char smem_raw[];
   const Smem s = carve(smem_raw, a.O, a.out_bytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int O = a.O;
@@ -305,7 +306,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       const int nrows = (int)min((long long)TM, a.rows - row0);
       const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
       const float* src = a.obs + (size_t)row0 * O;
-      tc::mbar_wait(s.obs_empty, obs_phase ^ 1u);   // the epilogue warps are done with the previous tile's rows
+      tc::mbar_wait_relaxed(s.obs_empty, obs_phase ^ 1u);   // the epilogue warps are done with the previous tile's rows
       obs_phase ^= 1u;
       if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
         tc::mbar_arrive_expect_tx(s.obs_full, bytes);
@@ -315,7 +316,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
         const unsigned char* g = a.wpack + (size_t)first * STAGE;
         for (int i = 0; i < count; ++i, ++gs, g += STAGE) {
           const uint32_t slot = gs & (NST - 1);
-          tc::mbar_wait(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
+          tc::mbar_wait_relaxed(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
           const uint32_t bar = tc::smem_u32(&s.full[slot]);
           asm volatile(
               "{\n\t.reg .pred q;\n\t.reg .b64 st;\n\tsetp.ne.b32 q, %4, 0;\n\t"
@@ -334,40 +335,43 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
     // =========================================================================== MMA issuer (warp-uniform)
     MmaState m{tc::elect_one() ? 1u : 0u, tc::smem_u32(s.ring), s.full, s.empty, 0u};
     const uint32_t xh = tc::smem_u32(s.xhi), xl = tc::smem_u32(s.xlo);
-    uint32_t pa0 = 0u, pa1 = 0u;
+    uint32_t pa = 0u;   // bit b = phase of bar_a[b]
     int ti = 0;
     unsigned long long* mtrace = (lane == 0) ? a.trace : nullptr;
+    auto wait_a = [&](int b) {
+      tc::mbar_wait_relaxed(&s.bar_a[b], (pa >> b) & 1u);
+      pa ^= 1u << b;
+      tc::tc_fence_after();
+    };
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       trace_mark(mtrace, ti, 64);
-      tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; tc::tc_fence_after();   // X staged
+      wait_a(0);   // X staged
       trace_mark(mtrace, ti, 64);
-      mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1, false);
-      umma_commit_if(m.leader, &s.bar_d[0]);
-      mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1 + CH, false);
-      umma_commit_if(m.leader, &s.bar_d[1]);
-#pragma unroll
-      for (int c = 0; c < NCH; ++c) {
-        const int b = c & 1;
-        if (b == 0) { tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; }
-        else        { tc::mbar_wait(&s.bar_a[1], pa1); pa1 ^= 1u; }
-        tc::tc_fence_after();           // A2[b] = ELU(D1[b] + b1) written, D1[b] drained
-        trace_mark(mtrace, ti, 64);
-        mma_segment<H2, CH / 8, false>(m, tb + C_A2 + 128 * b, tb + C_A2 + 128 * b + CH, tb + C_D2, c > 0);
+      // issue order (== packed stream order): W1[0], W1[1], then (W2[c], W1[c+2]) for c = 0..3
+#pragma unroll 1
+      for (int c = -2; c < NCH; ++c) {
+        if (c >= 0) {
+          const int b = c & 1;
+          wait_a(b);                    // A2[b] = ELU(D1[b] + b1) written, D1[b] drained
+          trace_mark(mtrace, ti, 64);
+          mma_segment<H2, CH / 8, false>(m, tb + C_A2 + 128 * b, tb + C_A2 + 128 * b + CH, tb + C_D2, c > 0);
+        }
         if (c + 2 < NCH) {
-          mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1 + CH * b, false);
-          umma_commit_if(m.leader, &s.bar_d[b]);
+          const int b2 = (c + 2) & 1;
+          mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1 + CH * b2, false);
+          umma_commit_if(m.leader, &s.bar_d[b2]);
         }
       }
       umma_commit_if(m.leader, &s.bar_d[0]);   // D2 complete
       trace_mark(mtrace, ti, 64);
-      tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; tc::tc_fence_after();   // A3
+      wait_a(0);                               // A3
       trace_mark(mtrace, ti, 64);
       if (WANT_PI) mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3, false);
       if (WANT_V) mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3 + H3, false);
       umma_commit_if(m.leader, &s.bar_d[0]);   // D3
       if (WANT_PI) {
         trace_mark(mtrace, ti, 64);
-        tc::mbar_wait(&s.bar_a[0], pa0); pa0 ^= 1u; tc::tc_fence_after(); // A4
+        wait_a(0);                             // A4
         trace_mark(mtrace, ti, 64);
         mma_segment<APAD, H3 / 8, false>(m, tb + C_A4H, tb + C_A4L, tb + C_D4, false);
         umma_commit_if(m.leader, &s.bar_d[0]); // D4
@@ -379,9 +383,14 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
     const int q = warp & 3, h = warp >> 2;
     const uint32_t lane_base = (uint32_t)q * 32u;
     const int r = q * 32 + lane;   // row inside the tile
-    uint32_t pd0 = 0u, pd1 = 0u, obs_phase = 0u;
+    uint32_t pd = 0u, obs_phase = 0u;   // bit b of pd = phase of bar_d[b]
     int ti = 64;
     unsigned long long* etrace = (threadIdx.x == 0) ? a.trace : nullptr;
+    auto wait_d = [&](int b) {
+      tc::mbar_wait(&s.bar_d[b], (pd >> b) & 1u);
+      pd ^= 1u << b;
+      tc::tc_fence_after();
+    };
     auto arrive_a = [&](int b) {
       tc::tmem_wait_st();
       tc::tc_fence_before();
@@ -409,18 +418,15 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       {
         const float* xr = s.obs + r * O;
         const bool live = r < nrows;
-        float x[K0 / 2];
-#pragma unroll
-        for (int j = 0; j < K0 / 2; ++j) {
-          const int c = h * (K0 / 2) + j;
-          x[j] = (live && c < O) ? xr[c] : 0.0f;
-        }
-#pragma unroll
+#pragma unroll 2
         for (int g = 0; g < K0 / 8; ++g) {
           const int kc = h * (K0 / 8) + g;   // 16-byte K chunk
           uint32_t hi[4], lo[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) split_fast(x[g * 4 + j], hi[j], lo[j]);
+          for (int j = 0; j < 4; ++j) {
+            const int c = kc * 4 + j;
+            split_fast((live && c < O) ? xr[c] : 0.0f, hi[j], lo[j]);
+          }
           reinterpret_cast<uint4*>(s.xhi)[kc * TM + r] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
           reinterpret_cast<uint4*>(s.xlo)[kc * TM + r] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
@@ -429,35 +435,30 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       trace_mark(etrace, ti, 128);
       fin.obs_consumed(s);
       arrive_a(0);
+      fin.early(s, row0, nrows);   // mu-independent work, overlapped with the first MMAs of the tile
 
       // ---- trunk: 4 chunks of layer 1 -> layer-2 K-chunks (32 columns per thread)
-#pragma unroll
+#pragma unroll 1
       for (int c = 0; c < NCH; ++c) {
         const int b = c & 1;
-        if (b == 0) { tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; }
-        else        { tc::mbar_wait(&s.bar_d[1], pd1); pd1 ^= 1u; }
-        tc::tc_fence_after();
+        wait_d(b);
         trace_mark(etrace, ti, 128);
-        epi_elu32(tb, lane_base, C_D1 + CH * b + 32 * h, C_A2 + 128 * b + 32 * h, C_A2 + 128 * b + CH + 32 * h,
-                  s.bias + B_B1 + c * CH + 32 * h);
+        epi_elu(tb, lane_base, C_D1 + CH * b + 32 * h, C_A2 + 128 * b + 32 * h, C_A2 + 128 * b + CH + 32 * h,
+                s.bias + B_B1 + c * CH + 32 * h, 32);
         arrive_a(b);
         trace_mark(etrace, ti, 128);
       }
       // ---- A3 = ELU(D2 + b2): 64 columns per thread
-      tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; tc::tc_fence_after();
+      wait_d(0);
       trace_mark(etrace, ti, 128);
-#pragma unroll
-      for (int g = 0; g < 2; ++g) {
-        const int c0 = h * 64 + g * 32;
-        epi_elu32(tb, lane_base, C_D2 + c0, C_A3H + c0, C_A3L + c0, s.bias + B_B2 + c0);
-      }
+      epi_elu(tb, lane_base, C_D2 + 64 * h, C_A3H + 64 * h, C_A3L + 64 * h, s.bias + B_B2 + 64 * h, 64);
       arrive_a(0);
       trace_mark(etrace, ti, 128);
       // ---- heads, first layer
-      tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; tc::tc_fence_after();
+      wait_d(0);
       trace_mark(etrace, ti, 128);
       if (WANT_PI) {   // A4 = ELU(D3pi + b3pi): 32 columns per thread
-        epi_elu32(tb, lane_base, C_D3 + 32 * h, C_A4H + 32 * h, C_A4L + 32 * h, s.bias + B_B3PI + 32 * h);
+        epi_elu(tb, lane_base, C_D3 + 32 * h, C_A4H + 32 * h, C_A4L + 32 * h, s.bias + B_B3PI + 32 * h, 32);
         arrive_a(0);
       }
       if (WANT_V) {    // value = ELU(D3v + b3v) . w + b : each half sums 32 columns, half 0 finishes
@@ -480,7 +481,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       if (WANT_PI) {
         trace_mark(etrace, ti, 128);
         fin.pre_pi(s, row0, r, h, nrows);   // work that does not depend on mu, done while the last MMAs run
-        tc::mbar_wait(&s.bar_d[0], pd0); pd0 ^= 1u; tc::tc_fence_after();
+        wait_d(0);
         trace_mark(etrace, ti, 128);
         float mu[APAD];
 #pragma unroll

@@ -109,6 +109,7 @@ struct FwdFinal {
   FLYB_D void value(long long row0, int r, int nrows, float v) {
     if (r < nrows) value_out[row0 + r] = v;
   }
+  FLYB_D void early(const tcm::Smem&, long long, int) {}
   FLYB_D void pre_pi(const tcm::Smem&, long long, int, int, int) {
     if (threadIdx.x == 0) tc::tma_store_wait_read<0>();   // previous tile's bulk store has drained the staging
     tcm::epi_bar_sync();
@@ -132,6 +133,10 @@ struct FwdFinal {
 // per-kernel tables the act finaliser reads from shared memory
 struct ActTables {
   float std[FLYB_MAX_DOF];      // sqrt(action_var[k])
+  float inv_std[FLYB_MAX_DOF];
+  int dof[FLYB_MAX_DOF];        // action k -> DOF it drives (cfg.action_idx)
+  int free_dof[FLYB_MAX_DOF];   // DOFs no action drives (they keep initial_pos as target, fly.py:626)
+  int n_free;
   float lo[FLYB_MAX_DOF];       // lower limit of the DOF action k drives
   float hi[FLYB_MAX_DOF];
   float init_pos[FLYB_MAX_DOF]; // per DOF
@@ -140,6 +145,10 @@ struct ActTables {
   float half_log_det;
 };
 
+// Act finaliser.  The 256 epilogue threads work on the tile's (rows x A) actions as ONE flat array, a pair of
+// consecutive elements per thread and trip (balanced, conflict-free shared memory, coalesced float2 global stores);
+// per-row quantities (log-prob, reset bookkeeping) are finished by the thread that owns the row.
+// Staging in s.out (floats): mu_s [TM*A] | eps_s, later scaled_s [TM*A] | dsq_s [TM*A].
 struct ActFinal {
   const float* noise;
   unsigned long long seed, draw;
@@ -161,6 +170,11 @@ struct ActFinal {
   float* dof_state;
   const ActTables* t;      // shared memory
   long long rst_raw;       // this row's reset flag, fetched at the start of the tile (consumed at its end)
+  unsigned long long* trace;   // debug timeline (slots 128..159), thread 0 of CTA 0
+  int ti;
+  FLYB_D void mark() {
+    if (trace != nullptr && threadIdx.x == 0 && blockIdx.x == 0 && ti < 160) trace[ti++] = clock64();
+  }
 
   FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {
     rst_raw = (has_env && r < nrows) ? reset[row0 + r] : 0;
@@ -176,104 +190,108 @@ struct ActFinal {
   }
   FLYB_D void value(long long, int, int, float) {}
 
-  // the two column halves of a row share its A actions: [0, half) and [half, A), half even so that the Philox
-  // pairs (2j, 2j+1) of a row stay inside one thread when A is even
-  FLYB_D void k_range(int h, int& k_lo, int& k_hi) const {
-    const int half = min((((A + 1) >> 1) + 1) & ~1, A);
-    k_lo = h ? half : 0;
-    k_hi = h ? A : half;
-  }
-  // eps for this thread's share of the row -> staging (scaled_s slots, overwritten by the scaled action later)
-  FLYB_D void pre_pi(const tcm::Smem& s, long long row0, int r, int h, int nrows) {
-    float* scaled_s = s.out + tcm::TM * A;
-    if (threadIdx.x == 0) tc::tma_store_wait_read<0>();   // previous tile's bulk stores have drained the staging
-    tcm::epi_bar_sync();
-    if (r >= nrows) return;
-    const long long row = row0 + r;
-    int k_lo, k_hi;
-    k_range(h, k_lo, k_hi);
-    unsigned long long cached = ~0ull;
-    float n_even = 0.0f, n_odd = 0.0f;
-    for (int k = k_lo; k < k_hi; ++k) {
-      float eps;
+  // eps for the whole tile -> eps_s; independent of mu, so it runs while the first MMAs of the tile do
+  FLYB_D void early(const tcm::Smem& s, long long row0, int nrows) {
+    float* eps_s = s.out + tcm::TM * A;
+    tcm::epi_bar_sync();   // every thread has left the previous tile's pi(), which reads this staging
+    const int n = nrows * A;
+    const unsigned long long g0 = (unsigned long long)row0 * A;   // even: row0 is a multiple of 128
+    for (int e = 2 * threadIdx.x; e < n; e += 2 * tcm::EPI_THREADS) {
+      float n0, n1;
       if (noise) {
-        eps = __ldg(noise + (size_t)row * A + k);
+        n0 = __ldg(noise + g0 + e);
+        n1 = (e + 1 < n) ? __ldg(noise + g0 + e + 1) : 0.0f;
       } else {
-        const unsigned long long idx = (unsigned long long)row * A + k;
-        if ((idx >> 1) != cached) {
-          cached = idx >> 1;
-          philox_normal_pair(seed, draw, cached, n_even, n_odd);
-        }
-        eps = (idx & 1ull) ? n_odd : n_even;
+        philox_normal_pair(seed, draw, (g0 + e) >> 1, n0, n1);
       }
-      scaled_s[r * A + k] = eps;
+      eps_s[e] = n0;
+      if (e + 1 < n) eps_s[e + 1] = n1;
     }
   }
+  FLYB_D void pre_pi(const tcm::Smem&, long long, int, int, int) {}
   FLYB_D void pi(const tcm::Smem& s, long long row0, int r, int h, int nrows, const float (&mu)[tcm::APAD]) {
-    float* act_s = s.out;                   // [TM][A]  mu, then the clipped action
-    float* scaled_s = act_s + tcm::TM * A;  // [TM][A]
-    float* tgt_s = scaled_s + tcm::TM * A;  // [TM][D]
-    const long long row = row0 + r;
-    const bool valid = r < nrows;
-    const bool rst = rst_raw != 0;
-    int k_lo, k_hi;
-    k_range(h, k_lo, k_hi);
+    float* mu_s = s.out;
+    float* sc_s = mu_s + tcm::TM * A;    // eps (written by early()), overwritten by the scaled action
+    float* dsq_s = sc_s + tcm::TM * A;   // ((a - mu) / std)^2 per element
+    if (h == 0) {
 #pragma unroll
-    for (int k = 0; k < tcm::APAD; ++k)
-      if (k >= k_lo && k < k_hi) act_s[r * A + k] = mu[k];   // own range only: read back below by the same thread
-    float m = 0.0f;
-    if (valid) {
-      for (int k = k_lo; k < k_hi; ++k) {
-        const float mu_k = act_s[r * A + k];
-        const float eps = scaled_s[r * A + k];   // staged by pre_pi
-        const float sd = t->std[k];
-        const float sample = mu_k + sd * eps;                       // MultivariateNormal.sample (ppo.py:218)
-        const float diff = (sample - mu_k) / sd;
-        m += diff * diff;
-        const float clipped = fminf(fmaxf(sample, -1.0f), 1.0f);    // ppo.py:220 (after log_prob)
-        act_s[r * A + k] = clipped;
-        if (mu_out) mu_out[(size_t)row * A + k] = mu_k;
-        if (has_env) scaled_s[r * A + k] = scale_action(clipped, t->lo[k], t->hi[k]);   // fly.py:629-630
-      }
+      for (int k = 0; k < tcm::APAD; ++k)
+        if (k < A) mu_s[r * A + k] = mu[k];
     }
-    if (h == 1) s.vpart[r] = m;
+    mark();
     tcm::epi_bar_sync();
-    if (h == 0 && valid) {
-      const float a_log_2pi = (float)((double)A * 1.8378770664093453);
-      logp[row] = -0.5f * (a_log_2pi + (m + s.vpart[r])) - t->half_log_det;             // ppo.py:219
-    }
-    if (has_env && valid) {
-      const int dh = (D + 1) >> 1;
-      const int d_lo = h ? dh : 0, d_hi = h ? D : dh;
-      for (int d = d_lo; d < d_hi; ++d) {
-        const int k = t->slot[d];
-        tgt_s[r * D + d] = (k >= 0) ? scaled_s[r * A + k] : t->init_pos[d];             // fly.py:626, 648-651
-        if (rst)                                                                        // fly.py:454-455
-          reinterpret_cast<float2*>(dof_state)[(size_t)row * D + d] = make_float2(t->init_pos[d], t->init_vel[d]);
-      }
-      if (rst) {                                                                        // fly.py:459-477
-        if (h == 1) {
+    mark();
+    const int n = nrows * A;
+    const size_t g0 = (size_t)row0 * A;
+    const int kstep = (2 * tcm::EPI_THREADS) % A;
+    int e = 2 * threadIdx.x;
+    int k = e % A;
+    for (; e < n; e += 2 * tcm::EPI_THREADS) {
+      float cl[2], sc[2] = {0.0f, 0.0f};
 #pragma unroll
-          for (int j = 0; j < 13; ++j) root[(size_t)row * 13 + j] = cfg->origin_root[j];
-        } else {
-          const float tx = cfg->target[0] - cfg->origin_root[0];
-          const float ty = cfg->target[1] - cfg->origin_root[1];
-          const float p = -sqrtf(tx * tx + ty * ty + 0.0f) / cfg->dt;
-          prev_potentials[row] = p;
-          potentials[row] = p;
-          progress[row] = 0;
-          reset[row] = 0;
+      for (int u = 0; u < 2; ++u) {
+        const int ee = (e + u < n) ? e + u : e;
+        int kk = k + u;
+        if (kk >= A) kk -= A;
+        const float mu_k = mu_s[ee];
+        const float sample = mu_k + t->std[kk] * sc_s[ee];            // MultivariateNormal.sample (ppo.py:218)
+        const float diff = (sample - mu_k) * t->inv_std[kk];
+        cl[u] = fminf(fmaxf(sample, -1.0f), 1.0f);                    // ppo.py:220 (after log_prob)
+        if (has_env) sc[u] = scale_action(cl[u], t->lo[kk], t->hi[kk]);   // fly.py:629-630
+        if (e + u < n) {
+          dsq_s[ee] = diff * diff;
+          if (has_env) sc_s[ee] = sc[u];
+          if (mu_out) mu_out[g0 + ee] = mu_k;
         }
       }
+      if (e + 1 < n) {
+        *reinterpret_cast<float2*>(action + g0 + e) = make_float2(cl[0], cl[1]);
+        if (has_env) *reinterpret_cast<float2*>(actions_scaled + g0 + e) = make_float2(sc[0], sc[1]);   // fly.py:633-636
+      } else {
+        action[g0 + e] = cl[0];
+        if (has_env) actions_scaled[g0 + e] = sc[0];
+      }
+      k += kstep;
+      if (k >= A) k -= A;
     }
-    tc::fence_proxy_async();
+    mark();
     tcm::epi_bar_sync();
-    store_tile(action + (size_t)row0 * A, act_s, nrows * A);
-    if (has_env) {
-      store_tile(actions_scaled + (size_t)row0 * A, scaled_s, nrows * A);               // fly.py:633-636
-      store_tile(dof_targets + (size_t)row0 * D, tgt_s, nrows * D);
+    mark();
+    const long long row = row0 + r;
+    if (h == 0 && r < nrows) {
+      float m = 0.0f;
+      for (int kk = 0; kk < A; ++kk) m += dsq_s[r * A + kk];
+      const float a_log_2pi = (float)((double)A * 1.8378770664093453);
+      logp[row] = -0.5f * (a_log_2pi + m) - t->half_log_det;          // ppo.py:219
     }
-    if (threadIdx.x == 0) tc::tma_store_commit();
+    mark();
+    if (has_env) {
+      // DOF position targets, flat over (rows x D): the driven DOFs take the scaled action, the others initial_pos
+      const int nd = nrows * D;
+      const int rstep = tcm::EPI_THREADS / D, dstep = tcm::EPI_THREADS % D;
+      int rr = threadIdx.x / D, d = threadIdx.x - rr * D;
+      float* tg = dof_targets + (size_t)row0 * D;
+      for (int f = threadIdx.x; f < nd; f += tcm::EPI_THREADS) {
+        const int slot = t->slot[d];
+        tg[f] = (slot >= 0) ? sc_s[rr * A + slot] : t->init_pos[d];   // fly.py:626, 648-651
+        rr += rstep;
+        d += dstep;
+        if (d >= D) { d -= D; ++rr; }
+      }
+      if (h == 1 && r < nrows && rst_raw != 0) {                      // Fly.reset (fly.py:446-480), rare
+        for (int dd = 0; dd < D; ++dd)
+          reinterpret_cast<float2*>(dof_state)[(size_t)row * D + dd] = make_float2(t->init_pos[dd], t->init_vel[dd]);
+#pragma unroll
+        for (int j = 0; j < 13; ++j) root[(size_t)row * 13 + j] = cfg->origin_root[j];
+        const float tx = cfg->target[0] - cfg->origin_root[0];
+        const float ty = cfg->target[1] - cfg->origin_root[1];
+        const float p = -sqrtf(tx * tx + ty * ty + 0.0f) / cfg->dt;
+        prev_potentials[row] = p;
+        potentials[row] = p;
+        progress[row] = 0;
+        reset[row] = 0;
+      }
+    }
   }
   FLYB_D void finish(const tcm::Smem&) {
     if (threadIdx.x == 0) tc::tma_store_wait<0>();
@@ -285,9 +303,8 @@ template <bool WANT_PI, bool WANT_V>
 __global__ void __launch_bounds__(tcm::THREADS, 1)
 net_forward_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_constant__ tcm::FwdArgs a,
                       float* __restrict__ mu_out, float* __restrict__ value_out) {
-  extern __shared__ unsigned char smem_raw[];
   FwdFinal fin{mu_out, value_out, net.num_act};
-  tcm::forward_persistent<WANT_PI, WANT_V>(net, a, fin, smem_raw);
+  tcm::forward_persistent<WANT_PI, WANT_V>(net, a, fin);
 }
 
 struct ActTcArgs {
@@ -313,13 +330,14 @@ struct ActTcArgs {
 __global__ void __launch_bounds__(tcm::THREADS, 1)
 policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_constant__ tcm::FwdArgs a,
                      const __grid_constant__ ActTcArgs x, const __grid_constant__ FlybEnvCfg cfg) {
-  extern __shared__ unsigned char smem_raw[];
   __shared__ ActTables tab;
   const int A = net.num_act;
   for (int k = threadIdx.x; k < A; k += tcm::THREADS) {
     tab.std[k] = sqrtf(__ldg(x.action_var + k));
+    tab.inv_std[k] = 1.0f / tab.std[k];
     if (x.has_env) {
       const int d = cfg.action_idx[k];
+      tab.dof[k] = d;
       tab.lo[k] = cfg.lower[d];
       tab.hi[k] = cfg.upper[d];
     }
@@ -338,6 +356,11 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
     float hl = 0.0f;
     for (int k = 0; k < A; ++k) hl += logf(tab.std[k]);
     tab.half_log_det = hl;
+    int nf = 0;
+    if (x.has_env)
+      for (int d = 0; d < cfg.num_dof; ++d)
+        if (tab.slot[d] < 0) tab.free_dof[nf++] = d;
+    tab.n_free = nf;
   }
   __syncthreads();
   ActFinal fin;
@@ -348,8 +371,8 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
   fin.cfg = &cfg; fin.has_env = x.has_env;
   fin.actions_scaled = x.actions_scaled; fin.dof_targets = x.dof_targets; fin.reset = x.reset; fin.progress = x.progress;
   fin.potentials = x.potentials; fin.prev_potentials = x.prev_potentials; fin.root = x.root; fin.dof_state = x.dof_state;
-  fin.t = &tab; fin.rst_raw = 0;
-  tcm::forward_persistent<true, false>(net, a, fin, smem_raw);
+  fin.t = &tab; fin.rst_raw = 0; fin.trace = a.trace; fin.ti = 128;
+  tcm::forward_persistent<true, false>(net, a, fin);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -400,7 +423,7 @@ int tc_launch_forward(const FlybNetLayout* net, const float* params, const void*
 // true when the fused act + pre-physics staging fits next to the weight ring
 bool tc_act_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg) {
   if (!tc_supported(net)) return false;
-  const size_t out = (size_t)tcm::TM * (2 * net->num_act + (cfg ? cfg->num_dof : 0)) * 4;
+  const size_t out = (size_t)tcm::TM * 3 * net->num_act * 4;
   return tcm::smem_bytes(net->num_obs, out) <= 227u * 1024u;
 }
 
@@ -409,7 +432,7 @@ int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpa
                   const uint64_t* offset_dev, float* action, float* logp, float* mu_out, float* obs_store,
                   const FlybEnvCfg* cfg, float* actions_scaled, float* dof_targets, int64_t* reset, int64_t* progress,
                   float* potentials, float* prev_potentials, float* root, float* dof_state, cudaStream_t st) {
-  const size_t out = (size_t)tcm::TM * (2 * net->num_act + (cfg ? cfg->num_dof : 0)) * 4;
+  const size_t out = (size_t)tcm::TM * 3 * net->num_act * 4;
   tcm::FwdArgs a{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, out, g_trace};
   ActTcArgs x{};
   x.action_var = action_var; x.noise = noise; x.seed = seed; x.offset = offset;

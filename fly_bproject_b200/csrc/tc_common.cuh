@@ -52,6 +52,11 @@ FLYB_D void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// same, for warps whose wake-up latency is not critical: back off between polls so that the polling does not
+// take issue slots / barrier-unit bandwidth from the warps doing the work
+FLYB_D void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) __nanosleep(64);
+}
 
 // ---------------------------------------------------------------------------------------------- TMA (1-D bulk)
 // global -> shared::cta, completion signalled on `bar` as transaction bytes.  16-byte aligned, size % 16 == 0.

@@ -26,3 +26,4 @@ t = trace.cpu().tolist()
 t0 = min(x for x in t if x > 0)
 print("MMA thread :", [x - t0 for x in t[:64] if x > 0])
 print("epilogue w0:", [x - t0 for x in t[64:128] if x > 0])
+print("finaliser  :", [x - t0 for x in t[128:160] if x > 0])
