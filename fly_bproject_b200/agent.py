@@ -17,7 +17,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib
+from . import _lib, dp
 from .env import Fly, _get
 
 PARAM_NAMES = [
@@ -210,10 +210,9 @@ class PPO:
         self._graphs = {}
 
         # data-parallel: one process per GPU, the only collective is the gradient all-reduce
-        self.world_size = 1
-        if torch.distributed.is_available() and torch.distributed.is_initialized():
-            self.world_size = torch.distributed.get_world_size()
-            torch.distributed.broadcast(self.net.flat, src=0)
+        self.rank, self.world_size = dp.world()
+        if self.world_size > 1:
+            dp.broadcast_params_(self.net.flat, src=0)
             self.net.repack()
 
     # ------------------------------------------------------------------ reference-compatible views
@@ -340,11 +339,10 @@ class PPO:
             lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self._obs_ring[k:j]), p(self.all_acts[k:j]),
             p(self.all_log_prob[k:j]), p(self._target[k:j]), p(self.all_advantage[k:j]), p(self.action_var), rows,
             p(self.grad), p(self.loss), self._ws_ptr, stream), "flyb_ppo_grad")
-        if self.world_size > 1:
-            torch.distributed.all_reduce(self.grad)          # SUM over ranks; the mean is taken by grad_scale
+        grad_scale = dp.grad_all_reduce_(self.grad)          # SUM over ranks; the mean is taken by grad_scale
         _lib.check(self.lib.flyb_ppo_apply(
             lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.grad), p(self.exp_avg), p(self.exp_avg_sq),
-            p(self.adam_step), 1.0 / self.world_size, p(self.grad_norm), self._ws_ptr, p(self.net.wpack), stream),
+            p(self.adam_step), grad_scale, p(self.grad_norm), self._ws_ptr, p(self.net.wpack), stream),
             "flyb_ppo_apply")
 
     def _update_body(self) -> int:

@@ -19,11 +19,13 @@
 
 namespace flyb {
 
-constexpr int ENVS = 128;          // envs per CTA == threads per CTA
+constexpr int ENVS = 64;           // envs per CTA
+constexpr int PP_THREADS = 256;    // 4 threads per env for the load / store sweeps; threads [0, ENVS) own one env each
+constexpr int PP_WARPS = PP_THREADS / 32;
 
 // look-back status word: [63:32] flag (0 none, 1 aggregate, 2 inclusive prefix), [31:0] value
 struct ScanScratch {
-  unsigned int ticket;
+  unsigned int ticket;   // unused (kept so that the scratch size / zeroing contract of ABI v2 stands)
   unsigned int done;
   unsigned long long status[1];
 };
@@ -37,7 +39,11 @@ FLYB_D void st_status(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(ENVS)
+// The kernel is latency-bound at the env counts of the reference's configs (16384 envs = 12.5 MB per launch), so
+// every thread issues ALL its global loads before the first dependent shared-memory store, the per-env scalars
+// are fetched in that same wave, the observation slab leaves before the cross-CTA scan is waited for, and the
+// look-back inspects 256 predecessors per round (one per thread) instead of 32.
+__global__ void __launch_bounds__(PP_THREADS)
 post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restrict__ root,
                     const float* __restrict__ dof_state, const float* __restrict__ force,
                     const float* __restrict__ actions_scaled, float* __restrict__ potentials,
@@ -52,55 +58,107 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   float* obs_s = smem;                        // [ENVS][O]      (O is odd -> conflict-free row access)
   float* root_s = obs_s + ENVS * O;           // [ENVS][13]
   float* force_s = root_s + ENVS * 13;        // [ENVS][33]
-  __shared__ int s_block;                     // ticket = logical CTA id
   __shared__ int s_warp_cnt[ENVS / 32];
-  __shared__ int s_excl;
+  __shared__ int s_red[PP_WARPS];
+  __shared__ int s_first;
+  __shared__ int s_last;
+  // small index / limit tables: per-lane indexed reads of the __grid_constant__ copy would serialise in the
+  // constant cache (one replay per distinct address), shared memory serves them in one wavefront
+  __shared__ int s_body[FORCE_ROWS];
+  __shared__ int s_aidx[FLYB_MAX_DOF];
+  __shared__ float s_lo[FLYB_MAX_DOF], s_hi[FLYB_MAX_DOF];
 
   const int tid = threadIdx.x;
-  if (tid == 0) s_block = (int)atomicAdd(&scratch->ticket, 1u);
-  __syncthreads();
-  const int blk = s_block;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int blk = blockIdx.x;                 // CTAs are dispatched in blockIdx order: predecessors are resident or done
   const int env0 = blk * ENVS;
   const int nenv = min(ENVS, N - env0);
 
-  // ---- stage root slab (contiguous nenv*13 floats; slab base is 16B aligned since ENVS*52 % 16 == 0)
-  {
-    const float* src = root + (size_t)env0 * 13;
-    const int n = nenv * 13;
-    const int n4 = n >> 2;
-    const float4* src4 = reinterpret_cast<const float4*>(src);
-    for (int i = tid; i < n4; i += ENVS) reinterpret_cast<float4*>(root_s)[i] = ldg_stream4(src4 + i);
-    for (int i = (n4 << 2) + tid; i < n; i += ENVS) root_s[i] = __ldg(src + i);
+  // ---- wave of loads 1: root slab (contiguous nenv*13 floats; 16B aligned since ENVS*52 % 16 == 0),
+  //      per-env scalars, the 11 gathered contact-force rows per env (flat (env, row, comp) index: a warp touches
+  //      ~11 sectors per request instead of 32)
+  constexpr int ROOT4 = ENVS * 13 / 4;        // 208 <= PP_THREADS
+  static_assert(ROOT4 <= PP_THREADS, "one float4 of the root slab per thread");
+  const int nroot = nenv * 13;
+  float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (tid * 4 + 3 < nroot) r4 = ldg_stream4(reinterpret_cast<const float4*>(root + (size_t)env0 * 13) + tid);
+  float pot_in = 0.0f;
+  long long prog_in = 0, reset_in = 0;
+  if (tid < nenv) {
+    pot_in = potentials[env0 + tid];
+    prog_in = progress[env0 + tid];
+    reset_in = reset[env0 + tid];
   }
-  // ---- contact-force gather: flat (env, row, comp)
-  {
-    const int n = nenv * FORCE_VALS;
-    for (int i = tid; i < n; i += ENVS) {
+  if (tid < FORCE_ROWS)
+    s_body[tid] = (tid < FLYB_NUM_ABDOMEN) ? cfg.abdomen_local[tid] : cfg.legtip_local[tid - FLYB_NUM_ABDOMEN];
+  if (tid >= 32 && tid < 32 + A) {
+    const int d = cfg.action_idx[tid - 32];
+    s_aidx[tid - 32] = d;
+    s_lo[tid - 32] = cfg.lower[d];
+    s_hi[tid - 32] = cfg.upper[d];
+  }
+  __syncthreads();
+  constexpr int FITER = (ENVS * FORCE_VALS + PP_THREADS - 1) / PP_THREADS;   // 9
+  float fv[FITER];
+  const int nforce = nenv * FORCE_VALS;
+#pragma unroll
+  for (int it = 0; it < FITER; ++it) {
+    const int i = tid + it * PP_THREADS;
+    fv[it] = 0.0f;
+    if (i < nforce) {
       const int e = i / FORCE_VALS;
       const int rc = i - e * FORCE_VALS;
       const int r = rc / 3;
       const int comp = rc - r * 3;
-      const int body = (r < FLYB_NUM_ABDOMEN) ? cfg.abdomen_local[r] : cfg.legtip_local[r - FLYB_NUM_ABDOMEN];
-      force_s[i] = __ldg(force + ((size_t)(env0 + e) * B + body) * 3 + comp);
+      fv[it] = __ldg(force + ((size_t)(env0 + e) * B + s_body[r]) * 3 + comp);
     }
   }
-  // ---- actuated DOF (pos, vel) pairs -> obs[12 : 12+A], obs[12+A : 12+2A]   (fly.py:795, 801)
+  // ---- wave of loads 2: actuated DOF (pos, vel) pairs and the commanded actions, 4 (env, k) elements in flight
+  //      per thread -> obs[12 : 12+A], obs[12+A : 12+2A], obs[12+2A : 12+3A]   (fly.py:795, 801, 802)
   {
     const float2* dof2 = reinterpret_cast<const float2*>(dof_state);
+    const float inv_a = 1.0f / (float)A;
     const int n = nenv * A;
-    for (int i = tid; i < n; i += ENVS) {
-      const int e = i / A;
-      const int k = i - e * A;
-      const int d = cfg.action_idx[k];
-      const float2 pv = __ldg(dof2 + (size_t)(env0 + e) * D + d);
-      obs_s[e * O + 12 + k] = unscale(pv.x, cfg.lower[d], cfg.upper[d]);
-      obs_s[e * O + 12 + A + k] = pv.y * cfg.dof_vel_scale;
-      obs_s[e * O + 12 + 2 * A + k] = __ldg(actions_scaled + (size_t)env0 * A + i);  // fly.py:802
+    constexpr int DU = 4;
+    for (int base = 0; base < n; base += DU * PP_THREADS) {
+      float2 pv[DU];
+      float act[DU];
+      int ee[DU], kk[DU];
+#pragma unroll
+      for (int u = 0; u < DU; ++u) {
+        const int i = base + u * PP_THREADS + tid;
+        const int e = (int)(((float)i + 0.5f) * inv_a);   // i / A, exact for i < 2^22
+        ee[u] = e;
+        kk[u] = i - e * A;
+        pv[u] = make_float2(0.f, 0.f);
+        act[u] = 0.0f;
+        if (i < n) {
+          pv[u] = __ldg(dof2 + (size_t)(env0 + e) * D + s_aidx[kk[u]]);
+          act[u] = __ldg(actions_scaled + (size_t)env0 * A + i);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < DU; ++u) {
+        const int i = base + u * PP_THREADS + tid;
+        if (i < n) {
+          float* o = obs_s + ee[u] * O + 12 + kk[u];
+          o[0] = unscale(pv[u].x, s_lo[kk[u]], s_hi[kk[u]]);
+          o[A] = pv[u].y * cfg.dof_vel_scale;
+          o[2 * A] = act[u];
+        }
+      }
     }
+  }
+  if (tid * 4 + 3 < nroot) reinterpret_cast<float4*>(root_s)[tid] = r4;
+  for (int i = (nroot & ~3) + tid; i < nroot; i += PP_THREADS) root_s[i] = __ldg(root + (size_t)env0 * 13 + i);
+#pragma unroll
+  for (int it = 0; it < FITER; ++it) {
+    const int i = tid + it * PP_THREADS;
+    if (i < nforce) force_s[i] = fv[it];
   }
   __syncthreads();
 
-  // ---- per-env math: one thread per env
+  // ---- per-env math: one thread per env (warps 0 .. ENVS/32-1)
   bool flag = false;
   float my_reward = 0.0f;
   if (tid < nenv) {
@@ -108,8 +166,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     float r[13];
 #pragma unroll
     for (int j = 0; j < 13; ++j) r[j] = root_s[tid * 13 + j];
-    const EnvStepOut out = env_post_one(cfg, r, force_s + tid * FORCE_VALS, obs_s + tid * O, potentials[env],
-                                        progress[env], reset[env]);
+    const EnvStepOut out = env_post_one(cfg, r, force_s + tid * FORCE_VALS, obs_s + tid * O, pot_in, prog_in, reset_in);
     potentials[env] = out.potential;
     prev_potentials[env] = out.prev_potential;
     progress[env] = out.progress;
@@ -122,14 +179,14 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     heading_vec[env * 3 + 2] = out.heading_vec.z;
     flag = out.reset != 0;
   }
-
-  // ---- reset-id compaction, ascending: ballot -> CTA prefix -> look-back across CTAs
-  const unsigned ballot = __ballot_sync(0xffffffffu, flag);
-  const int lane = tid & 31, warp = tid >> 5;
-  if (lane == 0) s_warp_cnt[warp] = __popc(ballot);
-  if (reward_sum) {   // score accumulator (ppo.py:233), one atomic per warp
-    const float ws = warp_sum(my_reward);
-    if (lane == 0) atomicAdd(reward_sum, ws);
+  unsigned ballot = 0u;
+  if (warp < ENVS / 32) {
+    ballot = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) s_warp_cnt[warp] = __popc(ballot);
+    if (reward_sum) {   // score accumulator (ppo.py:233), one atomic per warp
+      const float ws = warp_sum(my_reward);
+      if (lane == 0) atomicAdd(reward_sum, ws);
+    }
   }
   __syncthreads();
   int warp_off = 0, block_cnt = 0;
@@ -138,41 +195,9 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     if (w < warp) warp_off += s_warp_cnt[w];
     block_cnt += s_warp_cnt[w];
   }
-  if (warp == 0) {
-    unsigned long long* status = scratch->status;
-    int excl = 0;
-    if (blk == 0) {
-      if (lane == 0) st_status(status, (2ull << 32) | (unsigned)block_cnt);
-    } else {
-      if (lane == 0) st_status(status + blk, (1ull << 32) | (unsigned)block_cnt);
-      int look = blk - 1;  // lane l inspects CTA (look - l)
-      while (true) {
-        const int idx = look - lane;
-        unsigned long long st = 2ull << 32;  // lanes before CTA 0 act as a zero-valued inclusive prefix
-        if (idx >= 0) {
-          do { st = ld_status(status + idx); } while ((st >> 32) == 0ull);
-        }
-        const unsigned has_prefix = __ballot_sync(0xffffffffu, (st >> 32) == 2ull);
-        const int first = __ffs(has_prefix) - 1;  // nearest predecessor that already holds an inclusive prefix
-        int v = (first < 0 || lane <= first) ? (int)(unsigned)(st & 0xffffffffull) : 0;
-#pragma unroll
-        for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
-        excl += v;
-        if (first >= 0) break;
-        look -= 32;
-      }
-      if (lane == 0) st_status(status + blk, (2ull << 32) | (unsigned)(excl + block_cnt));
-    }
-    if (lane == 0) {
-      s_excl = excl;
-      if (env0 + ENVS >= N) *reset_count = excl + block_cnt;  // the CTA that owns the last env
-    }
-  }
-  __syncthreads();
-  if (flag) {
-    const int pos = s_excl + warp_off + __popc(ballot & ((1u << lane) - 1u));
-    reset_ids[pos] = env0 + tid;
-  }
+  // publish this CTA's count as early as possible: an inclusive prefix for CTA 0, an aggregate otherwise
+  unsigned long long* status = scratch->status;
+  if (tid == 0) st_status(status + blk, ((blk == 0 ? 2ull : 1ull) << 32) | (unsigned)block_cnt);
 
   // ---- obs slab out: full 128-bit stores (slab base 16B aligned: ENVS*O*4 % 16 == 0)
   {
@@ -180,32 +205,63 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     const int n4 = n >> 2;
     float4* dst4 = reinterpret_cast<float4*>(obs + (size_t)env0 * O);
     float4* cpy4 = obs_copy ? reinterpret_cast<float4*>(obs_copy + (size_t)env0 * O) : nullptr;
-    for (int i = tid; i < n4; i += ENVS) {
+    for (int i = tid; i < n4; i += PP_THREADS) {
       const float4 v = reinterpret_cast<const float4*>(obs_s)[i];
       dst4[i] = v;
       if (cpy4) stg_stream4(cpy4 + i, v);
     }
-    for (int i = (n4 << 2) + tid; i < n; i += ENVS) {
+    for (int i = (n4 << 2) + tid; i < n; i += PP_THREADS) {
       obs[(size_t)env0 * O + i] = obs_s[i];
       if (obs_copy) obs_copy[(size_t)env0 * O + i] = obs_s[i];
     }
   }
 
-  // ---- self-cleaning scratch: the last CTA to finish re-arms ticket / status for the next launch
+  // ---- reset-id compaction, ascending (== torch.nonzero): decoupled look-back across CTAs, one predecessor per
+  //      thread and round; threads that fall before CTA 0 act as a zero-valued inclusive prefix
+  int excl = 0;
+  if (blk > 0) {
+    int look = blk - 1;
+    while (true) {   // block-uniform
+      const int idx = look - tid;
+      unsigned long long st = 2ull << 32;
+      if (idx >= 0) {
+        do { st = ld_status(status + idx); } while ((st >> 32) == 0ull);
+      }
+      if (tid == 0) s_first = PP_THREADS;
+      __syncthreads();
+      if ((st >> 32) == 2ull) atomicMin(&s_first, tid);   // nearest predecessor that already holds an inclusive prefix
+      __syncthreads();
+      const int first = s_first;
+      int v = (first == PP_THREADS || tid <= first) ? (int)(unsigned)(st & 0xffffffffull) : 0;
+#pragma unroll
+      for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
+      if (lane == 0) s_red[warp] = v;
+      __syncthreads();
+#pragma unroll
+      for (int w = 0; w < PP_WARPS; ++w) excl += s_red[w];
+      if (first != PP_THREADS) break;
+      look -= PP_THREADS;
+    }
+    if (tid == 0) st_status(status + blk, (2ull << 32) | (unsigned)(excl + block_cnt));
+  }
+  if (tid == 0 && env0 + ENVS >= N) *reset_count = excl + block_cnt;   // the CTA that owns the last env
+  if (flag) {
+    const int pos = excl + warp_off + __popc(ballot & ((1u << lane) - 1u));
+    reset_ids[pos] = env0 + tid;
+  }
+
+  // ---- self-cleaning scratch: the last CTA to finish re-arms the status words for the next launch
   __syncthreads();
   if (tid == 0) {
     __threadfence();
     const unsigned nblk = gridDim.x;
     const unsigned prev = atomicAdd(&scratch->done, 1u);
-    s_block = (prev == nblk - 1) ? 1 : 0;
+    s_last = (prev == nblk - 1) ? 1 : 0;
   }
   __syncthreads();
-  if (s_block) {
-    for (int i = tid; i < (int)gridDim.x; i += ENVS) scratch->status[i] = 0ull;
-    if (tid == 0) {
-      scratch->ticket = 0u;
-      scratch->done = 0u;
-    }
+  if (s_last) {
+    for (int i = tid; i < (int)gridDim.x; i += PP_THREADS) scratch->status[i] = 0ull;
+    if (tid == 0) scratch->done = 0u;
   }
 }
 
@@ -309,7 +365,7 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
   rc = ensure_smem(reinterpret_cast<const void*>(post_physics_kernel), smem);
   if (rc != FLYB_OK) return rc;
   const int grid = (cfg->num_envs + ENVS - 1) / ENVS;
-  post_physics_kernel<<<grid, ENVS, smem, (cudaStream_t)stream>>>(
+  post_physics_kernel<<<grid, PP_THREADS, smem, (cudaStream_t)stream>>>(
       *cfg, root, dof_state, force, actions_scaled, potentials, prev_potentials, (long long*)progress,
       (long long*)reset, obs, reward, up_vec, heading_vec, reset_ids, reset_count, (ScanScratch*)scratch, obs_copy,
       reward_copy, reward_sum);
