@@ -63,7 +63,7 @@ SIGNATURES = {
     "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, _P]),
     "flyb_gae": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, _P]),
     "flyb_ppo_workspace_bytes": (C.c_size_t, [C.POINTER(NetLayout), C.c_int64]),
-    "flyb_ppo_grad": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 7 + [C.c_int64] + [_P] * 4),
+    "flyb_ppo_grad": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 8 + [C.c_int64] + [_P] * 4),
     "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5 + [C.c_float, _P, _P, _P, _P]),
     "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P, _P]),
 }
@@ -84,7 +84,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)  # AttributeError if the .so does not export it
             fn.restype = restype
             fn.argtypes = argtypes
-        if handle.flyb_abi_version() != 2:
+        if handle.flyb_abi_version() != 3:
             raise FlybError("libflyb200.so ABI version mismatch")
         _lib = handle
     return _lib

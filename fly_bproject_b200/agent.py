@@ -336,7 +336,7 @@ class PPO:
         rows = (j - k) * self.num_envs
         lay = C.byref(self.net.layout)
         _lib.check(self.lib.flyb_ppo_grad(
-            lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self._obs_ring[k:j]), p(self.all_acts[k:j]),
+            lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.net.wpack), p(self._obs_ring[k:j]), p(self.all_acts[k:j]),
             p(self.all_log_prob[k:j]), p(self._target[k:j]), p(self.all_advantage[k:j]), p(self.action_var), rows,
             p(self.grad), p(self.loss), self._ws_ptr, stream), "flyb_ppo_grad")
         grad_scale = dp.grad_all_reduce_(self.grad)          # SUM over ranks; the mean is taken by grad_scale

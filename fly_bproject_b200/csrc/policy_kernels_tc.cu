@@ -56,6 +56,16 @@ static PackPlan forward_plan(const FlybNetLayout& net) {
   add(H3, H2 / 8, net.off[4], H2, 0, 0, H3, H2);                   // W3pi  (to_mean.0)
   add(H3, H2 / 8, net.off[8], H2, 0, 0, H3, H2);                   // W3v   (to_value.0)
   add(APAD, H3 / 8, net.off[6], H3, 0, 0, net.num_act, H3);        // W4    (to_mean.2), rows >= A are zero
+  // ---- backward operands (ppo_kernels_tc.cu): B[n][k] = W[k][n], consumed after the forward stages
+  auto addt = [&](int N, int ksteps, int w_off, int ldw, int n0, int n_rows, int k_cols) {
+    add(N, ksteps, w_off, ldw, n0, 0, n_rows, k_cols);
+    p.seg[p.nseg - 1].transposed = 1;
+  };
+  addt(H3, APAD / 8, net.off[6], H3, 0, H3, net.num_act);          // W4^T : dM1 = dZmu * W4       (k = action)
+  addt(H2, H3 / 8, net.off[4], H2, 0, H2, H3);                     // W3pi^T: dH2 += dZm1 * W3pi    (k = m1 feature)
+  addt(H2, H3 / 8, net.off[8], H2, 0, H2, H3);                     // W3v^T : dH2 += dZv1 * W3v
+  addt(128, H2 / 8, net.off[2], H1, 0, 128, H2);                   // W2^T, h1 features [0,128)   (k = h2 feature)
+  addt(128, H2 / 8, net.off[2], H1, 128, 128, H2);                 // W2^T, h1 features [128,256)
   p.total_stages = stage;
   return p;
 }

@@ -21,6 +21,11 @@ int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
 bool tc_supported(const FlybNetLayout* net);
 int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st);
+size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows);
+int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
+                const float* obs, const float* action, const float* old_logp, const float* target,
+                const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
+                void* workspace, cudaStream_t st);
 
 constexpr int DW_SPLITS_MAX = 64;
 constexpr int NORM_BLOCKS = 64;
@@ -416,11 +421,11 @@ using namespace flyb;
 
 extern "C" size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t rows) {
   if (!net || rows <= 0) return 0;
-  return carve_ws(*net, rows, nullptr).bytes;
+  return std::max(carve_ws(*net, rows, nullptr).bytes, tc_ppo_workspace_bytes(net, rows));
 }
 
-extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const float* obs,
-                             const float* action, const float* old_logp, const float* target,
+extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
+                             const float* obs, const float* action, const float* old_logp, const float* target,
                              const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
                              void* workspace, void* stream) {
   int rc = validate_net(net, params);
@@ -430,6 +435,11 @@ extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, co
   FLYB_REQUIRE(rows > 0, "flyb_ppo_grad: rows must be > 0");
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_grad: workspace must be 256-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
+  if (wpack) {   // tensor-core path (ppo_kernels_tc.cu)
+    FLYB_REQUIRE(tc_supported(net), "flyb_ppo_grad: wpack given but the tensor-core path does not cover this shape");
+    return tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
+                       workspace, st);
+  }
   const PpoWs w = carve_ws(*net, rows, workspace);
 
   GradArgs a{};

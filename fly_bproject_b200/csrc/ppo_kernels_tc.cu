@@ -1,0 +1,869 @@
+// Kernel (d), tensor-core path: one optimiser step's gradient of PPO.update (reference ppo.py:183-197) on
+// tcgen05 / TMEM — forward of both heads on ONE trunk evaluation, clipped-surrogate + SmoothL1 loss, backward
+// chain and weight gradients as 3xTF32 GEMMs with fp32 accumulation.  Same results contract as the CUDA-core path
+// in ppo_kernels.cu.
+//
+//   ppo_fwd_bwd_tc_kernel  persistent over 128-row tiles, same role split as the forward (mlp_tc.cuh): 8 epilogue
+//       warps, a TMA producer warp, an MMA issuer warp.  The forward is the forward of mlp_tc.cuh; its epilogues
+//       additionally write every layer input (X, h1, h2, [m1|v1]) to the workspace as fp32 "row images".  The loss
+//       terms are evaluated per row in registers; dL/dmu and dL/dv start the backward chain, which runs as TS-mode
+//       MMAs (A = dZ in tensor memory) against TRANSPOSED weight slabs of the packed stream:
+//           dM1 = dZmu * W4          dH2 = [dZm1 | dZv1] * [W3pi ; W3v]          dH1 = dZh2 * W2  (two N = 128 halves)
+//       and each epilogue multiplies by ELU'(y) = y > 0 ? 1 : y + 1.  Every dZ is written as a row image too.
+//   ppo_dw_tc_kernel       dW_l = dZ_l^T * X_l: the sample dimension is the MMA's K.  Row images are streamed by bulk
+//       TMA, transposed + hi/lo split by 8 warps into K-major UMMA operands in shared memory (SS MMAs), accumulators
+//       stay in TMEM over all tiles of a CTA; bias gradients come from the same MMAs against a constant ones operand.
+//       CTAs alternate between two roles (layers {2,4} and {1,3}) so that a role's accumulators fit 512 columns.
+//   ppo_reduce_tc_kernel   grad = sum over the per-CTA partials in a fixed order (deterministic), loss.
+//
+// Row image of an operand with F features, one 128-row tile: [16 k-steps][F/4][8 rows][4 floats]: a thread that owns
+// row r writes/reads 16-byte chunks, a warp's access is 4 x 128 contiguous bytes, and a k-step group is one
+// contiguous block for the bulk copy.
+//
+// TMEM columns of the fwd/bwd kernel.  Trunk as in mlp_tc.cuh.  Afterwards:
+//   A3 (h2) hi|lo [0,256)   D3 pi|v [256,384)   A4 (m1) hi|lo [384,512)   D4 (mu) [256,288)
+//   backward:  A5 (dZmu) hi [0,32) lo [32,64)      D5 (dM1) [320,384)
+//              A6 ([dZm1|dZv1]) hi [0,128) lo [128,256)      D6 (dH2) [384,512)
+//              A7 (dZh2) hi [0,128) lo [128,256)             D7 (dH1) [256,512)
+#include <algorithm>
+
+#include "mlp_tc.cuh"
+
+namespace flyb {
+
+int num_sms();
+int validate_net(const FlybNetLayout* net, const float* params);
+bool tc_supported(const FlybNetLayout* net);
+
+namespace tcb {
+using namespace tcm;
+
+constexpr int W4T_STAGES = (APAD / 8) * 2 * (H3 * 32) / STAGE;        // 2
+constexpr int W3T_STAGES = (2 * H3 / 8) * 2 * (H2 * 32) / STAGE;      // 16
+constexpr int W2T_STAGES = 2 * (H2 / 8) * 2 * (128 * 32) / STAGE;     // 32
+constexpr int ALL_STAGES = FWD_STAGES + W4T_STAGES + W3T_STAGES + W2T_STAGES;   // 120
+
+// image feature counts
+constexpr int F_X = K0, F_H1 = H1, F_H2 = H2, F_MV = 2 * H3, F_DZMUV = 64, F_DZMV = 2 * H3, F_DZH2 = H2, F_DZH1 = H1;
+
+struct Images {   // per-operand base pointers; tile t of an operand with F features starts at base + t * 128 * F
+  float *x, *h1, *h2, *mv, *dzmuv, *dzmv, *dzh2, *dzh1;
+};
+
+struct GradArgs {
+  const float* action;
+  const float* old_logp;
+  const float* target;
+  const float* advantage;
+  const float* action_var;
+  float clip_lo, clip_hi, inv_rows;
+  float* loss_part;   // [gridDim.x][2]
+};
+
+FLYB_D float* img_ptr(float* tile_base, int F, int r, int f) {
+  return tile_base + (r >> 3) * (F * 8) + (f >> 2) * 32 + (r & 7) * 4;
+}
+FLYB_D void img_store16(float* p, const float (&y)[16]) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g)
+    *reinterpret_cast<float4*>(p + g * 32) = make_float4(y[4 * g], y[4 * g + 1], y[4 * g + 2], y[4 * g + 3]);
+}
+FLYB_D void img_load16(const float* p, float (&y)[16]) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const float4 v = *reinterpret_cast<const float4*>(p + g * 32);
+    y[4 * g] = v.x; y[4 * g + 1] = v.y; y[4 * g + 2] = v.z; y[4 * g + 3] = v.w;
+  }
+}
+// 16 fp32 values -> hi / lo planes of an A operand in tensor memory
+FLYB_D void tmem_put16(uint32_t hi_addr, uint32_t lo_addr, const float (&y)[16]) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) split_fast(y[j], hi[j], lo[j]);
+  tc::tmem_st16(hi_addr, hi);
+  tc::tmem_st16(lo_addr, lo);
+}
+// y = ELU(D + bias) for `ncols` (multiple of 16) accumulator columns: A operand (hi/lo) + row image
+FLYB_D void epi_elu_save(uint32_t d_addr, uint32_t ah_addr, uint32_t al_addr, const float* bias, float* img, int ncols) {
+#pragma unroll 1
+  for (int c = 0; c < ncols; c += 16) {
+    uint32_t v[16];
+    tc::tmem_ld16(d_addr + c, v);
+    tc::tmem_wait_ld();
+    float y[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) y[j] = elu_fast(__uint_as_float(v[j]) + bias[c + j]);
+    tmem_put16(ah_addr + c, al_addr + c, y);
+    img_store16(img + (c >> 2) * 32, y);
+  }
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_constant__ FwdArgs a,
+                      const __grid_constant__ GradArgs ga, const __grid_constant__ Images im) {
+  extern __shared__ unsigned char smem_raw[];
+  const Smem s = carve(smem_raw, a.O, 0);
+  __shared__ float s_std[APAD], s_inv_var[APAD];
+  __shared__ float s_half_log_det;
+  __shared__ float s_vp[2 * TM];
+  __shared__ float s_red[EPI_WARPS][2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int O = a.O, A = a.A;
+  const long long ntiles = (a.rows + TM - 1) / TM;
+
+  // ---- one-time setup
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NST; ++i) {
+      tc::mbar_init(&s.full[i], 1);
+      tc::mbar_init(&s.empty[i], 1);
+    }
+    tc::mbar_init(&s.bar_a[0], EPI_WARPS);
+    tc::mbar_init(&s.bar_a[1], EPI_WARPS);
+    tc::mbar_init(&s.bar_d[0], 1);
+    tc::mbar_init(&s.bar_d[1], 1);
+    tc::mbar_init(s.obs_full, 1);
+    tc::mbar_init(s.obs_empty, EPI_WARPS);
+    tc::fence_mbar_init();
+  }
+  if (warp == MMA_WARP) tc::tmem_alloc(s.tmem_slot, 512);
+  {
+    const float* p = a.params;
+    for (int i = threadIdx.x; i < B_TOTAL; i += THREADS) {
+      float v = 0.0f;
+      if (i < B_B2) v = p[net.off[1] + i];
+      else if (i < B_B3PI) v = p[net.off[3] + i - B_B2];
+      else if (i < B_B3V) v = p[net.off[5] + i - B_B3PI];
+      else if (i < B_B4) v = p[net.off[9] + i - B_B3V];
+      else if (i < B_W4V) v = (i - B_B4 < A) ? p[net.off[7] + i - B_B4] : 0.0f;
+      else if (i < B_B4V) v = p[net.off[10] + i - B_W4V];
+      else if (i == B_B4V) v = p[net.off[11]];
+      s.bias[i] = v;
+    }
+    if (threadIdx.x < APAD) {
+      const float var = threadIdx.x < A ? __ldg(ga.action_var + threadIdx.x) : 1.0f;
+      const float sd = sqrtf(var);
+      s_std[threadIdx.x] = sd;
+      s_inv_var[threadIdx.x] = 1.0f / (sd * sd);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  if (threadIdx.x == 0) {
+    float hl = 0.0f;
+    for (int k = 0; k < A; ++k) hl += logf(s_std[k]);
+    s_half_log_det = hl;
+  }
+  const uint32_t tb = *s.tmem_slot;
+  constexpr uint32_t C_D4B = 256, C_A5H = 0, C_A5L = 32, C_D5 = 320, C_A6H = 0, C_A6L = 128, C_D6 = 384, C_A7H = 0,
+                     C_A7L = 128, C_D7 = 256;
+
+  if (warp == PRODUCER_WARP) {
+    // =========================================================================== TMA producer (warp-uniform)
+    const uint32_t leader = tc::elect_one() ? 1u : 0u;
+    const uint32_t ring = tc::smem_u32(s.ring);
+    uint32_t gs = 0, obs_phase = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long row0 = tile * TM;
+      const int nrows = (int)min((long long)TM, a.rows - row0);
+      const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
+      const float* src = a.obs + (size_t)row0 * O;
+      tc::mbar_wait_relaxed(s.obs_empty, obs_phase ^ 1u);
+      obs_phase ^= 1u;
+      if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
+        tc::mbar_arrive_expect_tx(s.obs_full, bytes);
+        tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
+      }
+      const unsigned char* g = a.wpack;
+      for (int i = 0; i < ALL_STAGES; ++i, ++gs, g += STAGE) {
+        const uint32_t slot = gs & (NST - 1);
+        tc::mbar_wait_relaxed(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
+        const uint32_t bar = tc::smem_u32(&s.full[slot]);
+        asm volatile(
+            "{\n\t.reg .pred q;\n\t.reg .b64 st;\n\tsetp.ne.b32 q, %4, 0;\n\t"
+            "@q mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %3;\n\t"
+            "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2], %3, [%0];\n\t}" ::"r"(bar),
+            "r"(ring + slot * STAGE), "l"(g), "r"((uint32_t)STAGE), "r"(leader)
+            : "memory");
+      }
+    }
+  } else if (warp == MMA_WARP) {
+    // =========================================================================== MMA issuer (warp-uniform)
+    MmaState m{tc::elect_one() ? 1u : 0u, tc::smem_u32(s.ring), s.full, s.empty, 0u};
+    const uint32_t xh = tc::smem_u32(s.xhi), xl = tc::smem_u32(s.xlo);
+    uint32_t pa = 0u;
+    auto wait_a = [&](int b) {
+      tc::mbar_wait_relaxed(&s.bar_a[b], (pa >> b) & 1u);
+      pa ^= 1u << b;
+      tc::tc_fence_after();
+    };
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      wait_a(0);   // X staged (and the previous tile's accumulators drained)
+#pragma unroll 1
+      for (int c = -2; c < NCH; ++c) {
+        if (c >= 0) {
+          const int b = c & 1;
+          wait_a(b);
+          mma_segment<H2, CH / 8, false>(m, tb + C_A2 + 128 * b, tb + C_A2 + 128 * b + CH, tb + C_D2, c > 0);
+        }
+        if (c + 2 < NCH) {
+          const int b2 = (c + 2) & 1;
+          mma_segment<CH, K0 / 8, true>(m, xh, xl, tb + C_D1 + CH * b2, false);
+          umma_commit_if(m.leader, &s.bar_d[b2]);
+        }
+      }
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D2
+      wait_a(0);                               // A3
+      mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3, false);
+      mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3 + H3, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D3
+      wait_a(0);                               // A4
+      mma_segment<APAD, H3 / 8, false>(m, tb + C_A4H, tb + C_A4L, tb + C_D4B, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D4
+      wait_a(0);                               // A5 = dZmu (and dZv1 in its A6 slots)
+      mma_segment<H3, APAD / 8, false>(m, tb + C_A5H, tb + C_A5L, tb + C_D5, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D5 = dM1
+      wait_a(0);                               // A6 = [dZm1 | dZv1]
+      mma_segment<H2, 2 * H3 / 8, false>(m, tb + C_A6H, tb + C_A6L, tb + C_D6, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D6 = dH2
+      wait_a(0);                               // A7 = dZh2
+      mma_segment<128, H2 / 8, false>(m, tb + C_A7H, tb + C_A7L, tb + C_D7, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D7, h1 features [0,128)
+      mma_segment<128, H2 / 8, false>(m, tb + C_A7H, tb + C_A7L, tb + C_D7 + 128, false);
+      umma_commit_if(m.leader, &s.bar_d[1]);   // D7, h1 features [128,256)
+    }
+  } else {
+    // =========================================================================== epilogue warps
+    const int q = warp & 3, h = warp >> 2;
+    const uint32_t lane_base = (uint32_t)q * 32u;
+    const int r = q * 32 + lane;
+    const uint32_t t0 = tc::tmem_addr(tb, lane_base, 0);
+    uint32_t pd = 0u, obs_phase = 0u;
+    float surr_sum = 0.0f, sl1_sum = 0.0f;
+    const float a_log_2pi = (float)((double)A * 1.8378770664093453);
+    auto wait_d = [&](int b) {
+      tc::mbar_wait(&s.bar_d[b], (pd >> b) & 1u);
+      pd ^= 1u << b;
+      tc::tc_fence_after();
+    };
+    auto arrive_a = [&](int b) {
+      tc::tmem_wait_st();
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&s.bar_a[b]);
+    };
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long row0 = tile * TM;
+      const int nrows = (int)min((long long)TM, a.rows - row0);
+      const bool live = r < nrows;
+      const long long row = row0 + r;
+      float* x_t = im.x + (size_t)tile * TM * F_X;
+      float* h1_t = im.h1 + (size_t)tile * TM * F_H1;
+      float* h2_t = im.h2 + (size_t)tile * TM * F_H2;
+      float* mv_t = im.mv + (size_t)tile * TM * F_MV;
+      float* dzmuv_t = im.dzmuv + (size_t)tile * TM * F_DZMUV;
+      float* dzmv_t = im.dzmv + (size_t)tile * TM * F_DZMV;
+      float* dzh2_t = im.dzh2 + (size_t)tile * TM * F_DZH2;
+      float* dzh1_t = im.dzh1 + (size_t)tile * TM * F_DZH1;
+
+      const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
+      const float* src = a.obs + (size_t)row0 * O;
+      const bool by_tma = (bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0;
+      if (by_tma) {
+        tc::mbar_wait(s.obs_full, obs_phase);
+        obs_phase ^= 1u;
+      } else {
+        for (int i = threadIdx.x; i < nrows * O; i += EPI_THREADS) s.obs[i] = __ldg(src + i);
+        tc::fence_proxy_async();
+        epi_bar_sync();
+      }
+      // ---- X = split(obs row) in the UMMA K-major layout (layer-1 A operand) + row image (dW1's B operand)
+      {
+        const float* xr = s.obs + r * O;
+#pragma unroll 2
+        for (int g = 0; g < K0 / 8; ++g) {
+          const int kc = h * (K0 / 8) + g;
+          uint32_t hi[4], lo[4];
+          float xv[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c = kc * 4 + j;
+            xv[j] = (live && c < O) ? xr[c] : 0.0f;
+            split_fast(xv[j], hi[j], lo[j]);
+          }
+          reinterpret_cast<uint4*>(s.xhi)[kc * TM + r] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          reinterpret_cast<uint4*>(s.xlo)[kc * TM + r] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          *reinterpret_cast<float4*>(img_ptr(x_t, F_X, r, kc * 4)) = make_float4(xv[0], xv[1], xv[2], xv[3]);
+        }
+        tc::fence_proxy_async();
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(s.obs_empty);
+      arrive_a(0);
+
+      // ---- trunk
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        const int b = c & 1;
+        wait_d(b);
+        epi_elu_save(t0 + C_D1 + CH * b + 32 * h, t0 + C_A2 + 128 * b + 32 * h, t0 + C_A2 + 128 * b + CH + 32 * h,
+                     s.bias + B_B1 + c * CH + 32 * h, img_ptr(h1_t, F_H1, r, c * CH + 32 * h), 32);
+        arrive_a(b);
+      }
+      wait_d(0);   // D2
+      epi_elu_save(t0 + C_D2 + 64 * h, t0 + C_A3H + 64 * h, t0 + C_A3L + 64 * h, s.bias + B_B2 + 64 * h,
+                   img_ptr(h2_t, F_H2, r, 64 * h), 64);
+      arrive_a(0);
+      wait_d(0);   // D3
+      epi_elu_save(t0 + C_D3 + 32 * h, t0 + C_A4H + 32 * h, t0 + C_A4L + 32 * h, s.bias + B_B3PI + 32 * h,
+                   img_ptr(mv_t, F_MV, r, 32 * h), 32);
+      arrive_a(0);   // -> D4
+
+      // ---- value head: v1 = ELU(D3v + b3v) (32 columns per thread), value, dL/dv, dZv1
+      float dval;
+      {
+        float v1[32];
+        float part = 0.0f;
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          const int c0 = h * 32 + g * 16;
+          uint32_t v[16];
+          tc::tmem_ld16(t0 + C_D3 + H3 + c0, v);
+          tc::tmem_wait_ld();
+          float y[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            y[j] = elu_fast(__uint_as_float(v[j]) + s.bias[B_B3V + c0 + j]);
+            v1[g * 16 + j] = y[j];
+            part = fmaf(y[j], s.bias[B_W4V + c0 + j], part);
+          }
+          img_store16(img_ptr(mv_t, F_MV, r, H3 + c0), y);
+        }
+        s_vp[h * TM + r] = part;
+        const float tgt = live ? __ldg(ga.target + row) : 0.0f;
+        tc::tc_fence_before();
+        epi_bar_sync();
+        const float value = s_vp[r] + s_vp[TM + r] + s.bias[B_B4V];
+        const float z = value - tgt;
+        const float az = fabsf(z);
+        dval = live ? ga.inv_rows * (az < 1.0f ? z : (z > 0.0f ? 1.0f : -1.0f)) : 0.0f;   // smooth_l1, beta = 1
+        if (h == 0 && live) sl1_sum += az < 1.0f ? 0.5f * z * z : az - 0.5f;
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          const int c0 = h * 32 + g * 16;
+          float dz[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) dz[j] = dval * s.bias[B_W4V + c0 + j] * elu_grad_from_out(v1[g * 16 + j]);
+          tmem_put16(t0 + C_A6H + H3 + c0, t0 + C_A6L + H3 + c0, dz);
+          img_store16(img_ptr(dzmv_t, F_DZMV, r, H3 + c0), dz);
+        }
+      }
+      // ---- policy head: loss terms of this row (ppo.py:184-194), dL/dmu -> dZmu
+      {
+        float act[APAD];
+#pragma unroll
+        for (int k = 0; k < APAD; ++k) act[k] = (live && k < A) ? __ldg(ga.action + (size_t)row * A + k) : 0.0f;
+        const float old_lp = live ? __ldg(ga.old_logp + row) : 0.0f;
+        const float adv = live ? __ldg(ga.advantage + row) : 0.0f;
+        wait_d(0);   // D4
+        float mu[APAD];
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          uint32_t v[16];
+          tc::tmem_ld16(t0 + C_D4B + g * 16, v);
+          tc::tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) mu[g * 16 + j] = elu_fast(__uint_as_float(v[j]) + s.bias[B_B4 + g * 16 + j]);
+        }
+        float msum = 0.0f;
+#pragma unroll
+        for (int k = 0; k < APAD; ++k)
+          if (k < A) {
+            const float diff = (act[k] - mu[k]) / s_std[k];
+            msum += diff * diff;
+          }
+        const float logp = -0.5f * (a_log_2pi + msum) - s_half_log_det;
+        const float ratio = expf(logp - old_lp);
+        const float s1 = ratio * adv;
+        const float s2 = fminf(fmaxf(ratio, ga.clip_lo), ga.clip_hi) * adv;
+        const bool in_range = ratio >= ga.clip_lo && ratio <= ga.clip_hi;
+        float gsel;   // d min(s1, s2) / d ratio with torch.minimum's tie rule (half to each side)
+        if (s1 < s2) gsel = adv;
+        else if (s1 > s2) gsel = in_range ? adv : 0.0f;
+        else gsel = 0.5f * adv + (in_range ? 0.5f * adv : 0.0f);
+        const float dlogp = live ? -ga.inv_rows * gsel * ratio : 0.0f;
+        if (h == 0 && live) surr_sum += fminf(s1, s2);
+        float dz[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          // columns 16h .. 16h+15 (static register indexing: select after computing both candidates)
+          const float mu_k = h ? mu[16 + j] : mu[j];
+          const float a_k = h ? act[16 + j] : act[j];
+          const int k = 16 * h + j;
+          const float dmu = dlogp * ((a_k - mu_k) * s_inv_var[k]);
+          dz[j] = (k < A) ? dmu * elu_grad_from_out(mu_k) : 0.0f;   // trailing ELU on mu (ppo.py:30)
+        }
+        tmem_put16(t0 + C_A5H + 16 * h, t0 + C_A5L + 16 * h, dz);   // [0,64): A3 columns, dead since D3
+        // image [dZmu (32) | dZval | 0 ...]: each half writes its 16 dZmu columns and one 16-block of the tail
+        img_store16(img_ptr(dzmuv_t, F_DZMUV, r, 16 * h), dz);
+        float tail[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) tail[j] = 0.0f;
+        if (h == 0) tail[0] = dval;   // feature 32
+        img_store16(img_ptr(dzmuv_t, F_DZMUV, r, 32 + 16 * h), tail);
+        arrive_a(0);   // -> D5
+      }
+      // ---- dZm1 = (dZmu * W4) .* ELU'(m1): 32 columns per thread
+      wait_d(0);   // D5
+#pragma unroll 1
+      for (int g = 0; g < 2; ++g) {
+        const int c0 = 32 * h + 16 * g;
+        uint32_t d[16], mh[16], ml[16];
+        tc::tmem_ld16(t0 + C_D5 + c0, d);
+        tc::tmem_ld16(t0 + C_A4H + c0, mh);
+        tc::tmem_ld16(t0 + C_A4L + c0, ml);
+        tc::tmem_wait_ld();
+        float dz[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          dz[j] = __uint_as_float(d[j]) * elu_grad_from_out(__uint_as_float(mh[j]) + __uint_as_float(ml[j]));
+        tmem_put16(t0 + C_A6H + c0, t0 + C_A6L + c0, dz);
+        img_store16(img_ptr(dzmv_t, F_DZMV, r, c0), dz);
+      }
+      arrive_a(0);   // -> D6
+      // ---- dZh2 = (dZm1 * W3pi + dZv1 * W3v) .* ELU'(h2): 64 columns per thread, h2 re-read from its row image
+      wait_d(0);   // D6
+#pragma unroll 1
+      for (int g = 0; g < 4; ++g) {
+        const int c0 = 64 * h + 16 * g;
+        float y[16];
+        img_load16(img_ptr(h2_t, F_H2, r, c0), y);
+        uint32_t d[16];
+        tc::tmem_ld16(t0 + C_D6 + c0, d);
+        tc::tmem_wait_ld();
+        float dz[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) dz[j] = __uint_as_float(d[j]) * elu_grad_from_out(y[j]);
+        tmem_put16(t0 + C_A7H + c0, t0 + C_A7L + c0, dz);
+        img_store16(img_ptr(dzh2_t, F_DZH2, r, c0), dz);
+      }
+      arrive_a(0);   // -> D7
+      // ---- dZh1 = (dZh2 * W2) .* ELU'(h1): chunks c of 64 features, 32 per thread; image only
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        if (c == 0) wait_d(0);
+        if (c == 2) wait_d(1);
+#pragma unroll 1
+        for (int g = 0; g < 2; ++g) {
+          const int c0 = c * CH + 32 * h + 16 * g;
+          float y[16];
+          img_load16(img_ptr(h1_t, F_H1, r, c0), y);
+          uint32_t d[16];
+          tc::tmem_ld16(t0 + C_D7 + c0, d);
+          tc::tmem_wait_ld();
+          float dz[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) dz[j] = __uint_as_float(d[j]) * elu_grad_from_out(y[j]);
+          img_store16(img_ptr(dzh1_t, F_DZH1, r, c0), dz);
+        }
+      }
+      tc::tc_fence_before();
+    }
+    // ---- loss partials of this CTA
+    surr_sum = warp_sum(surr_sum);
+    sl1_sum = warp_sum(sl1_sum);
+    if (lane == 0) { s_red[warp][0] = surr_sum; s_red[warp][1] = sl1_sum; }
+    epi_bar_sync();
+    if (threadIdx.x == 0) {
+      float x = 0.0f, y = 0.0f;
+      for (int i = 0; i < EPI_WARPS; ++i) { x += s_red[i][0]; y += s_red[i][1]; }
+      ga.loss_part[blockIdx.x * 2 + 0] = x;
+      ga.loss_part[blockIdx.x * 2 + 1] = y;
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == MMA_WARP) tc::tmem_dealloc(tb, 512);
+}
+
+// ================================================================================================ weight gradients
+// One "pair" = one layer's dW = dZ^T X:  A = dZ image (MA features -> D lanes), B = X image (NB features -> columns).
+constexpr int DW_KG = 2;                       // k-steps (of 8 rows) per pipeline stage
+constexpr int DW_RAW_SLOTS = 3, DW_OP_SLOTS = 2;
+constexpr int DW_TRANS_WARPS = 8, DW_THREADS = (2 + DW_TRANS_WARPS) * 32;
+constexpr int DW_MAX_FEATS = 384;              // MA + NB of the widest pair (dZh2 128 + h1 256)
+constexpr uint32_t DW_RAW_SLOT = DW_KG * DW_MAX_FEATS * 32;               // 24576 B
+// operand stage: per k-step and operand [hi plane | lo plane], plane = 2 K-chunks x (F * 16 + 16) bytes
+__host__ __device__ constexpr uint32_t dw_plane_bytes(int F) { return 2u * ((uint32_t)F * 16u + 16u); }
+constexpr uint32_t DW_OP_SLOT = DW_KG * 2 * (dw_plane_bytes(128) + dw_plane_bytes(256)) + 4096;   // + over-read slack
+
+struct DwPair {
+  const float* a_img;   // dZ row images
+  const float* b_img;   // X row images
+  int MA, NB;           // features
+  int mhalves;          // MA / 128 (1 or 2); MA = 64 runs as one M = 128 MMA whose lanes >= 64 are ignored
+  uint32_t d_col[2];    // accumulator columns per M half
+  uint32_t bias_col[2]; // 16-column bias accumulators
+};
+struct DwRole {
+  DwPair pair[2];
+};
+struct DwArgs {
+  DwRole role[2];
+  long long ntiles;
+  int ctas_per_role;
+  float* dw_part;       // [ctas_per_role][net.total]
+  int net_total;
+  int off[12];
+  int A;
+};
+
+__global__ void __launch_bounds__(DW_THREADS, 1)
+ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t pad = (1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u;
+  unsigned char* base = smem_raw + pad;
+  unsigned char* raw = base;                                       // DW_RAW_SLOTS x DW_RAW_SLOT
+  unsigned char* ops = raw + DW_RAW_SLOTS * DW_RAW_SLOT;           // DW_OP_SLOTS x DW_OP_SLOT
+  float* ones = reinterpret_cast<float*>(ops + DW_OP_SLOTS * DW_OP_SLOT);   // K-major [2 chunks][16 feats][4 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ones + 128);
+  uint64_t* raw_full = bars;
+  uint64_t* raw_empty = raw_full + DW_RAW_SLOTS;
+  uint64_t* op_full = raw_empty + DW_RAW_SLOTS;
+  uint64_t* op_empty = op_full + DW_OP_SLOTS;
+  uint64_t* acc_done = op_empty + DW_OP_SLOTS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_done + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int role_id = blockIdx.x & 1, ci = blockIdx.x >> 1;
+  const DwRole& role = a.role[role_id];
+  const long long my_tiles = (a.ntiles - ci + a.ctas_per_role - 1) / a.ctas_per_role;   // >= 1 by construction
+  const int stages_per_tile = 2 * (16 / DW_KG);                    // both pairs
+  const long long nstages = my_tiles * stages_per_tile;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < DW_RAW_SLOTS; ++i) {
+      tc::mbar_init(&raw_full[i], 1);
+      tc::mbar_init(&raw_empty[i], DW_TRANS_WARPS);
+    }
+    for (int i = 0; i < DW_OP_SLOTS; ++i) {
+      tc::mbar_init(&op_full[i], DW_TRANS_WARPS);
+      tc::mbar_init(&op_empty[i], 1);
+    }
+    tc::mbar_init(acc_done, 1);
+    tc::fence_mbar_init();
+  }
+  for (int i = threadIdx.x; i < 128; i += DW_THREADS) ones[i] = ((i & 63) < 4) ? 1.0f : 0.0f;   // feature 0, all 8 rows
+  tc::fence_proxy_async();
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tb = *tmem_slot;
+
+  if (warp == 0) {
+    // =========================================================================== TMA producer
+    if (tc::elect_one()) {
+      for (long long st = 0; st < nstages; ++st) {
+        const long long lt = st / stages_per_tile;
+        const int within = (int)(st - lt * stages_per_tile);
+        const int pi = within / (16 / DW_KG), kg = within - pi * (16 / DW_KG);
+        const DwPair& p = role.pair[pi];
+        const long long tile = ci + lt * a.ctas_per_role;
+        const uint32_t slot = (uint32_t)(st % DW_RAW_SLOTS);
+        const uint32_t use = (uint32_t)(st / DW_RAW_SLOTS);
+        tc::mbar_wait_relaxed(&raw_empty[slot], (use & 1u) ^ 1u);
+        const uint32_t a_bytes = (uint32_t)DW_KG * p.MA * 32u, b_bytes = (uint32_t)DW_KG * p.NB * 32u;
+        tc::mbar_arrive_expect_tx(&raw_full[slot], a_bytes + b_bytes);
+        unsigned char* dst = raw + slot * DW_RAW_SLOT;
+        const float* ga = p.a_img + (size_t)tile * TM * p.MA + (size_t)kg * DW_KG * p.MA * 8;
+        const float* gb = p.b_img + (size_t)tile * TM * p.NB + (size_t)kg * DW_KG * p.NB * 8;
+        tc::tma_load_1d(dst, ga, a_bytes, &raw_full[slot]);
+        tc::tma_load_1d(dst + a_bytes, gb, b_bytes, &raw_full[slot]);
+      }
+    }
+  } else if (warp == 1) {
+    // =========================================================================== MMA issuer
+    const uint32_t leader = tc::elect_one() ? 1u : 0u;
+    const uint32_t ones_addr = tc::smem_u32(ones);
+    const uint64_t ones_desc = tc::umma_smem_desc(ones_addr, 256u, 128u);
+    for (long long st = 0; st < nstages; ++st) {
+      const long long lt = st / stages_per_tile;
+      const int within = (int)(st - lt * stages_per_tile);
+      const int pi = within / (16 / DW_KG);
+      const DwPair& p = role.pair[pi];
+      const uint32_t slot = (uint32_t)(st % DW_OP_SLOTS);
+      const uint32_t use = (uint32_t)(st / DW_OP_SLOTS);
+      tc::mbar_wait(&op_full[slot], use & 1u);
+      tc::tc_fence_after();
+      const uint32_t pa_b = dw_plane_bytes(p.MA), pb_b = dw_plane_bytes(p.NB);
+      const uint32_t a_lbo = (uint32_t)p.MA * 16u + 16u, b_lbo = (uint32_t)p.NB * 16u + 16u;
+      const uint32_t sbase = tc::smem_u32(ops) + slot * DW_OP_SLOT;
+      const uint32_t idesc = tc::umma_idesc_tf32(p.NB), idesc1 = tc::umma_idesc_tf32(16);
+      const bool first_stage_of_pair = (lt == 0) && (within % (16 / DW_KG) == 0);
+#pragma unroll
+      for (int j = 0; j < DW_KG; ++j) {
+        const uint32_t a_hi = sbase + (uint32_t)j * 2u * (pa_b + pb_b), a_lo = a_hi + pa_b;
+        const uint32_t b_hi = a_lo + pa_b, b_lo = b_hi + pb_b;
+        const uint64_t bd_hi = tc::umma_smem_desc(b_hi, b_lbo, 128u), bd_lo = tc::umma_smem_desc(b_lo, b_lbo, 128u);
+        const uint32_t acc0 = (first_stage_of_pair && j == 0) ? 0u : 1u;
+        for (int mh = 0; mh < p.mhalves; ++mh) {
+          const uint64_t ad_hi = tc::umma_smem_desc(a_hi + (uint32_t)mh * 2048u, a_lbo, 128u);
+          const uint64_t ad_lo = tc::umma_smem_desc(a_lo + (uint32_t)mh * 2048u, a_lbo, 128u);
+          umma_ss_if(leader, tb + p.d_col[mh], ad_lo, bd_hi, idesc, acc0);
+          umma_ss_if(leader, tb + p.d_col[mh], ad_hi, bd_lo, idesc, 1u);
+          umma_ss_if(leader, tb + p.d_col[mh], ad_hi, bd_hi, idesc, 1u);
+          umma_ss_if(leader, tb + p.bias_col[mh], ad_lo, ones_desc, idesc1, acc0);
+          umma_ss_if(leader, tb + p.bias_col[mh], ad_hi, ones_desc, idesc1, 1u);
+        }
+      }
+      umma_commit_if(leader, &op_empty[slot]);
+    }
+    umma_commit_if(leader, acc_done);
+  } else {
+    // =========================================================================== transposers, then flush
+    const int tw = warp - 2;
+    const int tid = tw * 32 + lane;   // 0..255
+    for (long long st = 0; st < nstages; ++st) {
+      const long long lt = st / stages_per_tile;
+      const int within = (int)(st - lt * stages_per_tile);
+      const int pi = within / (16 / DW_KG);
+      const DwPair& p = role.pair[pi];
+      const uint32_t rslot = (uint32_t)(st % DW_RAW_SLOTS), ruse = (uint32_t)(st / DW_RAW_SLOTS);
+      const uint32_t oslot = (uint32_t)(st % DW_OP_SLOTS), ouse = (uint32_t)(st / DW_OP_SLOTS);
+      tc::mbar_wait(&raw_full[rslot], ruse & 1u);
+      tc::mbar_wait(&op_empty[oslot], (ouse & 1u) ^ 1u);
+      tc::tc_fence_after();
+      const float* rsrc = reinterpret_cast<const float*>(raw + rslot * DW_RAW_SLOT);
+      unsigned char* odst = ops + oslot * DW_OP_SLOT;
+      const uint32_t pa_b = dw_plane_bytes(p.MA), pb_b = dw_plane_bytes(p.NB);
+      // raw stage: [A: DW_KG x (MA/4) x 8 rows x 4] [B: DW_KG x (NB/4) x 8 x 4]; one float4 = (k-step j, group g, row r8)
+      const int a_chunks = DW_KG * (p.MA / 4) * 8, b_chunks = DW_KG * (p.NB / 4) * 8;
+      for (int i = tid; i < a_chunks + b_chunks; i += DW_TRANS_WARPS * 32) {
+        const bool is_b = i >= a_chunks;
+        const int ii = is_b ? i - a_chunks : i;
+        const int F = is_b ? p.NB : p.MA;
+        const int per_k = (F / 4) * 8;
+        const int j = ii / per_k, rem = ii - j * per_k;
+        const int g = rem >> 3, r8 = rem & 7;
+        const float4 v = reinterpret_cast<const float4*>(rsrc)[i];
+        // K-major operand: plane[(chunk = r8 >> 2)][feature][r8 & 3], chunk stride F*16 + 16 bytes
+        unsigned char* kbase = odst + (size_t)j * 2u * (pa_b + pb_b) + (is_b ? 2u * pa_b : 0u);
+        const uint32_t plane = is_b ? pb_b : pa_b;
+        float* hi_p = reinterpret_cast<float*>(kbase + (r8 >> 2) * (F * 16 + 16)) + (r8 & 3);
+        float* lo_p = reinterpret_cast<float*>(kbase + plane + (r8 >> 2) * (F * 16 + 16)) + (r8 & 3);
+        const float xs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          uint32_t hi, lo;
+          split_fast(xs[e], hi, lo);
+          hi_p[(4 * g + e) * 4] = __uint_as_float(hi);
+          lo_p[(4 * g + e) * 4] = __uint_as_float(lo);
+        }
+      }
+      tc::fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        tc::mbar_arrive(&raw_empty[rslot]);
+        tc::mbar_arrive(&op_full[oslot]);
+      }
+    }
+    // ---- flush the accumulators of this CTA to its partial: lane = output row (feature of dZ)
+    tc::mbar_wait(acc_done, 0u);
+    tc::tc_fence_after();
+    {
+      const int q = warp & 3;                 // TMEM lane quarter this warp may read
+      const int hsel = tw >> 2;               // two warps per quarter: split the columns
+      const int m = q * 32 + lane;
+      const uint32_t t0 = tc::tmem_addr(tb, (uint32_t)q * 32u, 0);
+      float* out = a.dw_part + (size_t)ci * a.net_total;
+      auto dump = [&](uint32_t col0, int ncols, float* dst_row, int col_lo, int col_hi) {
+        // writes columns [col_lo, col_hi) of the accumulator row to dst_row[col - col_lo]; this warp takes every
+        // other 16-column block
+        for (int c = 16 * hsel; c < ncols; c += 32) {
+          uint32_t v[16];
+          tc::tmem_ld16(t0 + col0 + c, v);
+          tc::tmem_wait_ld();
+          if (dst_row != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (c + j >= col_lo && c + j < col_hi) dst_row[c + j - col_lo] = __uint_as_float(v[j]);
+          }
+        }
+      };
+      auto bias_val = [&](uint32_t col0) {
+        uint32_t v[16];
+        tc::tmem_ld16(t0 + col0, v);
+        tc::tmem_wait_ld();
+        return __uint_as_float(v[0]);
+      };
+      if (role_id == 0) {
+        {   // layer 2: dW2[m][n] (128 x 256), db2[m]
+          const DwPair& p = role.pair[0];
+          dump(p.d_col[0], 256, out + a.off[2] + (size_t)m * 256, 0, 256);
+          const float b = bias_val(p.bias_col[0]);
+          if (hsel == 0) out[a.off[3] + m] = b;
+        }
+        {   // layer 4: lanes [0,A) = to_mean.2 rows over m1 columns [0,64); lane 32 = to_value.2 over v1 columns [64,128)
+          const DwPair& p = role.pair[1];
+          float* dst = nullptr;
+          int lo = 0, hi = 0;
+          if (m < a.A) { dst = out + a.off[6] + (size_t)m * 64; lo = 0; hi = 64; }
+          else if (m == 32) { dst = out + a.off[10]; lo = 64; hi = 128; }
+          dump(p.d_col[0], 128, dst, lo, hi);
+          const float b = bias_val(p.bias_col[0]);
+          if (hsel == 0) {
+            if (m < a.A) out[a.off[7] + m] = b;
+            else if (m == 32) out[a.off[11]] = b;
+          }
+        }
+      } else {
+        {   // layer 1: dW1[128 mh + m][n] (256 x 80), db1
+          const DwPair& p = role.pair[0];
+          for (int mh = 0; mh < 2; ++mh) {
+            // 80 columns = 5 blocks of 16: alternate blocks between the two warps of the quarter
+            dump(p.d_col[mh], 80, out + a.off[0] + (size_t)(128 * mh + m) * 80, 0, 80);
+            const float b = bias_val(p.bias_col[mh]);
+            if (hsel == 0) out[a.off[1] + 128 * mh + m] = b;
+          }
+        }
+        {   // layer 3: lanes [0,64) = to_mean.0 rows, lanes [64,128) = to_value.0 rows, 128 columns (h2)
+          const DwPair& p = role.pair[1];
+          float* dst = (m < 64) ? out + a.off[4] + (size_t)m * 128 : out + a.off[8] + (size_t)(m - 64) * 128;
+          dump(p.d_col[0], 128, dst, 0, 128);
+          const float b = bias_val(p.bias_col[0]);
+          if (hsel == 0) {
+            if (m < 64) out[a.off[5] + m] = b;
+            else out[a.off[9] + m - 64] = b;
+          }
+        }
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc(tb, 512);
+}
+
+// grad = sum of the per-CTA partials (fixed order); entries outside the 12 parameter tensors (alignment padding) = 0
+struct ReduceArgs {
+  int off[12], size[12];
+  int total, nparts, nloss;
+  float inv_rows;
+};
+__global__ void __launch_bounds__(256)
+ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restrict__ dw_part,
+                     const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < a.total) {
+    bool valid = false;
+#pragma unroll
+    for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= a.off[sg] && i < a.off[sg] + a.size[sg]);
+    float g = 0.0f;
+    if (valid)
+      for (int p = 0; p < a.nparts; ++p) g += dw_part[(size_t)p * a.total + i];
+    grad[i] = g;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
+    float x = 0.0f, y = 0.0f;
+    for (int t = threadIdx.x; t < a.nloss; t += 32) {
+      x += loss_part[t * 2 + 0];
+      y += loss_part[t * 2 + 1];
+    }
+    x = warp_sum(x);
+    y = warp_sum(y);
+    if (threadIdx.x == 0) *loss = -x * a.inv_rows + y * a.inv_rows;
+  }
+}
+
+struct Ws {
+  float* norm_part;   // first slot, shared with flyb_ppo_apply
+  Images im;
+  float* loss_part;
+  float* dw_part;
+  int grid1, ctas_per_role;
+  size_t bytes;
+};
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+static Ws carve_ws(const FlybNetLayout& net, long long rows, void* basep) {
+  Ws w{};
+  char* p = (char*)basep;
+  size_t off = 0;
+  auto take = [&](size_t nfloats) {
+    float* r = (float*)(p + off);
+    off += align_up(nfloats * sizeof(float), 256);
+    return r;
+  };
+  const long long ntiles = (rows + TM - 1) / TM;
+  const size_t R = (size_t)ntiles * TM;
+  const int sms = num_sms();
+  w.grid1 = (int)std::min<long long>(ntiles, sms);
+  w.ctas_per_role = (int)std::max<long long>(1, std::min<long long>(ntiles, sms / 2));
+  w.norm_part = take(64);
+  w.im.x = take(R * F_X); w.im.h1 = take(R * F_H1); w.im.h2 = take(R * F_H2); w.im.mv = take(R * F_MV);
+  w.im.dzmuv = take(R * F_DZMUV + 4096);   // + slack: the M = 128 MMA of the 64-feature operand never reads it, TMA does not either
+  w.im.dzmv = take(R * F_DZMV); w.im.dzh2 = take(R * F_DZH2); w.im.dzh1 = take(R * F_DZH1);
+  w.loss_part = take((size_t)sms * 2 + 64);
+  w.dw_part = take((size_t)w.ctas_per_role * net.total);
+  w.bytes = off;
+  return w;
+}
+
+}  // namespace tcb
+
+size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows) {
+  if (!tc_supported(net)) return 0;
+  return tcb::carve_ws(*net, rows, nullptr).bytes;
+}
+
+int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
+                const float* obs, const float* action, const float* old_logp, const float* target,
+                const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
+                void* workspace, cudaStream_t st) {
+  using namespace tcb;
+  const Ws w = carve_ws(*net, rows, workspace);
+  const long long ntiles = (rows + TM - 1) / TM;
+  FwdArgs fa{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, 0, nullptr};
+  GradArgs ga{};
+  ga.action = action; ga.old_logp = old_logp; ga.target = target; ga.advantage = advantage; ga.action_var = action_var;
+  ga.clip_lo = (float)(1.0 - cfg->clip);
+  ga.clip_hi = (float)(1.0 + cfg->clip);
+  ga.inv_rows = 1.0f / (float)rows;
+  ga.loss_part = w.loss_part;
+  const size_t smem1 = smem_bytes(net->num_obs, 0);
+  int rc;
+  if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_fwd_bwd_tc_kernel), smem1)) != FLYB_OK) return rc;
+  ppo_fwd_bwd_tc_kernel<<<w.grid1, THREADS, smem1, st>>>(*net, fa, ga, w.im);
+  FLYB_LAUNCH_CHECK("ppo_fwd_bwd_tc_kernel");
+
+  DwArgs d{};
+  // role 0: layer 2 (dZh2 x h1) and layer 4 ([dZmu|dZval] x [m1|v1]);  role 1: layer 1 (dZh1 x X), layer 3 ([dZm1|dZv1] x h2)
+  d.role[0].pair[0] = DwPair{w.im.dzh2, w.im.h1, F_DZH2, F_H1, 1, {0u, 0u}, {256u, 256u}};
+  d.role[0].pair[1] = DwPair{w.im.dzmuv, w.im.mv, F_DZMUV, F_MV, 1, {288u, 288u}, {416u, 416u}};
+  d.role[1].pair[0] = DwPair{w.im.dzh1, w.im.x, F_DZH1, F_X, 2, {0u, 96u}, {192u, 208u}};
+  d.role[1].pair[1] = DwPair{w.im.dzmv, w.im.h2, F_DZMV, F_H2, 1, {256u, 256u}, {384u, 384u}};
+  d.ntiles = ntiles;
+  d.ctas_per_role = w.ctas_per_role;
+  d.dw_part = w.dw_part;
+  d.net_total = net->total;
+  for (int i = 0; i < 12; ++i) d.off[i] = net->off[i];
+  d.A = net->num_act;
+  const size_t smem2 = 1024 + (size_t)DW_RAW_SLOTS * DW_RAW_SLOT + (size_t)DW_OP_SLOTS * DW_OP_SLOT + 512 + 256;
+  if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel), smem2)) != FLYB_OK) return rc;
+  ppo_dw_tc_kernel<<<2 * w.ctas_per_role, DW_THREADS, smem2, st>>>(d);
+  FLYB_LAUNCH_CHECK("ppo_dw_tc_kernel");
+
+  ReduceArgs r{};
+  const int A = net->num_act;
+  const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
+  for (int i = 0; i < 12; ++i) { r.off[i] = net->off[i]; r.size[i] = sizes[i]; }
+  r.total = net->total; r.nparts = w.ctas_per_role; r.nloss = w.grid1; r.inv_rows = ga.inv_rows;
+  ppo_reduce_tc_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss);
+  FLYB_LAUNCH_CHECK("ppo_reduce_tc_kernel");
+  return FLYB_OK;
+}
+
+}  // namespace flyb

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FLYB_ABI_VERSION 2
+#define FLYB_ABI_VERSION 3
 #define FLYB_MAX_DOF 64      /* asset DOF count D: 18 (nmf_no_limits_limited_Dofs.urdf) or 42 (nmf_no_limits.urdf) */
 #define FLYB_NUM_ABDOMEN 5   /* reference fly.py:299 */
 #define FLYB_NUM_LEGTIPS 6   /* reference fly.py:300 */
@@ -168,7 +168,9 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
 
 /* ---- agent, kernel (d): one optimiser step of reference PPO.update (ppo.py:183-199), split where a
  *      data-parallel run all-reduces:  flyb_ppo_grad -> [all-reduce(grad)/world] -> flyb_ppo_apply.
- * flyb_ppo_grad: forward, clipped-surrogate + SmoothL1 loss, backward.  obs (rows,O), action (rows,A),
+ * flyb_ppo_grad: forward, clipped-surrogate + SmoothL1 loss, backward.  wpack (nullable): packed weight stream of
+ *   the CURRENT params -> tcgen05 3xTF32 forward/backward/weight-gradient GEMMs; NULL -> exact-fp32 CUDA cores.
+ *   obs (rows,O), action (rows,A),
  *   old_logp/target/advantage (rows).  Out: grad (net->total) = d(loss.mean())/d(params) over THESE rows,
  *   loss (1).  workspace: flyb_ppo_workspace_bytes(net, rows) bytes.
  * flyb_ppo_apply: grad *= grad_scale; clip_grad_norm_(max_grad_norm) with torch's coefficient
@@ -176,9 +178,10 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  *   grad_norm_out (1) nullable.  workspace: the flyb_ppo_grad workspace (only its first 256 bytes are used).
  *   wpack (nullable): re-packed from the updated parameters in the same call. */
 size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t rows);
-int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const float* obs,
-                  const float* action, const float* old_logp, const float* target, const float* advantage,
-                  const float* action_var, int64_t rows, float* grad, float* loss, void* workspace, void* stream);
+int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
+                  const float* obs, const float* action, const float* old_logp, const float* target,
+                  const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
+                  void* workspace, void* stream);
 int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad, float* exp_avg,
                    float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out, void* workspace,
                    void* wpack, void* stream);

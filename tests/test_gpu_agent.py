@@ -195,7 +195,7 @@ def _grad_step(net, g, k, j, var):
     # keep the device copies alive until the launch has finished
     dv = [x.contiguous().to(DEV) for x in (g["roll_obs"][k:j], g["roll_acts"][k:j], g["roll_logp"][k:j],
                                            g["roll_target"][k:j], g["roll_adv"][k:j], var)]
-    _lib.check(lib.flyb_ppo_grad(C.byref(net.layout), C.byref(cfg), p(net.flat), p(dv[0]), p(dv[1]), p(dv[2]),
+    _lib.check(lib.flyb_ppo_grad(C.byref(net.layout), C.byref(cfg), p(net.flat), p(net.wpack), p(dv[0]), p(dv[1]), p(dv[2]),
                                  p(dv[3]), p(dv[4]), p(dv[5]), rows, p(grad), p(loss), wsp, _lib.current_stream()))
     torch.cuda.synchronize()
     return grad, loss, ws, wsp, cfg
