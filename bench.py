@@ -41,6 +41,7 @@ FLOPS_ACT = 2 * (O * 256 + 256 * 128 + 128 * 64 + 64 * A)                       
 BYTES_ACT = 4 * O + 4 * A + 4 + 4 * D + 4 * A                                                           # obs read + action/logp/targets/scaled
 FLOPS_UPDATE = 6 * (O * 256 + 256 * 128 + 128 * 64 + 64 * A + 128 * 64 + 64)                            # 414 336 per sample
 BYTES_GAE = 20
+MMA_KIND = "tcgen05 kind::tf32, 3xTF32 (hi*lo + lo*hi + hi*hi), fp32 accumulate in TMEM"
 
 
 def peaks():
@@ -194,6 +195,29 @@ def cuda_time_ms(fn, iters, stream=None):
     return e0.elapsed_time(e1) / iters
 
 
+def graph_time_ms(fn, iters, replays=5):
+    """Device time per launch of `fn`: `iters` launches captured into ONE CUDA graph (so the host's launch rate —
+    a ctypes call costs more than some of these kernels run — is out of the picture), replayed `replays` times after
+    a warm-up replay, CUDA events on the capturing stream around the replays."""
+    import torch
+    for i in range(min(iters, 4)):
+        fn(i)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(iters):
+            fn(i)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(replays):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (iters * replays)
+
+
 def run_own(args):
     import torch
     import torch.distributed as dist
@@ -297,11 +321,20 @@ def run_own(args):
     def k_grad(i):
         agent._minibatch(0, agent.mini_chunk_size)
 
+    def k_gradonly(i):
+        lay = C.byref(agent.net.layout)
+        _lib.check(agent.lib.flyb_ppo_grad(
+            lay, C.byref(agent.ppo_cfg), p(agent.net.flat), p(agent.net.wpack), p(agent._obs_ring[0:agent.mini_chunk_size]),
+            p(agent.all_acts[0:agent.mini_chunk_size]), p(agent.all_log_prob[0:agent.mini_chunk_size]),
+            p(agent._target[0:agent.mini_chunk_size]), p(agent.all_advantage[0:agent.mini_chunk_size]),
+            p(agent.action_var), agent.mini_chunk_size * NUM_ENVS, p(agent.grad), p(agent.loss), agent._ws_ptr,
+            _lib.current_stream()))
+
     kt = {}
-    for name, fn, iters in [("post_physics", k_env, 64), ("policy_act", k_act, 64), ("gae_scan", k_gae, 32),
-                            ("value_forward", k_vfwd, 8), ("ppo_minibatch_step", k_grad, 8)]:
-        fn(0)
-        kt[name] = cuda_time_ms(fn, iters)
+    for name, fn, iters in [("post_physics", k_env, 4 * POOL), ("policy_act", k_act, 4 * POOL), ("gae_scan", k_gae, 32),
+                            ("value_forward", k_vfwd, 4), ("ppo_grad", k_gradonly, 8),
+                            ("ppo_minibatch_step", k_grad, 8)]:
+        kt[name] = graph_time_ms(fn, iters)
     rows_mb = agent.mini_chunk_size * NUM_ENVS
     kernels = {
         "post_physics": {"ms": kt["post_physics"], "bound": "hbm",
@@ -309,21 +342,33 @@ def run_own(args):
                          "peak": pk["hbm"]},
         "policy_act": {"ms": kt["policy_act"], "bound": "tensor",
                        "achieved": FLOPS_ACT * NUM_ENVS / kt["policy_act"] / 1e9, "unit": "TFLOP/s",
-                       "peak": pk["tf_sustained"], "mma_kind": "fp32 CUDA cores (exact-fp32 path)"},
+                       "peak": pk["tf_sustained"], "mma_kind": MMA_KIND},
         "gae_scan": {"ms": kt["gae_scan"], "bound": "hbm",
                      "achieved": BYTES_GAE * NUM_ENVS * HORIZON / kt["gae_scan"] / 1e6, "unit": "GB/s", "peak": pk["hbm"]},
         "value_forward": {"ms": kt["value_forward"], "bound": "tensor",
                           "achieved": 2 * (O * 256 + 256 * 128 + 128 * 64 + 64) * (HORIZON + 1) * NUM_ENVS /
-                          kt["value_forward"] / 1e9, "unit": "TFLOP/s", "peak": pk["tf_sustained"]},
+                          kt["value_forward"] / 1e9, "unit": "TFLOP/s", "peak": pk["tf_sustained"], "mma_kind": MMA_KIND},
+        "ppo_grad": {"ms": kt["ppo_grad"], "bound": "tensor",
+                     "achieved": FLOPS_UPDATE * rows_mb / kt["ppo_grad"] / 1e9, "unit": "TFLOP/s",
+                     "peak": pk["tf_sustained"], "mma_kind": MMA_KIND,
+                     "note": "fwd+bwd chain kernel + weight-gradient kernel + partial reduce"},
         "ppo_minibatch_step": {"ms": kt["ppo_minibatch_step"], "bound": "tensor",
                                "achieved": FLOPS_UPDATE * rows_mb / kt["ppo_minibatch_step"] / 1e9, "unit": "TFLOP/s",
-                               "peak": pk["tf_sustained"]},
+                               "peak": pk["tf_sustained"], "mma_kind": MMA_KIND,
+                               "note": "ppo_grad + norm + clip/Adam + weight re-pack"},
     }
     for k in kernels.values():
         k["frac"] = k["achieved"] / k["peak"]
+        if k["bound"] == "tensor":   # 3xTF32: TF32 runs at half the bf16 rate and every product takes 3 MMAs
+            k["kind_peak"] = k["peak"] / 6.0
+            k["frac_of_kind_peak"] = k["achieved"] / k["kind_peak"]
+    traffic = {}
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath))
     dom = "policy_act" if kt["policy_act"] >= kt["post_physics"] else "post_physics"
     roofline = dict(kernels[dom])
-    roofline.update({"kernel": dom, "traffic": None,
+    roofline.update({"kernel": dom, "traffic": traffic.get(dom),
                      "peak_source": pk["tf_src" if roofline["bound"] == "tensor" else "hbm_src"] +
                      (" (sustained: timed inside a long step)" if roofline["bound"] == "tensor" else "")})
     roofline.pop("ms", None)
@@ -357,7 +402,7 @@ def run_own(args):
         e2e_step(i)
     ke = 4 * HORIZON
     barrier()
-    e2e_ms = max_over_ranks(cuda_time_ms(e2e_step, ke) * ke)
+    e2e_ms = max_over_ranks(cuda_time_ms(e2e_step, ke) * ke)   # eager on purpose: the user-facing call, host in the loop
     h2d_bytes = sum(v.numel() * v.element_size() for v in live.values())
     d2h_bytes = host_reward.numel() * 4 + 4
     e2e_value = NUM_ENVS * ke * world / (e2e_ms * 1e-3)

@@ -431,40 +431,59 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
         img_store16(img_ptr(dzmv_t, F_DZMV, r, c0), dz);
       }
       arrive_a(0);   // -> D6
-      // ---- dZh2 = (dZm1 * W3pi + dZv1 * W3v) .* ELU'(h2): 64 columns per thread, h2 re-read from its row image
-      wait_d(0);   // D6
-#pragma unroll 1
-      for (int g = 0; g < 4; ++g) {
-        const int c0 = 64 * h + 16 * g;
-        float y[16];
-        img_load16(img_ptr(h2_t, F_H2, r, c0), y);
-        uint32_t d[16];
-        tc::tmem_ld16(t0 + C_D6 + c0, d);
-        tc::tmem_wait_ld();
-        float dz[16];
+      // ---- dZh2 = (dZm1 * W3pi + dZv1 * W3v) .* ELU'(h2): 64 columns per thread; h2 is re-read from its row image
+      //      (written by this same thread) BEFORE the accumulator is waited for, so the loads fly during the MMAs
+      {
+        float y2[4][16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) dz[j] = __uint_as_float(d[j]) * elu_grad_from_out(y[j]);
-        tmem_put16(t0 + C_A7H + c0, t0 + C_A7L + c0, dz);
-        img_store16(img_ptr(dzh2_t, F_DZH2, r, c0), dz);
-      }
-      arrive_a(0);   // -> D7
-      // ---- dZh1 = (dZh2 * W2) .* ELU'(h1): chunks c of 64 features, 32 per thread; image only
-#pragma unroll 1
-      for (int c = 0; c < NCH; ++c) {
-        if (c == 0) wait_d(0);
-        if (c == 2) wait_d(1);
-#pragma unroll 1
-        for (int g = 0; g < 2; ++g) {
-          const int c0 = c * CH + 32 * h + 16 * g;
-          float y[16];
-          img_load16(img_ptr(h1_t, F_H1, r, c0), y);
+        for (int g = 0; g < 4; ++g) img_load16(img_ptr(h2_t, F_H2, r, 64 * h + 16 * g), y2[g]);
+        wait_d(0);   // D6
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int c0 = 64 * h + 16 * g;
           uint32_t d[16];
-          tc::tmem_ld16(t0 + C_D7 + c0, d);
+          tc::tmem_ld16(t0 + C_D6 + c0, d);
           tc::tmem_wait_ld();
           float dz[16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) dz[j] = __uint_as_float(d[j]) * elu_grad_from_out(y[j]);
-          img_store16(img_ptr(dzh1_t, F_DZH1, r, c0), dz);
+          for (int j = 0; j < 16; ++j) dz[j] = __uint_as_float(d[j]) * elu_grad_from_out(y2[g][j]);
+          tmem_put16(t0 + C_A7H + c0, t0 + C_A7L + c0, dz);
+          img_store16(img_ptr(dzh2_t, F_DZH2, r, c0), dz);
+        }
+      }
+      arrive_a(0);   // -> D7
+      // ---- dZh1 = (dZh2 * W2) .* ELU'(h1): chunks c of 64 features, 32 per thread; image only.  The h1 rows of
+      //      chunk c + 1 are fetched while chunk c is processed.
+      {
+        float yb[2][16];
+#pragma unroll
+        for (int g = 0; g < 2; ++g) img_load16(img_ptr(h1_t, F_H1, r, 32 * h + 16 * g), yb[g]);
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          if (c == 0) wait_d(0);
+          if (c == 2) wait_d(1);
+          float yn[2][16];
+          if (c + 1 < NCH) {
+#pragma unroll
+            for (int g = 0; g < 2; ++g) img_load16(img_ptr(h1_t, F_H1, r, (c + 1) * CH + 32 * h + 16 * g), yn[g]);
+          }
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            const int c0 = c * CH + 32 * h + 16 * g;
+            uint32_t d[16];
+            tc::tmem_ld16(t0 + C_D7 + c0, d);
+            tc::tmem_wait_ld();
+            float dz[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) dz[j] = __uint_as_float(d[j]) * elu_grad_from_out(yb[g][j]);
+            img_store16(img_ptr(dzh1_t, F_DZH1, r, c0), dz);
+          }
+          if (c + 1 < NCH) {
+#pragma unroll
+            for (int g = 0; g < 2; ++g)
+#pragma unroll
+              for (int j = 0; j < 16; ++j) yb[g][j] = yn[g][j];
+          }
         }
       }
       tc::tc_fence_before();
@@ -490,7 +509,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
 // ================================================================================================ weight gradients
 // One "pair" = one layer's dW = dZ^T X:  A = dZ image (MA features -> D lanes), B = X image (NB features -> columns).
 constexpr int DW_KG = 2;                       // k-steps (of 8 rows) per pipeline stage
-constexpr int DW_RAW_SLOTS = 3, DW_OP_SLOTS = 2;
+constexpr int DW_RAW_SLOTS = 4, DW_OP_SLOTS = 2;
 constexpr int DW_TRANS_WARPS = 8, DW_THREADS = (2 + DW_TRANS_WARPS) * 32;
 constexpr int DW_MAX_FEATS = 384;              // MA + NB of the widest pair (dZh2 128 + h1 256)
 constexpr uint32_t DW_RAW_SLOT = DW_KG * DW_MAX_FEATS * 32;               // 24576 B
@@ -639,28 +658,35 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
       unsigned char* odst = ops + oslot * DW_OP_SLOT;
       const uint32_t pa_b = dw_plane_bytes(p.MA), pb_b = dw_plane_bytes(p.NB);
       // raw stage: [A: DW_KG x (MA/4) x 8 rows x 4] [B: DW_KG x (NB/4) x 8 x 4]; one float4 = (k-step j, group g, row r8)
-      const int a_chunks = DW_KG * (p.MA / 4) * 8, b_chunks = DW_KG * (p.NB / 4) * 8;
-      for (int i = tid; i < a_chunks + b_chunks; i += DW_TRANS_WARPS * 32) {
-        const bool is_b = i >= a_chunks;
-        const int ii = is_b ? i - a_chunks : i;
-        const int F = is_b ? p.NB : p.MA;
-        const int per_k = (F / 4) * 8;
-        const int j = ii / per_k, rem = ii - j * per_k;
-        const int g = rem >> 3, r8 = rem & 7;
-        const float4 v = reinterpret_cast<const float4*>(rsrc)[i];
-        // K-major operand: plane[(chunk = r8 >> 2)][feature][r8 & 3], chunk stride F*16 + 16 bytes
-        unsigned char* kbase = odst + (size_t)j * 2u * (pa_b + pb_b) + (is_b ? 2u * pa_b : 0u);
-        const uint32_t plane = is_b ? pb_b : pa_b;
-        float* hi_p = reinterpret_cast<float*>(kbase + (r8 >> 2) * (F * 16 + 16)) + (r8 & 3);
-        float* lo_p = reinterpret_cast<float*>(kbase + plane + (r8 >> 2) * (F * 16 + 16)) + (r8 & 3);
-        const float xs[4] = {v.x, v.y, v.z, v.w};
+      static_assert(DW_KG == 2, "the k-step of a chunk is found by one compare");
+      const float4* src4 = reinterpret_cast<const float4*>(rsrc);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          uint32_t hi, lo;
-          split_fast(xs[e], hi, lo);
-          hi_p[(4 * g + e) * 4] = __uint_as_float(hi);
-          lo_p[(4 * g + e) * 4] = __uint_as_float(lo);
+      for (int op = 0; op < 2; ++op) {
+        const int F = op ? p.NB : p.MA;
+        const int per_k = F * 2;                       // float4 chunks of one k-step: (F / 4) groups x 8 rows
+        const uint32_t plane = op ? pb_b : pa_b;
+        const uint32_t cstride = (uint32_t)F * 16u + 16u;   // K-chunk stride inside a plane
+        unsigned char* obase = odst + (op ? 2u * pa_b : 0u);
+        for (int i = tid; i < DW_KG * per_k; i += DW_TRANS_WARPS * 32) {
+          const int j = i >= per_k ? 1 : 0;
+          const int rem = i - j * per_k;
+          const int g = rem >> 3, r8 = rem & 7;
+          const float4 v = src4[i];
+          // K-major operand: plane[(chunk = r8 >> 2)][feature][r8 & 3]
+          unsigned char* kbase = obase + (uint32_t)j * 2u * (pa_b + pb_b) + (uint32_t)(r8 >> 2) * cstride +
+                                 (uint32_t)g * 64u + (uint32_t)(r8 & 3) * 4u;
+          uint32_t hi[4], lo[4];
+          split_fast(v.x, hi[0], lo[0]);
+          split_fast(v.y, hi[1], lo[1]);
+          split_fast(v.z, hi[2], lo[2]);
+          split_fast(v.w, hi[3], lo[3]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            *reinterpret_cast<uint32_t*>(kbase + e * 16) = hi[e];
+            *reinterpret_cast<uint32_t*>(kbase + plane + e * 16) = lo[e];
+          }
         }
+        src4 += DW_KG * per_k;
       }
       tc::fence_proxy_async();
       __syncwarp();
@@ -752,19 +778,26 @@ struct ReduceArgs {
   int total, nparts, nloss;
   float inv_rows;
 };
-__global__ void __launch_bounds__(256)
+constexpr int RED_ELEMS = 64, RED_GROUPS = 4;   // 256 threads: 64 gradient entries x 4 interleaved partial groups
+__global__ void __launch_bounds__(RED_ELEMS * RED_GROUPS)
 ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restrict__ dw_part,
                      const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float s_acc[RED_GROUPS][RED_ELEMS];
+  const int e = threadIdx.x & (RED_ELEMS - 1), pg = threadIdx.x / RED_ELEMS;
+  const int i = blockIdx.x * RED_ELEMS + e;
+  float acc = 0.0f;
   if (i < a.total) {
     bool valid = false;
 #pragma unroll
     for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= a.off[sg] && i < a.off[sg] + a.size[sg]);
-    float g = 0.0f;
-    if (valid)
-      for (int p = 0; p < a.nparts; ++p) g += dw_part[(size_t)p * a.total + i];
-    grad[i] = g;
+    if (valid) {   // group pg sums partials pg, pg + 4, ... in order; the groups are combined in a fixed order below
+#pragma unroll 8
+      for (int p = pg; p < a.nparts; p += RED_GROUPS) acc += dw_part[(size_t)p * a.total + i];
+    }
   }
+  s_acc[pg][e] = acc;
+  __syncthreads();
+  if (pg == 0 && i < a.total) grad[i] = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
     float x = 0.0f, y = 0.0f;
     for (int t = threadIdx.x; t < a.nloss; t += 32) {
@@ -861,7 +894,7 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
   for (int i = 0; i < 12; ++i) { r.off[i] = net->off[i]; r.size[i] = sizes[i]; }
   r.total = net->total; r.nparts = w.ctas_per_role; r.nloss = w.grid1; r.inv_rows = ga.inv_rows;
-  ppo_reduce_tc_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss);
+  ppo_reduce_tc_kernel<<<(net->total + RED_ELEMS - 1) / RED_ELEMS, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss);
   FLYB_LAUNCH_CHECK("ppo_reduce_tc_kernel");
   return FLYB_OK;
 }
