@@ -232,6 +232,8 @@ def run_own(args):
     dev = f"cuda:{local}"
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO") and not os.environ.get("FLYB_KEEP_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL's banner goes to stdout: keep stdout to the ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device(dev))
     if args.gpus != world and rank == 0 and world > 1:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}", file=sys.stderr)
@@ -334,7 +336,11 @@ def run_own(args):
     for name, fn, iters in [("post_physics", k_env, 4 * POOL), ("policy_act", k_act, 4 * POOL), ("gae_scan", k_gae, 32),
                             ("value_forward", k_vfwd, 4), ("ppo_grad", k_gradonly, 8),
                             ("ppo_minibatch_step", k_grad, 8)]:
-        kt[name] = graph_time_ms(fn, iters)
+        if world > 1 and name == "ppo_minibatch_step":   # contains the NCCL all-reduce: timed eagerly, not captured
+            fn(0)
+            kt[name] = cuda_time_ms(fn, iters)
+        else:
+            kt[name] = graph_time_ms(fn, iters)
     rows_mb = agent.mini_chunk_size * NUM_ENVS
     kernels = {
         "post_physics": {"ms": kt["post_physics"], "bound": "hbm",

@@ -357,7 +357,9 @@ class PPO:
         return steps
 
     def update(self, use_graph: bool = False) -> None:
-        if not use_graph:
+        # data-parallel runs keep the NCCL all-reduce out of graph capture (the kernels are enqueued eagerly; the
+        # host stays ahead of the device because one optimiser step is ~170 us of GPU work)
+        if not use_graph or self.world_size > 1:
             self.optim_step += self._update_body()
             return
         g = self._graphs.get("update")

@@ -26,6 +26,7 @@
 //              A6 ([dZm1|dZv1]) hi [0,128) lo [128,256)      D6 (dH2) [384,512)
 //              A7 (dZh2) hi [0,128) lo [128,256)             D7 (dH1) [256,512)
 #include <algorithm>
+#include <cstdlib>
 
 #include "mlp_tc.cuh"
 
@@ -510,7 +511,8 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
 // One "pair" = one layer's dW = dZ^T X:  A = dZ image (MA features -> D lanes), B = X image (NB features -> columns).
 constexpr int DW_KG = 2;                       // k-steps (of 8 rows) per pipeline stage
 constexpr int DW_RAW_SLOTS = 4, DW_OP_SLOTS = 2;
-constexpr int DW_TRANS_WARPS = 8, DW_THREADS = (2 + DW_TRANS_WARPS) * 32;
+constexpr int DW_TRANS_WARPS = 16, DW_THREADS = (2 + DW_TRANS_WARPS) * 32;
+FLYB_D void dw_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(DW_TRANS_WARPS * 32) : "memory"); }
 constexpr int DW_MAX_FEATS = 384;              // MA + NB of the widest pair (dZh2 128 + h1 256)
 constexpr uint32_t DW_RAW_SLOT = DW_KG * DW_MAX_FEATS * 32;               // 24576 B
 // operand stage: per k-step and operand [hi plane | lo plane], plane = 2 K-chunks x (F * 16 + 16) bytes
@@ -536,6 +538,7 @@ struct DwArgs {
   int net_total;
   int off[12];
   int A;
+  int dbg;              // timing experiments only (FLYB_DW_DBG): 1 skip transposition, 2 skip MMAs, 4 skip flush
 };
 
 __global__ void __launch_bounds__(DW_THREADS, 1)
@@ -546,7 +549,8 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
   unsigned char* raw = base;                                       // DW_RAW_SLOTS x DW_RAW_SLOT
   unsigned char* ops = raw + DW_RAW_SLOTS * DW_RAW_SLOT;           // DW_OP_SLOTS x DW_OP_SLOT
   float* ones = reinterpret_cast<float*>(ops + DW_OP_SLOTS * DW_OP_SLOT);   // K-major [2 chunks][16 feats][4 rows]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ones + 128);
+  float* bias_s = ones + 128;                                              // [2 pairs][256 features]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + 512);
   uint64_t* raw_full = bars;
   uint64_t* raw_empty = raw_full + DW_RAW_SLOTS;
   uint64_t* op_full = raw_empty + DW_RAW_SLOTS;
@@ -584,15 +588,13 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
   if (warp == 0) {
     // =========================================================================== TMA producer
     if (tc::elect_one()) {
+      uint32_t slot = 0, phase = 0;
+      int within = 0;
+      long long tile = ci;
       for (long long st = 0; st < nstages; ++st) {
-        const long long lt = st / stages_per_tile;
-        const int within = (int)(st - lt * stages_per_tile);
-        const int pi = within / (16 / DW_KG), kg = within - pi * (16 / DW_KG);
+        const int pi = within >= (16 / DW_KG) ? 1 : 0, kg = within - pi * (16 / DW_KG);
         const DwPair& p = role.pair[pi];
-        const long long tile = ci + lt * a.ctas_per_role;
-        const uint32_t slot = (uint32_t)(st % DW_RAW_SLOTS);
-        const uint32_t use = (uint32_t)(st / DW_RAW_SLOTS);
-        tc::mbar_wait_relaxed(&raw_empty[slot], (use & 1u) ^ 1u);
+        tc::mbar_wait_relaxed(&raw_empty[slot], phase ^ 1u);
         const uint32_t a_bytes = (uint32_t)DW_KG * p.MA * 32u, b_bytes = (uint32_t)DW_KG * p.NB * 32u;
         tc::mbar_arrive_expect_tx(&raw_full[slot], a_bytes + b_bytes);
         unsigned char* dst = raw + slot * DW_RAW_SLOT;
@@ -600,93 +602,126 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         const float* gb = p.b_img + (size_t)tile * TM * p.NB + (size_t)kg * DW_KG * p.NB * 8;
         tc::tma_load_1d(dst, ga, a_bytes, &raw_full[slot]);
         tc::tma_load_1d(dst + a_bytes, gb, b_bytes, &raw_full[slot]);
+        if (++slot == DW_RAW_SLOTS) { slot = 0; phase ^= 1u; }
+        if (++within == stages_per_tile) { within = 0; tile += a.ctas_per_role; }
       }
     }
   } else if (warp == 1) {
     // =========================================================================== MMA issuer
     const uint32_t leader = tc::elect_one() ? 1u : 0u;
-    const uint32_t ones_addr = tc::smem_u32(ones);
-    const uint64_t ones_desc = tc::umma_smem_desc(ones_addr, 256u, 128u);
+    uint32_t slot = 0, phase = 0;
+    int within = 0;
+    bool first_tile = true;
     for (long long st = 0; st < nstages; ++st) {
-      const long long lt = st / stages_per_tile;
-      const int within = (int)(st - lt * stages_per_tile);
-      const int pi = within / (16 / DW_KG);
+      const int pi = within >= (16 / DW_KG) ? 1 : 0;
       const DwPair& p = role.pair[pi];
-      const uint32_t slot = (uint32_t)(st % DW_OP_SLOTS);
-      const uint32_t use = (uint32_t)(st / DW_OP_SLOTS);
-      tc::mbar_wait(&op_full[slot], use & 1u);
+      tc::mbar_wait(&op_full[slot], phase);
       tc::tc_fence_after();
       const uint32_t pa_b = dw_plane_bytes(p.MA), pb_b = dw_plane_bytes(p.NB);
       const uint32_t a_lbo = (uint32_t)p.MA * 16u + 16u, b_lbo = (uint32_t)p.NB * 16u + 16u;
       const uint32_t sbase = tc::smem_u32(ops) + slot * DW_OP_SLOT;
-      const uint32_t idesc = tc::umma_idesc_tf32(p.NB), idesc1 = tc::umma_idesc_tf32(16);
-      const bool first_stage_of_pair = (lt == 0) && (within % (16 / DW_KG) == 0);
+      const uint32_t idesc = tc::umma_idesc_tf32(p.NB);
+      const bool first_stage_of_pair = first_tile && (within == 0 || within == 16 / DW_KG);
 #pragma unroll
       for (int j = 0; j < DW_KG; ++j) {
         const uint32_t a_hi = sbase + (uint32_t)j * 2u * (pa_b + pb_b), a_lo = a_hi + pa_b;
         const uint32_t b_hi = a_lo + pa_b, b_lo = b_hi + pb_b;
         const uint64_t bd_hi = tc::umma_smem_desc(b_hi, b_lbo, 128u), bd_lo = tc::umma_smem_desc(b_lo, b_lbo, 128u);
         const uint32_t acc0 = (first_stage_of_pair && j == 0) ? 0u : 1u;
-        for (int mh = 0; mh < p.mhalves; ++mh) {
+        for (int mh = 0; mh < ((a.dbg & 2) ? 0 : p.mhalves); ++mh) {
           const uint64_t ad_hi = tc::umma_smem_desc(a_hi + (uint32_t)mh * 2048u, a_lbo, 128u);
           const uint64_t ad_lo = tc::umma_smem_desc(a_lo + (uint32_t)mh * 2048u, a_lbo, 128u);
           umma_ss_if(leader, tb + p.d_col[mh], ad_lo, bd_hi, idesc, acc0);
           umma_ss_if(leader, tb + p.d_col[mh], ad_hi, bd_lo, idesc, 1u);
           umma_ss_if(leader, tb + p.d_col[mh], ad_hi, bd_hi, idesc, 1u);
-          umma_ss_if(leader, tb + p.bias_col[mh], ad_lo, ones_desc, idesc1, acc0);
-          umma_ss_if(leader, tb + p.bias_col[mh], ad_hi, ones_desc, idesc1, 1u);
         }
       }
       umma_commit_if(leader, &op_empty[slot]);
+      if (++slot == DW_OP_SLOTS) { slot = 0; phase ^= 1u; }
+      if (++within == stages_per_tile) { within = 0; first_tile = false; }
     }
     umma_commit_if(leader, acc_done);
   } else {
     // =========================================================================== transposers, then flush
     const int tw = warp - 2;
     const int tid = tw * 32 + lane;   // 0..255
-    for (long long st = 0; st < nstages; ++st) {
-      const long long lt = st / stages_per_tile;
-      const int within = (int)(st - lt * stages_per_tile);
-      const int pi = within / (16 / DW_KG);
+    const bool rot = (lane & 16) != 0;
+    const uint32_t eoff = rot ? 32u : 0u;
+    static_assert(DW_TRANS_WARPS * 32 == 512, "a thread meets ONE (feature group, row-in-k-step) slot per pair");
+    float4 bsum[2];   // [pair]: column sums of the dZ chunks this thread transposes
+#pragma unroll
+    for (int u = 0; u < 2; ++u) bsum[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = tid; i < 2 * 256; i += DW_TRANS_WARPS * 32) bias_s[i] = 0.0f;
+    dw_bar_sync();
+    // Per-thread chunk plan, fixed for the whole kernel: one float4 chunk = (k-step j, feature group g, row r8) of the
+    // raw stage [A: DW_KG x (MA/4) x 8 x 4 | B: DW_KG x (NB/4) x 8 x 4].  A thread owns chunk `tid` of an operand and,
+    // for the 256-feature operand only, chunk `tid + 512` (= the same slot of the second k-step).
+    static_assert(DW_KG == 2, "the k-step of a chunk is found by one compare");
+    int t_src[2][2], t_n[2][2];
+    uint32_t t_dst[2][2], t_plane[2][2], t_step[2];
+#pragma unroll
+    for (int pi = 0; pi < 2; ++pi) {
       const DwPair& p = role.pair[pi];
-      const uint32_t rslot = (uint32_t)(st % DW_RAW_SLOTS), ruse = (uint32_t)(st / DW_RAW_SLOTS);
-      const uint32_t oslot = (uint32_t)(st % DW_OP_SLOTS), ouse = (uint32_t)(st / DW_OP_SLOTS);
-      tc::mbar_wait(&raw_full[rslot], ruse & 1u);
-      tc::mbar_wait(&op_empty[oslot], (ouse & 1u) ^ 1u);
-      tc::tc_fence_after();
-      const float* rsrc = reinterpret_cast<const float*>(raw + rslot * DW_RAW_SLOT);
-      unsigned char* odst = ops + oslot * DW_OP_SLOT;
       const uint32_t pa_b = dw_plane_bytes(p.MA), pb_b = dw_plane_bytes(p.NB);
-      // raw stage: [A: DW_KG x (MA/4) x 8 rows x 4] [B: DW_KG x (NB/4) x 8 x 4]; one float4 = (k-step j, group g, row r8)
-      static_assert(DW_KG == 2, "the k-step of a chunk is found by one compare");
-      const float4* src4 = reinterpret_cast<const float4*>(rsrc);
+      t_step[pi] = 2u * (pa_b + pb_b);   // bytes of one k-step block [A hi | A lo | B hi | B lo] in the operand stage
 #pragma unroll
       for (int op = 0; op < 2; ++op) {
         const int F = op ? p.NB : p.MA;
-        const int per_k = F * 2;                       // float4 chunks of one k-step: (F / 4) groups x 8 rows
-        const uint32_t plane = op ? pb_b : pa_b;
-        const uint32_t cstride = (uint32_t)F * 16u + 16u;   // K-chunk stride inside a plane
-        unsigned char* obase = odst + (op ? 2u * pa_b : 0u);
-        for (int i = tid; i < DW_KG * per_k; i += DW_TRANS_WARPS * 32) {
-          const int j = i >= per_k ? 1 : 0;
-          const int rem = i - j * per_k;
-          const int g = rem >> 3, r8 = rem & 7;
-          const float4 v = src4[i];
-          // K-major operand: plane[(chunk = r8 >> 2)][feature][r8 & 3]
-          unsigned char* kbase = obase + (uint32_t)j * 2u * (pa_b + pb_b) + (uint32_t)(r8 >> 2) * cstride +
-                                 (uint32_t)g * 64u + (uint32_t)(r8 & 3) * 4u;
-          uint32_t hi[4], lo[4];
-          split_fast(v.x, hi[0], lo[0]);
-          split_fast(v.y, hi[1], lo[1]);
-          split_fast(v.z, hi[2], lo[2]);
-          split_fast(v.w, hi[3], lo[3]);
+        const int per_k = 2 * F, total = DW_KG * per_k;
+        const int j = tid >= per_k ? 1 : 0;
+        const int rem = tid - j * per_k;
+        const int g = rem >> 3, r8 = rem & 7;
+        t_src[pi][op] = (op ? DW_KG * 2 * p.MA : 0) + tid;
+        t_n[pi][op] = (a.dbg & 1) ? 0 : (tid < total ? (tid + DW_TRANS_WARPS * 32 < total ? 2 : 1) : 0);
+        t_plane[pi][op] = op ? pb_b : pa_b;
+        // K-major operand: plane[(chunk = r8 >> 2)][feature][r8 & 3], chunk stride F * 16 + 16 bytes
+        t_dst[pi][op] = (op ? 2u * pa_b : 0u) + (uint32_t)j * t_step[pi] + (uint32_t)(r8 >> 2) * ((uint32_t)F * 16u + 16u) +
+                        (uint32_t)g * 64u + (uint32_t)(r8 & 3) * 4u;
+      }
+    }
+    // Lanes 16..31 store their four features in the order 2,3,0,1: with the 16-byte feature pitch of the core matrix
+    // this spreads a warp's 4-byte stores over all 32 banks.
+    const uint32_t eo0 = eoff, eo1 = eoff + 16u, eo2 = eoff ^ 32u, eo3 = (eoff ^ 32u) + 16u;
+    uint32_t rslot = 0, rphase = 0, oslot = 0, ophase = 0;
+    int within = 0;
+    for (long long st = 0; st < nstages; ++st) {
+      const int pi = within >= (16 / DW_KG) ? 1 : 0;
+      tc::mbar_wait(&raw_full[rslot], rphase);
+      tc::mbar_wait(&op_empty[oslot], ophase ^ 1u);
+      tc::tc_fence_after();
+      const float4* src4 = reinterpret_cast<const float4*>(raw + rslot * DW_RAW_SLOT);
+      unsigned char* odst = ops + oslot * DW_OP_SLOT;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            *reinterpret_cast<uint32_t*>(kbase + e * 16) = hi[e];
-            *reinterpret_cast<uint32_t*>(kbase + plane + e * 16) = lo[e];
+      for (int op = 0; op < 2; ++op) {
+        const int src = pi ? t_src[1][op] : t_src[0][op];
+        const int n = pi ? t_n[1][op] : t_n[0][op];
+        const uint32_t plane = pi ? t_plane[1][op] : t_plane[0][op];
+        const uint32_t step = pi ? t_step[1] : t_step[0];
+        unsigned char* kbase = odst + (pi ? t_dst[1][op] : t_dst[0][op]);
+#pragma unroll
+        for (int it = 0; it < 2; ++it) {
+          if (it < n) {
+            const float4 v = src4[src + it * (DW_TRANS_WARPS * 32)];
+            if (op == 0) {   // bias gradient = column sums of dZ: exact fp32 adds, reduced over the 8 row lanes at the end
+              float4& acc = pi == 0 ? bsum[0] : bsum[1];
+              acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            unsigned char* kb = kbase + it * step;
+            uint32_t hi, lo;
+            split_fast(rot ? v.z : v.x, hi, lo);
+            *reinterpret_cast<uint32_t*>(kb + eo0) = hi;
+            *reinterpret_cast<uint32_t*>(kb + plane + eo0) = lo;
+            split_fast(rot ? v.w : v.y, hi, lo);
+            *reinterpret_cast<uint32_t*>(kb + eo1) = hi;
+            *reinterpret_cast<uint32_t*>(kb + plane + eo1) = lo;
+            split_fast(rot ? v.x : v.z, hi, lo);
+            *reinterpret_cast<uint32_t*>(kb + eo2) = hi;
+            *reinterpret_cast<uint32_t*>(kb + plane + eo2) = lo;
+            split_fast(rot ? v.y : v.w, hi, lo);
+            *reinterpret_cast<uint32_t*>(kb + eo3) = hi;
+            *reinterpret_cast<uint32_t*>(kb + plane + eo3) = lo;
           }
         }
-        src4 += DW_KG * per_k;
       }
       tc::fence_proxy_async();
       __syncwarp();
@@ -694,41 +729,66 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         tc::mbar_arrive(&raw_empty[rslot]);
         tc::mbar_arrive(&op_full[oslot]);
       }
+      if (++rslot == DW_RAW_SLOTS) { rslot = 0; rphase ^= 1u; }
+      if (++oslot == DW_OP_SLOTS) { oslot = 0; ophase ^= 1u; }
+      if (++within == stages_per_tile) within = 0;
     }
+    // ---- bias gradients: sum the 8 row lanes of every feature group, then one shared-memory add per contributor
+    //      (at most two per slot, so the order cannot change the result)
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+#pragma unroll
+      for (int o2 = 1; o2 < 8; o2 <<= 1) {
+        bsum[u].x += __shfl_xor_sync(0xffffffffu, bsum[u].x, o2);
+        bsum[u].y += __shfl_xor_sync(0xffffffffu, bsum[u].y, o2);
+        bsum[u].z += __shfl_xor_sync(0xffffffffu, bsum[u].z, o2);
+        bsum[u].w += __shfl_xor_sync(0xffffffffu, bsum[u].w, o2);
+      }
+    }
+    if ((lane & 7) == 0) {
+#pragma unroll
+      for (int pi = 0; pi < 2; ++pi) {
+        const int per_k = role.pair[pi].MA * 2;
+        if (tid < DW_KG * per_k) {   // threads beyond the stage's chunk count never held a chunk of this pair
+          float* b = bias_s + pi * 256 + 4 * ((tid & (per_k - 1)) >> 3);
+          atomicAdd(b + 0, bsum[pi].x); atomicAdd(b + 1, bsum[pi].y);
+          atomicAdd(b + 2, bsum[pi].z); atomicAdd(b + 3, bsum[pi].w);
+        }
+      }
+    }
+    dw_bar_sync();
     // ---- flush the accumulators of this CTA to its partial: lane = output row (feature of dZ)
     tc::mbar_wait(acc_done, 0u);
     tc::tc_fence_after();
     {
       const int q = warp & 3;                 // TMEM lane quarter this warp may read
-      const int hsel = tw >> 2;               // two warps per quarter: split the columns
+      const int hsel = tw >> 2;               // four warps per quarter: 16-column blocks are dealt round-robin
       const int m = q * 32 + lane;
       const uint32_t t0 = tc::tmem_addr(tb, (uint32_t)q * 32u, 0);
       float* out = a.dw_part + (size_t)ci * a.net_total;
       auto dump = [&](uint32_t col0, int ncols, float* dst_row, int col_lo, int col_hi) {
         // writes columns [col_lo, col_hi) of the accumulator row to dst_row[col - col_lo]; this warp takes every
         // other 16-column block
-        for (int c = 16 * hsel; c < ncols; c += 32) {
+        for (int c = 16 * hsel; c < ncols; c += 16 * (DW_TRANS_WARPS / 4)) {
           uint32_t v[16];
           tc::tmem_ld16(t0 + col0 + c, v);
           tc::tmem_wait_ld();
-          if (dst_row != nullptr) {
+          if (dst_row != nullptr && c >= col_lo && c < col_hi) {   // windows are multiples of 16 columns, rows 16-byte aligned
+            float4* d4 = reinterpret_cast<float4*>(dst_row + (c - col_lo));
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (c + j >= col_lo && c + j < col_hi) dst_row[c + j - col_lo] = __uint_as_float(v[j]);
+            for (int j = 0; j < 4; ++j)
+              d4[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                                  __uint_as_float(v[4 * j + 3]));
           }
         }
       };
-      auto bias_val = [&](uint32_t col0) {
-        uint32_t v[16];
-        tc::tmem_ld16(t0 + col0, v);
-        tc::tmem_wait_ld();
-        return __uint_as_float(v[0]);
-      };
-      if (role_id == 0) {
+      auto bias_val = [&](int pi, int feature) { return bias_s[pi * 256 + feature]; };
+      if (a.dbg & 4) {
+      } else if (role_id == 0) {
         {   // layer 2: dW2[m][n] (128 x 256), db2[m]
           const DwPair& p = role.pair[0];
           dump(p.d_col[0], 256, out + a.off[2] + (size_t)m * 256, 0, 256);
-          const float b = bias_val(p.bias_col[0]);
+          const float b = bias_val(0, m);
           if (hsel == 0) out[a.off[3] + m] = b;
         }
         {   // layer 4: lanes [0,A) = to_mean.2 rows over m1 columns [0,64); lane 32 = to_value.2 over v1 columns [64,128)
@@ -738,7 +798,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
           if (m < a.A) { dst = out + a.off[6] + (size_t)m * 64; lo = 0; hi = 64; }
           else if (m == 32) { dst = out + a.off[10]; lo = 64; hi = 128; }
           dump(p.d_col[0], 128, dst, lo, hi);
-          const float b = bias_val(p.bias_col[0]);
+          const float b = bias_val(1, m & 63);
           if (hsel == 0) {
             if (m < a.A) out[a.off[7] + m] = b;
             else if (m == 32) out[a.off[11]] = b;
@@ -750,7 +810,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
           for (int mh = 0; mh < 2; ++mh) {
             // 80 columns = 5 blocks of 16: alternate blocks between the two warps of the quarter
             dump(p.d_col[mh], 80, out + a.off[0] + (size_t)(128 * mh + m) * 80, 0, 80);
-            const float b = bias_val(p.bias_col[mh]);
+            const float b = bias_val(0, 128 * mh + m);
             if (hsel == 0) out[a.off[1] + 128 * mh + m] = b;
           }
         }
@@ -758,7 +818,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
           const DwPair& p = role.pair[1];
           float* dst = (m < 64) ? out + a.off[4] + (size_t)m * 128 : out + a.off[8] + (size_t)(m - 64) * 128;
           dump(p.d_col[0], 128, dst, 0, 128);
-          const float b = bias_val(p.bias_col[0]);
+          const float b = bias_val(1, m);
           if (hsel == 0) {
             if (m < 64) out[a.off[5] + m] = b;
             else out[a.off[9] + m - 64] = b;
@@ -884,7 +944,8 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   d.net_total = net->total;
   for (int i = 0; i < 12; ++i) d.off[i] = net->off[i];
   d.A = net->num_act;
-  const size_t smem2 = 1024 + (size_t)DW_RAW_SLOTS * DW_RAW_SLOT + (size_t)DW_OP_SLOTS * DW_OP_SLOT + 512 + 256;
+  { const char* e = getenv("FLYB_DW_DBG"); d.dbg = e ? atoi(e) : 0; }
+  const size_t smem2 = 1024 + (size_t)DW_RAW_SLOTS * DW_RAW_SLOT + (size_t)DW_OP_SLOTS * DW_OP_SLOT + 512 + 2048 + 256;
   if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel), smem2)) != FLYB_OK) return rc;
   ppo_dw_tc_kernel<<<2 * w.ctas_per_role, DW_THREADS, smem2, st>>>(d);
   FLYB_LAUNCH_CHECK("ppo_dw_tc_kernel");
