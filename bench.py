@@ -274,7 +274,7 @@ def run_own(args):
     roll_ms = max_over_ranks(e0.elapsed_time(e1))
     env_steps = NUM_ENVS * HORIZON * K * world
     value = env_steps / (roll_ms * 1e-3)
-    launches = K * HORIZON * 3
+    launches = K * HORIZON * 2
 
     # ---------------- update: GAE + 75 optimiser steps (graph), timed on its own
     for _ in range(2):

@@ -35,6 +35,11 @@ class EnvCfg(C.Structure):
     ]
 
 
+class StepTail(C.Structure):
+    _fields_ = [("action_var", C.c_void_p), ("num_act", C.c_int32), ("decay", C.c_float), ("floor", C.c_float),
+                ("step_counter", C.c_void_p)]
+
+
 class NetLayout(C.Structure):
     _fields_ = [("num_obs", C.c_int32), ("num_act", C.c_int32), ("k0_pad", C.c_int32), ("total", C.c_int32),
                 ("off", C.c_int32 * 12)]
@@ -56,7 +61,7 @@ SIGNATURES = {
     "flyb_wpack_bytes": (C.c_size_t, [C.POINTER(NetLayout)]),
     "flyb_pack_weights": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P]),
     "flyb_env_scratch_bytes": (C.c_size_t, [C.c_int32]),
-    "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 19),
+    "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 18 + [C.POINTER(StepTail), _P]),
     "flyb_env_pre_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 10),
     "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64, _P,
                                   _P, _P, _P, _P, C.POINTER(EnvCfg)] + [_P] * 9),
@@ -84,7 +89,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)  # AttributeError if the .so does not export it
             fn.restype = restype
             fn.argtypes = argtypes
-        if handle.flyb_abi_version() != 3:
+        if handle.flyb_abi_version() != 4:
             raise FlybError("libflyb200.so ABI version mismatch")
         _lib = handle
     return _lib

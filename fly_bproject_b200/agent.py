@@ -207,6 +207,9 @@ class PPO:
         self.seed = int(_get(args, "seed", 0))
         self._rng_counter = torch.zeros(1, dtype=torch.int64, device=dev)   # Philox draw number, advanced on device
         self._fused_env = isinstance(self.env, Fly)
+        testing = bool(_get(args, "testing", False))
+        self._tail = _lib.StepTail(self.action_var.data_ptr(), a, 0.0 if testing else 0.00001, 0.0 if testing else 0.01,
+                                   self._rng_counter.data_ptr())
         self._graphs = {}
 
         # data-parallel: one process per GPU, the only collective is the gradient all-reduce
@@ -246,7 +249,10 @@ class PPO:
             st.set_reset_ids(env.reset_ids, env.reset_count)
             env.simulate()
             env.render_count += 1
-            env.post_physics(obs_copy=self._obs_ring[i + 1], reward_copy=self.all_reward[i])
+            # ppo.py:236-237 (variance annealing, skipped in testing mode) and the Philox draw counter ride on the
+            # step's last launch
+            env.post_physics(obs_copy=self._obs_ring[i + 1], reward_copy=self.all_reward[i], tail=self._tail)
+            return
         else:   # foreign env object behind the reference's duck-typed surface (ppo.py:210-229)
             obs = env.obs_buf.contiguous()
             _lib.check(self.lib.flyb_policy_act(

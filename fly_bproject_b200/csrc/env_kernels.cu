@@ -51,7 +51,8 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
                     long long* __restrict__ reset, float* __restrict__ obs, float* __restrict__ reward,
                     float* __restrict__ up_vec, float* __restrict__ heading_vec, int* __restrict__ reset_ids,
                     int* __restrict__ reset_count, ScanScratch* __restrict__ scratch, float* __restrict__ obs_copy,
-                    float* __restrict__ reward_copy, float* __restrict__ reward_sum) {
+                    float* __restrict__ reward_copy, float* __restrict__ reward_sum,
+                    const __grid_constant__ FlybStepTail tail) {
   extern __shared__ __align__(16) float smem[];
   const int N = cfg.num_envs, D = cfg.num_dof, A = cfg.num_act, B = cfg.num_bodies;
   const int O = 19 + 3 * A;
@@ -262,6 +263,11 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   if (s_last) {
     for (int i = tid; i < (int)gridDim.x; i += PP_THREADS) scratch->status[i] = 0ull;
     if (tid == 0) scratch->done = 0u;
+    if (tail.action_var != nullptr) {   // end-of-step housekeeping (ppo.py:236-237), once per launch
+      for (int i = tid; i < tail.num_act; i += PP_THREADS)
+        tail.action_var[i] = fmaxf(tail.floor, tail.action_var[i] - tail.decay);
+      if (tid == 0 && tail.step_counter != nullptr) *tail.step_counter += 1ull;
+    }
   }
 }
 
@@ -352,7 +358,7 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
                                      float* prev_potentials, int64_t* progress, int64_t* reset, float* obs,
                                      float* reward, float* up_vec, float* heading_vec, int32_t* reset_ids,
                                      int32_t* reset_count, void* scratch, float* obs_copy, float* reward_copy,
-                                     float* reward_sum, void* stream) {
+                                     float* reward_sum, const FlybStepTail* tail, void* stream) {
   int rc = validate_cfg(cfg);
   if (rc != FLYB_OK) return rc;
   FLYB_REQUIRE(root && dof_state && force && actions_scaled && potentials && prev_potentials && progress && reset &&
@@ -365,10 +371,15 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
   rc = ensure_smem(reinterpret_cast<const void*>(post_physics_kernel), smem);
   if (rc != FLYB_OK) return rc;
   const int grid = (cfg->num_envs + ENVS - 1) / ENVS;
+  FlybStepTail t{};
+  if (tail && tail->action_var) {
+    FLYB_REQUIRE(tail->num_act > 0 && tail->num_act <= FLYB_MAX_DOF, "flyb_env_post_physics: tail.num_act out of range");
+    t = *tail;
+  }
   post_physics_kernel<<<grid, PP_THREADS, smem, (cudaStream_t)stream>>>(
       *cfg, root, dof_state, force, actions_scaled, potentials, prev_potentials, (long long*)progress,
       (long long*)reset, obs, reward, up_vec, heading_vec, reset_ids, reset_count, (ScanScratch*)scratch, obs_copy,
-      reward_copy, reward_sum);
+      reward_copy, reward_sum, t);
   FLYB_LAUNCH_CHECK("post_physics_kernel");
   return FLYB_OK;
 }

@@ -116,15 +116,17 @@ class Fly:
     def simulate(self) -> None:
         self.state.simulate()
 
-    def post_physics(self, obs_copy=None, reward_copy=None) -> None:
-        """fly.py:676-681: get_obs, progress_buf += 1, get_reward — one launch; also compacts the reset ids."""
+    def post_physics(self, obs_copy=None, reward_copy=None, tail=None) -> None:
+        """fly.py:676-681: get_obs, progress_buf += 1, get_reward — one launch; also compacts the reset ids.
+        `tail` (a `_lib.StepTail`): end-of-step housekeeping of PPO.run that rides on this launch (ppo.py:236-237)."""
         p = _lib.ptr
         st = self.state
         _lib.check(self.lib.flyb_env_post_physics(
             C.byref(self.cfg), p(st.root), p(st.dof_state), p(st.force), p(self._actions_scaled),
             p(self.potentials), p(self.prev_potentials), p(self.progress_buf), p(self.reset_buf), p(self.obs_buf),
             p(self.reward_buf), p(self.up_vec), p(self.heading_vec), p(self.reset_ids), p(self.reset_count),
-            p(self._scratch), p(obs_copy), p(reward_copy), p(self.reward_sum), _lib.current_stream()),
+            p(self._scratch), p(obs_copy), p(reward_copy), p(self.reward_sum),
+            C.byref(tail) if tail is not None else None, _lib.current_stream()),
             "flyb_env_post_physics")
 
     def step(self, actions: torch.Tensor) -> None:

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FLYB_ABI_VERSION 3
+#define FLYB_ABI_VERSION 4
 #define FLYB_MAX_DOF 64      /* asset DOF count D: 18 (nmf_no_limits_limited_Dofs.urdf) or 42 (nmf_no_limits.urdf) */
 #define FLYB_NUM_ABDOMEN 5   /* reference fly.py:299 */
 #define FLYB_NUM_LEGTIPS 6   /* reference fly.py:300 */
@@ -95,6 +95,16 @@ typedef struct FlybPpoCfg {
   double max_grad_norm; /* 1.0 (ppo.py:198) */
 } FlybPpoCfg;
 
+/* End-of-step housekeeping of PPO.run that rides on the last launch of a step (flyb_env_post_physics) instead of
+ * costing one of its own: action_var <- max(floor, action_var - decay) (reference ppo.py:236-237) and the Philox
+ * draw counter += 1.  Same effect as flyb_anneal_var. */
+typedef struct FlybStepTail {
+  float* action_var;        /* (num_act) device; NULL = nothing to do */
+  int32_t num_act;
+  float decay, floor;
+  uint64_t* step_counter;   /* device, nullable */
+} FlybStepTail;
+
 int flyb_abi_version(void);
 const char* flyb_last_error(void);
 /* Number of CUDA devices visible, or a negative code. */
@@ -123,13 +133,14 @@ int flyb_pack_weights(const FlybNetLayout* net, const float* params, void* wpack
  *      mask is now set (what `reset_buf.nonzero()` yields at fly.py:447, compacted on the device),
  *      reset_count (1) i32.  obs_copy / reward_copy (nullable) receive a second copy (rollout rows, ppo.py:228-229);
  *      reward_sum (1, nullable) += sum(reward) — the device-side accumulator behind the score log (ppo.py:233).
+ *      tail (nullable): FlybStepTail applied by the last CTA to finish.
  * scratch: flyb_env_scratch_bytes(N) bytes, zeroed once by the caller before first use. */
 size_t flyb_env_scratch_bytes(int32_t num_envs);
 int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, const float* dof_state, const float* force,
                           const float* actions_scaled, float* potentials, float* prev_potentials, int64_t* progress,
                           int64_t* reset, float* obs, float* reward, float* up_vec, float* heading_vec,
                           int32_t* reset_ids, int32_t* reset_count, void* scratch, float* obs_copy,
-                          float* reward_copy, float* reward_sum, void* stream);
+                          float* reward_copy, float* reward_sum, const FlybStepTail* tail, void* stream);
 
 /* ---- env: reference Fly.step up to simulate() (fly.py:626-660): scale policy actions to the joint range,
  *      scatter into the DOF position-target vector, then Fly.reset() (fly.py:446-480) for envs whose mask is set.
