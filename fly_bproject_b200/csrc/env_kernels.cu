@@ -6,15 +6,14 @@
 // reference become one launch each side of the physics step.
 //
 // Data movement (HBM-bound; algorithmic bytes per env-step in DESIGN.md):
-//   * one CTA owns ENVS consecutive envs; every global access is a flat, coalesced sweep over the CTA's
-//     contiguous slab (root rows, actuated DOF pairs, action rows, obs rows) — rows are 52 / 292 bytes, so
-//     per-thread row access would be misaligned; slabs are staged in shared memory instead and obs rows
-//     leave as full 128-bit stores;
-//   * the 11 contact-force rows an env needs (5 abdomen + 6 leg tips out of 93 bodies) are gathered with a
-//     flat (env, row, component) index so that a warp touches ~11 sectors per request instead of 32;
+//   * one CTA owns 64 consecutive envs, four threads per env; the root slab comes in as one coalesced float4
+//     sweep, obs rows are assembled in shared memory and leave as full 128-bit stores (rows are 52 / 292 bytes,
+//     so per-thread row access would be misaligned);
+//   * the 11 contact-force rows an env needs (5 abdomen + 6 leg tips out of 93 bodies) and its actuated DOF
+//     pairs are gathered by the env's four threads with stride 4 through shared-memory offset tables;
 //   * reset ids are compacted in ascending order (== torch.nonzero) inside the same launch: warp ballot ->
-//     CTA prefix -> decoupled look-back across CTAs (ticketed, so forward progress never depends on
-//     residency); the count stays on the device — the reference's host sync at fly.py:447-450 is gone.
+//     one 64-bit mask per CTA -> the last CTA to finish scans the bitmap and writes the id list; the count
+//     stays on the device — the reference's host sync at fly.py:447-450 is gone.
 #include "env_math.cuh"
 
 namespace flyb {
@@ -23,7 +22,7 @@ constexpr int ENVS = 64;           // envs per CTA
 constexpr int PP_THREADS = 256;    // 4 threads per env for the load / store sweeps; threads [0, ENVS) own one env each
 constexpr int PP_WARPS = PP_THREADS / 32;
 
-// look-back status word: [63:32] flag (0 none, 1 aggregate, 2 inclusive prefix), [31:0] value
+// cross-CTA scratch: `done` counts finished CTAs (re-armed by the last one), status[b] = 64-bit reset mask of CTA b
 struct ScanScratch {
   unsigned int ticket;   // unused (kept so that the scratch size / zeroing contract of ABI v2 stands)
   unsigned int done;
@@ -40,9 +39,11 @@ FLYB_D void st_status(unsigned long long* p, unsigned long long v) {
 }
 
 // The kernel is latency-bound at the env counts of the reference's configs (16384 envs = 12.5 MB per launch), so
-// every thread issues ALL its global loads before the first dependent shared-memory store, the per-env scalars
-// are fetched in that same wave, the observation slab leaves before the cross-CTA scan is waited for, and the
-// look-back inspects 256 predecessors per round (one per thread) instead of 32.
+// every thread issues ALL its global loads before the first dependent shared-memory store, with as little address
+// arithmetic in front of them as possible: a thread is (env e = tid / 4, quarter qd = tid % 4) and walks its env's
+// 33 gathered contact values / A actuated DOFs with stride 4 through small shared-memory offset tables.
+// Reset ids: every CTA publishes a 64-bit mask of its envs; the LAST CTA to finish (a counter tells) scans the
+// bitmap and writes the ascending id list (== torch.nonzero) and the count — no CTA ever waits for another one.
 __global__ void __launch_bounds__(PP_THREADS)
 post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restrict__ root,
                     const float* __restrict__ dof_state, const float* __restrict__ force,
@@ -59,25 +60,24 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   float* obs_s = smem;                        // [ENVS][O]      (O is odd -> conflict-free row access)
   float* root_s = obs_s + ENVS * O;           // [ENVS][13]
   float* force_s = root_s + ENVS * 13;        // [ENVS][33]
-  __shared__ int s_warp_cnt[ENVS / 32];
-  __shared__ int s_red[PP_WARPS];
-  __shared__ int s_first;
+  __shared__ unsigned s_mask[ENVS / 32];
+  __shared__ int s_scan[PP_WARPS];
   __shared__ int s_last;
-  // small index / limit tables: per-lane indexed reads of the __grid_constant__ copy would serialise in the
-  // constant cache (one replay per distinct address), shared memory serves them in one wavefront
-  __shared__ int s_body[FORCE_ROWS];
+  // small tables: per-lane indexed reads of the __grid_constant__ copy would serialise in the constant cache
+  __shared__ int s_foff[FORCE_VALS];          // float offset of gathered value rc inside one env's force block
   __shared__ int s_aidx[FLYB_MAX_DOF];
   __shared__ float s_lo[FLYB_MAX_DOF], s_hi[FLYB_MAX_DOF];
 
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
-  const int blk = blockIdx.x;                 // CTAs are dispatched in blockIdx order: predecessors are resident or done
+  const int blk = blockIdx.x;
   const int env0 = blk * ENVS;
   const int nenv = min(ENVS, N - env0);
+  static_assert(PP_THREADS == 4 * ENVS, "four threads per env");
+  const int e = tid >> 2, qd = tid & 3;
+  const bool e_ok = e < nenv;
 
-  // ---- wave of loads 1: root slab (contiguous nenv*13 floats; 16B aligned since ENVS*52 % 16 == 0),
-  //      per-env scalars, the 11 gathered contact-force rows per env (flat (env, row, comp) index: a warp touches
-  //      ~11 sectors per request instead of 32)
+  // ---- loads, wave 1: root slab (contiguous nenv*13 floats; 16B aligned since ENVS*52 % 16 == 0), per-env scalars
   constexpr int ROOT4 = ENVS * 13 / 4;        // 208 <= PP_THREADS
   static_assert(ROOT4 <= PP_THREADS, "one float4 of the root slab per thread");
   const int nroot = nenv * 13;
@@ -90,62 +90,56 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     prog_in = progress[env0 + tid];
     reset_in = reset[env0 + tid];
   }
-  if (tid < FORCE_ROWS)
-    s_body[tid] = (tid < FLYB_NUM_ABDOMEN) ? cfg.abdomen_local[tid] : cfg.legtip_local[tid - FLYB_NUM_ABDOMEN];
-  if (tid >= 32 && tid < 32 + A) {
-    const int d = cfg.action_idx[tid - 32];
-    s_aidx[tid - 32] = d;
-    s_lo[tid - 32] = cfg.lower[d];
-    s_hi[tid - 32] = cfg.upper[d];
+  if (tid < FORCE_VALS) {
+    const int r = tid / 3;
+    const int body = (r < FLYB_NUM_ABDOMEN) ? cfg.abdomen_local[r] : cfg.legtip_local[r - FLYB_NUM_ABDOMEN];
+    s_foff[tid] = body * 3 + (tid - r * 3);
+  }
+  if (tid >= 64 && tid < 64 + A) {
+    const int d = cfg.action_idx[tid - 64];
+    s_aidx[tid - 64] = d;
+    s_lo[tid - 64] = cfg.lower[d];
+    s_hi[tid - 64] = cfg.upper[d];
   }
   __syncthreads();
-  constexpr int FITER = (ENVS * FORCE_VALS + PP_THREADS - 1) / PP_THREADS;   // 9
+  // ---- wave 2: the 11 gathered contact-force rows of this thread's env, values rc = qd, qd + 4, ...
+  constexpr int FITER = (FORCE_VALS + 3) / 4;   // 9
   float fv[FITER];
-  const int nforce = nenv * FORCE_VALS;
+  {
+    const float* fe = force + (size_t)(env0 + e) * B * 3;
 #pragma unroll
-  for (int it = 0; it < FITER; ++it) {
-    const int i = tid + it * PP_THREADS;
-    fv[it] = 0.0f;
-    if (i < nforce) {
-      const int e = i / FORCE_VALS;
-      const int rc = i - e * FORCE_VALS;
-      const int r = rc / 3;
-      const int comp = rc - r * 3;
-      fv[it] = __ldg(force + ((size_t)(env0 + e) * B + s_body[r]) * 3 + comp);
+    for (int it = 0; it < FITER; ++it) {
+      const int rc = qd + 4 * it;
+      fv[it] = (e_ok && rc < FORCE_VALS) ? __ldg(fe + s_foff[rc]) : 0.0f;
     }
   }
-  // ---- wave of loads 2: actuated DOF (pos, vel) pairs and the commanded actions, 4 (env, k) elements in flight
-  //      per thread -> obs[12 : 12+A], obs[12+A : 12+2A], obs[12+2A : 12+3A]   (fly.py:795, 801, 802)
+  // ---- wave 3: actuated DOF (pos, vel) pairs and commanded actions of this thread's env, k = qd, qd + 4, ...
+  //      -> obs[12 : 12+A], obs[12+A : 12+2A], obs[12+2A : 12+3A]   (fly.py:795, 801, 802)
   {
-    const float2* dof2 = reinterpret_cast<const float2*>(dof_state);
-    const float inv_a = 1.0f / (float)A;
-    const int n = nenv * A;
-    constexpr int DU = 4;
-    for (int base = 0; base < n; base += DU * PP_THREADS) {
+    const float2* de = reinterpret_cast<const float2*>(dof_state) + (size_t)(env0 + e) * D;
+    const float* ae = actions_scaled + (size_t)(env0 + e) * A;
+    float* oe = obs_s + e * O + 12;
+    constexpr int DU = 5;                        // 20 DOFs per pass: one pass for the 18-DOF asset
+    for (int k0 = 0; k0 < A; k0 += 4 * DU) {
       float2 pv[DU];
       float act[DU];
-      int ee[DU], kk[DU];
 #pragma unroll
       for (int u = 0; u < DU; ++u) {
-        const int i = base + u * PP_THREADS + tid;
-        const int e = (int)(((float)i + 0.5f) * inv_a);   // i / A, exact for i < 2^22
-        ee[u] = e;
-        kk[u] = i - e * A;
+        const int k = k0 + qd + 4 * u;
         pv[u] = make_float2(0.f, 0.f);
         act[u] = 0.0f;
-        if (i < n) {
-          pv[u] = __ldg(dof2 + (size_t)(env0 + e) * D + s_aidx[kk[u]]);
-          act[u] = __ldg(actions_scaled + (size_t)env0 * A + i);
+        if (e_ok && k < A) {
+          pv[u] = __ldg(de + s_aidx[k]);
+          act[u] = __ldg(ae + k);
         }
       }
 #pragma unroll
       for (int u = 0; u < DU; ++u) {
-        const int i = base + u * PP_THREADS + tid;
-        if (i < n) {
-          float* o = obs_s + ee[u] * O + 12 + kk[u];
-          o[0] = unscale(pv[u].x, s_lo[kk[u]], s_hi[kk[u]]);
-          o[A] = pv[u].y * cfg.dof_vel_scale;
-          o[2 * A] = act[u];
+        const int k = k0 + qd + 4 * u;
+        if (e_ok && k < A) {
+          oe[k] = unscale(pv[u].x, s_lo[k], s_hi[k]);
+          oe[A + k] = pv[u].y * cfg.dof_vel_scale;
+          oe[2 * A + k] = act[u];
         }
       }
     }
@@ -154,8 +148,8 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   for (int i = (nroot & ~3) + tid; i < nroot; i += PP_THREADS) root_s[i] = __ldg(root + (size_t)env0 * 13 + i);
 #pragma unroll
   for (int it = 0; it < FITER; ++it) {
-    const int i = tid + it * PP_THREADS;
-    if (i < nforce) force_s[i] = fv[it];
+    const int rc = qd + 4 * it;
+    if (e_ok && rc < FORCE_VALS) force_s[e * FORCE_VALS + rc] = fv[it];
   }
   __syncthreads();
 
@@ -180,25 +174,25 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     heading_vec[env * 3 + 2] = out.heading_vec.z;
     flag = out.reset != 0;
   }
-  unsigned ballot = 0u;
   if (warp < ENVS / 32) {
-    ballot = __ballot_sync(0xffffffffu, flag);
-    if (lane == 0) s_warp_cnt[warp] = __popc(ballot);
+    const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) s_mask[warp] = ballot;
     if (reward_sum) {   // score accumulator (ppo.py:233), one atomic per warp
       const float ws = warp_sum(my_reward);
       if (lane == 0) atomicAdd(reward_sum, ws);
     }
   }
   __syncthreads();
-  int warp_off = 0, block_cnt = 0;
-#pragma unroll
-  for (int w = 0; w < ENVS / 32; ++w) {
-    if (w < warp) warp_off += s_warp_cnt[w];
-    block_cnt += s_warp_cnt[w];
+  static_assert(ENVS == 64, "one 64-bit reset mask per CTA");
+  unsigned long long* bitmap = scratch->status;
+  // publish the mask and count this CTA as done BEFORE its obs slab leaves: the CTA that sees the counter complete
+  // only needs the masks, so its scan overlaps the other CTAs' stores (the atomic's result is consumed after the slab)
+  unsigned done_prev = 0u;
+  if (tid == 0) {
+    st_status(bitmap + blk, ((unsigned long long)s_mask[1] << 32) | (unsigned long long)s_mask[0]);
+    __threadfence();
+    done_prev = atomicAdd(&scratch->done, 1u);
   }
-  // publish this CTA's count as early as possible: an inclusive prefix for CTA 0, an aggregate otherwise
-  unsigned long long* status = scratch->status;
-  if (tid == 0) st_status(status + blk, ((blk == 0 ? 2ull : 1ull) << 32) | (unsigned)block_cnt);
 
   // ---- obs slab out: full 128-bit stores (slab base 16B aligned: ENVS*O*4 % 16 == 0)
   {
@@ -217,57 +211,50 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     }
   }
 
-  // ---- reset-id compaction, ascending (== torch.nonzero): decoupled look-back across CTAs, one predecessor per
-  //      thread and round; threads that fall before CTA 0 act as a zero-valued inclusive prefix
-  int excl = 0;
-  if (blk > 0) {
-    int look = blk - 1;
-    while (true) {   // block-uniform
-      const int idx = look - tid;
-      unsigned long long st = 2ull << 32;
-      if (idx >= 0) {
-        do { st = ld_status(status + idx); } while ((st >> 32) == 0ull);
-      }
-      if (tid == 0) s_first = PP_THREADS;
-      __syncthreads();
-      if ((st >> 32) == 2ull) atomicMin(&s_first, tid);   // nearest predecessor that already holds an inclusive prefix
-      __syncthreads();
-      const int first = s_first;
-      int v = (first == PP_THREADS || tid <= first) ? (int)(unsigned)(st & 0xffffffffull) : 0;
-#pragma unroll
-      for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
-      if (lane == 0) s_red[warp] = v;
-      __syncthreads();
-#pragma unroll
-      for (int w = 0; w < PP_WARPS; ++w) excl += s_red[w];
-      if (first != PP_THREADS) break;
-      look -= PP_THREADS;
-    }
-    if (tid == 0) st_status(status + blk, (2ull << 32) | (unsigned)(excl + block_cnt));
-  }
-  if (tid == 0 && env0 + ENVS >= N) *reset_count = excl + block_cnt;   // the CTA that owns the last env
-  if (flag) {
-    const int pos = excl + warp_off + __popc(ballot & ((1u << lane) - 1u));
-    reset_ids[pos] = env0 + tid;
-  }
-
-  // ---- self-cleaning scratch: the last CTA to finish re-arms the status words for the next launch
-  __syncthreads();
+  // ---- the last CTA to finish turns the bitmap into the ascending id list (== reset_buf.nonzero(), fly.py:447)
   if (tid == 0) {
-    __threadfence();
-    const unsigned nblk = gridDim.x;
-    const unsigned prev = atomicAdd(&scratch->done, 1u);
-    s_last = (prev == nblk - 1) ? 1 : 0;
+    s_last = (done_prev == gridDim.x - 1) ? 1 : 0;
+    if (s_last) __threadfence();
   }
   __syncthreads();
-  if (s_last) {
-    for (int i = tid; i < (int)gridDim.x; i += PP_THREADS) scratch->status[i] = 0ull;
-    if (tid == 0) scratch->done = 0u;
-    if (tail.action_var != nullptr) {   // end-of-step housekeeping (ppo.py:236-237), once per launch
-      for (int i = tid; i < tail.num_act; i += PP_THREADS)
-        tail.action_var[i] = fmaxf(tail.floor, tail.action_var[i] - tail.decay);
-      if (tid == 0 && tail.step_counter != nullptr) *tail.step_counter += 1ull;
+  if (!s_last) return;
+  const int nblk = (int)gridDim.x;
+  int base = 0;
+  for (int w0 = 0; w0 < nblk; w0 += PP_THREADS) {      // 256 CTAs' masks per pass (one pass up to 16384 envs)
+    const int w = w0 + tid;
+    unsigned long long word = (w < nblk) ? ld_status(bitmap + w) : 0ull;
+    const int cnt = __popcll(word);
+    int incl = cnt;                                     // inclusive scan over the CTA
+#pragma unroll
+    for (int o2 = 1; o2 < 32; o2 <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o2);
+      if (lane >= o2) incl += t;
     }
+    if (lane == 31) s_scan[warp] = incl;
+    __syncthreads();
+    int warp_off = 0, pass_total = 0;
+#pragma unroll
+    for (int i = 0; i < PP_WARPS; ++i) {
+      if (i < warp) warp_off += s_scan[i];
+      pass_total += s_scan[i];
+    }
+    int pos = base + warp_off + incl - cnt;
+    while (word != 0ull) {
+      const int b = __ffsll((long long)word) - 1;
+      reset_ids[pos++] = w * ENVS + b;
+      word &= word - 1ull;
+    }
+    base += pass_total;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    *reset_count = base;
+    scratch->done = 0u;                                 // re-armed for the next launch
+  }
+  if (tail.action_var != nullptr) {   // end-of-step housekeeping (ppo.py:236-237), once per launch
+    for (int i = tid; i < tail.num_act; i += PP_THREADS)
+      tail.action_var[i] = fmaxf(tail.floor, tail.action_var[i] - tail.decay);
+    if (tid == 0 && tail.step_counter != nullptr) *tail.step_counter += 1ull;
   }
 }
 
