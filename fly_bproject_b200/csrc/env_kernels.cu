@@ -218,34 +218,34 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   }
   __syncthreads();
   if (!s_last) return;
+  // each thread owns a contiguous run of W masks: one sweep to count, one block scan, one sweep to write its ids
   const int nblk = (int)gridDim.x;
-  int base = 0;
-  for (int w0 = 0; w0 < nblk; w0 += PP_THREADS) {      // 256 CTAs' masks per pass (one pass up to 16384 envs)
-    const int w = w0 + tid;
-    unsigned long long word = (w < nblk) ? ld_status(bitmap + w) : 0ull;
-    const int cnt = __popcll(word);
-    int incl = cnt;                                     // inclusive scan over the CTA
+  const int W = (nblk + PP_THREADS - 1) / PP_THREADS;
+  const int w_begin = min(tid * W, nblk), w_end = min(w_begin + W, nblk);
+  int cnt = 0;
+  for (int w = w_begin; w < w_end; ++w) cnt += __popcll(ld_status(bitmap + w));
+  int incl = cnt;                                       // inclusive scan over the CTA
 #pragma unroll
-    for (int o2 = 1; o2 < 32; o2 <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, incl, o2);
-      if (lane >= o2) incl += t;
-    }
-    if (lane == 31) s_scan[warp] = incl;
-    __syncthreads();
-    int warp_off = 0, pass_total = 0;
+  for (int o2 = 1; o2 < 32; o2 <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o2);
+    if (lane >= o2) incl += t;
+  }
+  if (lane == 31) s_scan[warp] = incl;
+  __syncthreads();
+  int warp_off = 0, base = 0;
 #pragma unroll
-    for (int i = 0; i < PP_WARPS; ++i) {
-      if (i < warp) warp_off += s_scan[i];
-      pass_total += s_scan[i];
-    }
-    int pos = base + warp_off + incl - cnt;
+  for (int i = 0; i < PP_WARPS; ++i) {
+    if (i < warp) warp_off += s_scan[i];
+    base += s_scan[i];
+  }
+  int pos = warp_off + incl - cnt;
+  for (int w = w_begin; w < w_end; ++w) {
+    unsigned long long word = ld_status(bitmap + w);
     while (word != 0ull) {
       const int b = __ffsll((long long)word) - 1;
       reset_ids[pos++] = w * ENVS + b;
       word &= word - 1ull;
     }
-    base += pass_total;
-    __syncthreads();
   }
   if (tid == 0) {
     *reset_count = base;

@@ -144,3 +144,24 @@ def test_step_api_and_errors():
         env.step(torch.zeros(300, 18))                  # CPU tensor: no fallback
     assert env.dof_pos.shape == (300, 18) and env.root_tensor.shape == (300, 13)
     assert env.force_tensor.shape == (300 * 93, 3)
+
+
+def test_step_tail_rides_on_post_physics():
+    """FlybStepTail: the per-step variance annealing (ppo.py:236-237) and the Philox draw counter are applied exactly
+    once per launch by the last CTA, whatever the grid size; without a tail nothing else is touched."""
+    from fly_bproject_b200 import _lib
+    for n in (64, 1000, 40000):
+        env = fb.Fly(fb.make_args(num_envs=n, sim_device=DEV, state_pool=1, seed=n))
+        var = torch.full((18,), 0.2, device=DEV)
+        var[3] = 0.0100049                                  # lands on the floor after one step
+        counter = torch.zeros(1, dtype=torch.int64, device=DEV)
+        tail = _lib.StepTail(var.data_ptr(), 18, 0.00001, 0.01, counter.data_ptr())
+        want = var.cpu().clone()
+        for it in range(5):
+            env.post_physics(tail=tail)
+            want = fo.anneal_var(want)
+        env.post_physics()                                  # no tail: variance and counter stay
+        torch.cuda.synchronize()
+        assert int(counter.item()) == 5
+        torch.testing.assert_close(var.cpu(), want, rtol=0, atol=0)
+        assert float(var[3]) == pytest.approx(0.01)
