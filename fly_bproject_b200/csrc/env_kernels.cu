@@ -61,6 +61,8 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   float* root_s = obs_s + ENVS * O;           // [ENVS][13]
   float* force_s = root_s + ENVS * 13;        // [ENVS][33]
   __shared__ unsigned s_mask[ENVS / 32];
+  __shared__ int s_cnt[ENVS];                 // role 3 -> role 0: legs | at_limit << 8 | abdomen_hit << 16
+  __shared__ float s_sq[ENVS];
   __shared__ int s_scan[PP_WARPS];
   __shared__ int s_last;
   // small tables: per-lane indexed reads of the __grid_constant__ copy would serialise in the constant cache
@@ -153,28 +155,97 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   }
   __syncthreads();
 
-  // ---- per-env math: one thread per env (warps 0 .. ENVS/32-1)
+  // ---- per-env math, split over four warp pairs (independent dependency chains instead of one long one; a role is
+  //      a whole warp, so nothing diverges):  role 0: potential, heading / up projections, later reward + termination;
+  //      role 1: local velocities;  role 2: Euler angles, angle to target;  role 3: contact flags, action / limit sums.
+  static_assert(PP_WARPS == 8 && ENVS == 64, "four roles x two warps x 32 envs");
+  const int role = warp >> 1;
+  const int me = ((warp & 1) << 5) | lane;      // env of this thread inside the CTA (role 0: me == tid)
+  const bool me_ok = me < nenv;
+  EnvObsHead h;
+  h.heading_proj = 0.0f; h.potential = 0.0f;
+  float r[13];
+#pragma unroll
+  for (int j = 0; j < 13; ++j) r[j] = me_ok ? root_s[me * 13 + j] : (j == 6 ? 1.0f : 0.0f);
+  {
+    float* o = obs_s + me * O;
+    const Quat tq = env_torso_quat(r, cfg);
+    if (role == 0) {
+      env_head_heading(r, cfg, tq, h);
+      if (me_ok) { o[10] = h.up_proj; o[11] = h.heading_proj; }
+    } else if (role == 1) {
+      env_head_vel(r, tq, h);
+      if (me_ok) {
+        o[0] = h.height;
+        o[1] = h.vel_loc.x; o[2] = h.vel_loc.y; o[3] = h.vel_loc.z;
+        o[4] = h.angvel_loc.x; o[5] = h.angvel_loc.y; o[6] = h.angvel_loc.z;
+      }
+    } else if (role == 2) {
+      env_head_euler(r, cfg, tq, h);
+      if (me_ok) { o[7] = h.yaw; o[8] = h.roll; o[9] = h.angle_to_target; o[12 + 3 * A] = h.pitch; }
+    } else if (me_ok) {
+      const float* f = force_s + me * FORCE_VALS;
+      float abdomen = 0.0f;
+#pragma unroll
+      for (int b = 0; b < FLYB_NUM_ABDOMEN; ++b) abdomen += (f[b * 3] + f[b * 3 + 1]) + f[b * 3 + 2];
+      int legs = 0, at_limit = 0;
+#pragma unroll
+      for (int b = 0; b < FLYB_NUM_LEGTIPS; ++b) {
+        const float* fr = f + (FLYB_NUM_ABDOMEN + b) * 3;
+        const bool touch = ((fr[0] + fr[1]) + fr[2]) > 0.0f;
+        o[13 + 3 * A + b] = touch ? 1.0f : 0.0f;  // fly.py:797, 803
+        legs += touch ? 1 : 0;
+      }
+      float actions_sq_sum = 0.0f;
+      const float* cmd = o + 12 + 2 * A;
+      for (int k = 0; k < A; ++k) {
+        const float av = cmd[k];
+        actions_sq_sum += av * av;                 // fly.py:731 (the electricity term of fly.py:733 is identically 0)
+        at_limit += (av > s_hi[k] * 0.9f) ? 1 : 0;  // fly.py:736-737
+        at_limit += (av < s_lo[k] * 0.9f) ? 1 : 0;
+      }
+      s_cnt[me] = legs | (at_limit << 8) | ((abdomen > 0.0f ? 1 : 0) << 16);
+      s_sq[me] = actions_sq_sum;
+    }
+  }
+  __syncthreads();
   bool flag = false;
   float my_reward = 0.0f;
-  if (tid < nenv) {
-    const int env = env0 + tid;
-    float r[13];
-#pragma unroll
-    for (int j = 0; j < 13; ++j) r[j] = root_s[tid * 13 + j];
-    const EnvStepOut out = env_post_one(cfg, r, force_s + tid * FORCE_VALS, obs_s + tid * O, pot_in, prog_in, reset_in);
-    potentials[env] = out.potential;
-    prev_potentials[env] = out.prev_potential;
-    progress[env] = out.progress;
-    reset[env] = out.reset;
-    reward[env] = out.reward;
-    if (reward_copy) reward_copy[env] = out.reward;
-    my_reward = out.reward;
-    up_vec[env * 3 + 0] = out.up_vec.x; up_vec[env * 3 + 1] = out.up_vec.y; up_vec[env * 3 + 2] = out.up_vec.z;
-    heading_vec[env * 3 + 0] = out.heading_vec.x; heading_vec[env * 3 + 1] = out.heading_vec.y;
-    heading_vec[env * 3 + 2] = out.heading_vec.z;
-    flag = out.reset != 0;
+  if (role == 0 && me_ok) {
+    const int env = env0 + me;
+    const int packed = s_cnt[me];
+    EnvRewardIn in;
+    in.actions_sq_sum = s_sq[me];
+    in.electricity = 0.0f;
+    in.at_limit = (packed >> 8) & 0xff;
+    in.height = r[2];
+    in.heading_proj = h.heading_proj;
+    in.qz = r[5];
+    in.qw = r[6];
+    in.prev_potential = pot_in;  // fly.py:780
+    in.potential = h.potential;
+    in.legs_touching = packed & 0xff;
+    in.abdomen_hit = (packed >> 16) != 0;
+    long long prog = prog_in + 1;  // fly.py:678
+    if (prog == 0) prog = 1;       // fly.py:415-416
+    in.progress = prog;
+    in.reset_prev = reset_in;
+    float rew;
+    long long rst;
+    env_reward_reset(in, cfg, &rew, &rst);
+    potentials[env] = h.potential;
+    prev_potentials[env] = pot_in;
+    progress[env] = prog;
+    reset[env] = rst;
+    reward[env] = rew;
+    if (reward_copy) reward_copy[env] = rew;
+    my_reward = rew;
+    up_vec[env * 3 + 0] = h.up_vec.x; up_vec[env * 3 + 1] = h.up_vec.y; up_vec[env * 3 + 2] = h.up_vec.z;
+    heading_vec[env * 3 + 0] = h.heading_vec.x; heading_vec[env * 3 + 1] = h.heading_vec.y;
+    heading_vec[env * 3 + 2] = h.heading_vec.z;
+    flag = rst != 0;
   }
-  if (warp < ENVS / 32) {
+  if (role == 0) {
     const unsigned ballot = __ballot_sync(0xffffffffu, flag);
     if (lane == 0) s_mask[warp] = ballot;
     if (reward_sum) {   // score accumulator (ppo.py:233), one atomic per warp

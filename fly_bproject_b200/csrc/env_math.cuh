@@ -63,34 +63,40 @@ struct EnvObsHead {
   float potential;
 };
 
-// root = [pos3, quat4 (xyzw), linvel3, angvel3]  (reference fly.py:95-100)
-FLYB_HD EnvObsHead env_obs_head(const float* root, const FlybEnvCfg& c) {
-  EnvObsHead o;
-  const Vec3 pos = {root[0], root[1], root[2]};
+// root = [pos3, quat4 (xyzw), linvel3, angvel3]  (reference fly.py:95-100).
+// The head of the observation is split in three independent pieces so that the kernel can give each to a different
+// thread of an env; env_obs_head() chains them for the one-thread-per-env users (host emulation, tests).
+FLYB_HD Quat env_torso_quat(const float* root, const FlybEnvCfg& c) {
   const Quat q = {root[3], root[4], root[5], root[6]};
-  const Vec3 lin = {root[7], root[8], root[9]};
-  const Vec3 ang = {root[10], root[11], root[12]};
-
-  // fly.py:778-783
+  const Quat isr = {c.inv_start_rot[0], c.inv_start_rot[1], c.inv_start_rot[2], c.inv_start_rot[3]};
+  return quat_mul(q, isr);
+}
+// potential, compute_heading_and_up (fly.py:778-783, 789-790)
+FLYB_HD void env_head_heading(const float* root, const FlybEnvCfg& c, const Quat& tq, EnvObsHead& o) {
+  const Vec3 pos = {root[0], root[1], root[2]};
   Vec3 tt = {c.target[0] - pos.x, c.target[1] - pos.y, 0.0f};
   const float nrm = sqrtf(tt.x * tt.x + tt.y * tt.y + tt.z * tt.z);
   o.potential = -nrm / c.dt;
-
-  // compute_heading_and_up (fly.py:789-790)
   const float nc = fmaxf(nrm, 1e-9f);
   const Vec3 dir = {tt.x / nc, tt.y / nc, tt.z / nc};
-  const Quat isr = {c.inv_start_rot[0], c.inv_start_rot[1], c.inv_start_rot[2], c.inv_start_rot[3]};
-  const Quat tq = quat_mul(q, isr);
   const Vec3 b1 = {c.basis1[0], c.basis1[1], c.basis1[2]};
   const Vec3 b0 = {c.basis0[0], c.basis0[1], c.basis0[2]};
   o.up_vec = quat_rotate_signed(tq, b1, 1.0f);
   o.heading_vec = quat_rotate_signed(tq, b0, 1.0f);
   o.up_proj = o.up_vec.z;  // up_axis_idx = 2 (fly.py:17)
   o.heading_proj = o.heading_vec.x * dir.x + o.heading_vec.y * dir.y + o.heading_vec.z * dir.z;
-
-  // compute_rot (fly.py:792-793)
+}
+// compute_rot, velocities (fly.py:792-793)
+FLYB_HD void env_head_vel(const float* root, const Quat& tq, EnvObsHead& o) {
+  const Vec3 lin = {root[7], root[8], root[9]};
+  const Vec3 ang = {root[10], root[11], root[12]};
   o.vel_loc = quat_rotate_signed(tq, lin, -1.0f);
   o.angvel_loc = quat_rotate_signed(tq, ang, -1.0f);
+  o.height = root[2];
+}
+// compute_rot, Euler angles and angle to target (fly.py:792-793)
+FLYB_HD void env_head_euler(const float* root, const FlybEnvCfg& c, const Quat& tq, EnvObsHead& o) {
+  const Vec3 pos = {root[0], root[1], root[2]};
   const float sinr_cosp = 2.0f * (tq.w * tq.x + tq.y * tq.z);
   const float cosr_cosp = tq.w * tq.w - tq.x * tq.x - tq.y * tq.y + tq.z * tq.z;
   const float roll = atan2f(sinr_cosp, cosr_cosp);
@@ -107,7 +113,13 @@ FLYB_HD EnvObsHead env_obs_head(const float* root, const FlybEnvCfg& c) {
   // walk_target_angle uses the z component, as upstream
   const float walk_target_angle = atan2f(c.target[2] - pos.z, c.target[0] - pos.x);
   o.angle_to_target = walk_target_angle - o.yaw;
-  o.height = pos.z;
+}
+FLYB_HD EnvObsHead env_obs_head(const float* root, const FlybEnvCfg& c) {
+  EnvObsHead o;
+  const Quat tq = env_torso_quat(root, c);
+  env_head_heading(root, c, tq, o);
+  env_head_vel(root, tq, o);
+  env_head_euler(root, c, tq, o);
   return o;
 }
 
