@@ -245,25 +245,13 @@ FLYB_D void trace_mark(unsigned long long* trace, int& idx, int limit) {
   if (trace != nullptr && blockIdx.x == 0 && idx < limit) trace[idx++] = clock64();
 }
 
-// Per-tile consumer of the results (`Final`), called by the 256 epilogue threads:
-//   begin_tile(s, row0, r, nrows)          after the raw observation tile is in shared memory (s.obs, row-major)
-//   obs_consumed(s)                        after the A operand of layer 1 was built; must arrive on s.obs_empty
-//   early(s, row0, nrows)                  right after the layer-1 operand was handed to the MMA warp
-//   pre_pi(s, row0, r, h, nrows)           before the last accumulator is waited for (mu-independent work)
-//   pi(s, row0, r, h, nrows, mu[32])       both column halves call it with the full mu row (ELU applied)
-//   value(row0, r, nrows, v)               half 0 only
-//   finish(s)                              once, after the last tile
-// Implementations: policy_kernels_tc.cu.
-template <bool WANT_PI, bool WANT_V, class Final>
-FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final& fin) {
-  extern __shared__ unsigned char smem_raw[];
-  const Smem s = carve(smem_raw, a.O, a.out_bytes);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int O = a.O;
-  const long long ntiles = (a.rows + TM - 1) / TM;
-
-  // ---- one-time setup
-  if (threadIdx.x == 0) {
+// Barrier set-up + the first loads of a CTA, issued by the producer warp BEFORE the kernel's other set-up work
+// (tables, biases, TMEM allocation) so that their latency is hidden behind it: all mbarriers are initialised, then the
+// first tile's observation rows and the first NST stages of the weight stream are put in flight.  The producer loop
+// later skips exactly these (it still does its barrier bookkeeping).  Call once, by all 32 lanes of warp
+// PRODUCER_WARP, at kernel start; every other thread must pass a __syncthreads() before touching a barrier.
+FLYB_D void producer_kickoff(const Smem& s, const FwdArgs& a) {
+  if (tc::elect_one()) {
     for (int i = 0; i < NST; ++i) {
       tc::mbar_init(&s.full[i], 1);
       tc::mbar_init(&s.empty[i], 1);
@@ -275,22 +263,82 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
     tc::mbar_init(s.obs_full, 1);
     tc::mbar_init(s.obs_empty, EPI_WARPS);
     tc::fence_mbar_init();
-  }
-  if (warp == MMA_WARP) tc::tmem_alloc(s.tmem_slot, 512);
-  {  // biases + value output row -> shared memory
-    const float* p = a.params;
-    for (int i = threadIdx.x; i < B_TOTAL; i += THREADS) {
-      float v = 0.0f;
-      if (i < B_B2) v = p[net.off[1] + i];
-      else if (i < B_B3PI) v = p[net.off[3] + i - B_B2];
-      else if (i < B_B3V) v = p[net.off[5] + i - B_B3PI];
-      else if (i < B_B4) v = p[net.off[9] + i - B_B3V];
-      else if (i < B_W4V) v = (i - B_B4 < a.A) ? p[net.off[7] + i - B_B4] : 0.0f;
-      else if (i < B_B4V) v = p[net.off[10] + i - B_W4V];
-      else if (i == B_B4V) v = p[net.off[11]];
-      s.bias[i] = v;
+    const long long ntiles = (a.rows + TM - 1) / TM;
+    if ((long long)blockIdx.x < ntiles) {
+      const long long row0 = (long long)blockIdx.x * TM;
+      const int nrows = (int)min((long long)TM, a.rows - row0);
+      const uint32_t bytes = (uint32_t)nrows * (uint32_t)a.O * 4u;
+      const float* src = a.obs + (size_t)row0 * a.O;
+      if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+        tc::mbar_arrive_expect_tx(s.obs_full, bytes);
+        tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
+      }
+      for (int i = 0; i < NST; ++i) {
+        tc::mbar_arrive_expect_tx(&s.full[i], STAGE);
+        tc::tma_load_1d(s.ring + (size_t)i * STAGE, a.wpack + (size_t)i * STAGE, STAGE, &s.full[i]);
+      }
     }
   }
+  __syncwarp();
+}
+
+// biases + the 64 -> 1 value row -> the shared-memory bias block, by `nthreads` cooperating threads
+FLYB_D void load_bias_block(const Smem& s, const FlybNetLayout& net, const float* p, int A, int first, int nthreads) {
+  constexpr int BATCH = 10;   // loads in flight per thread: the block is filled by one warp, latency is what counts
+  for (int i0 = first; i0 < B_TOTAL; i0 += BATCH * nthreads) {
+    float v[BATCH];
+#pragma unroll
+    for (int u = 0; u < BATCH; ++u) {
+      const int i = i0 + u * nthreads;
+      int src = -1;
+      if (i < B_B2) src = net.off[1] + i;
+      else if (i < B_B3PI) src = net.off[3] + i - B_B2;
+      else if (i < B_B3V) src = net.off[5] + i - B_B3PI;
+      else if (i < B_B4) src = net.off[9] + i - B_B3V;
+      else if (i < B_W4V) src = (i - B_B4 < A) ? net.off[7] + i - B_B4 : -1;
+      else if (i < B_B4V) src = net.off[10] + i - B_W4V;
+      else if (i == B_B4V) src = net.off[11];
+      v[u] = src >= 0 ? __ldg(p + src) : 0.0f;
+    }
+#pragma unroll
+    for (int u = 0; u < BATCH; ++u) {
+      const int i = i0 + u * nthreads;
+      if (i < B_TOTAL) s.bias[i] = v[u];
+    }
+  }
+}
+// Late set-up hand-off: the producer warp fills the bias block / the finaliser's tables while the epilogue warps are
+// already splitting the first observation tile; they meet on named barrier 2 before the first bias is read.
+constexpr int SETUP_BAR_THREADS = EPI_THREADS + 32;
+FLYB_D void setup_arrive() {
+  __threadfence_block();
+  asm volatile("bar.arrive 2, %0;" ::"n"(SETUP_BAR_THREADS) : "memory");
+}
+FLYB_D void setup_wait() { asm volatile("bar.sync 2, %0;" ::"n"(SETUP_BAR_THREADS) : "memory"); }
+
+// Per-tile consumer of the results (`Final`), called by the 256 epilogue threads:
+//   setup(lane)                            once, by the 32 lanes of the producer warp: per-kernel tables (any thread
+//                                          may read them after its setup_wait())
+//   begin_tile(s, row0, r, nrows)          after the raw observation tile is in shared memory (s.obs, row-major)
+//   obs_consumed(s)                        after the A operand of layer 1 was built; must arrive on s.obs_empty
+//   early(s, row0, nrows)                  right after the layer-1 operand was handed to the MMA warp
+//   pre_pi(s, row0, r, h, nrows)           before the last accumulator is waited for (mu-independent work)
+//   pi(s, row0, r, h, nrows, mu[32])       both column halves call it with the full mu row (ELU applied)
+//   value(row0, r, nrows, v)               half 0 only
+//   finish(s)                              once, after the last tile
+// Implementations: policy_kernels_tc.cu.
+// KICKED: producer_kickoff() already ran (at the top of the kernel); otherwise it runs here.
+template <bool WANT_PI, bool WANT_V, class Final, bool KICKED = false>
+FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final& fin) {
+  extern __shared__ unsigned char smem_raw[];
+  const Smem s = carve(smem_raw, a.O, a.out_bytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int O = a.O;
+  const long long ntiles = (a.rows + TM - 1) / TM;
+
+  // ---- one-time setup
+  if (!KICKED && warp == PRODUCER_WARP) producer_kickoff(s, a);
+  if (warp == MMA_WARP) tc::tmem_alloc(s.tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -298,23 +346,33 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
 
   if (warp == PRODUCER_WARP) {
     // =========================================================================== TMA producer (warp-uniform)
+    // the first loads are in flight (producer_kickoff): fill the bias block and the finaliser's tables in their shadow
+    load_bias_block(s, net, a.params, a.A, lane, 32);
+    fin.setup(lane);
+    setup_arrive();
     const uint32_t leader = tc::elect_one() ? 1u : 0u;
     const uint32_t ring = tc::smem_u32(s.ring);
     uint32_t gs = 0, obs_phase = 0;
+    int kicked = NST;   // stages (and one observation tile) producer_kickoff() already put in flight
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const long long row0 = tile * TM;
       const int nrows = (int)min((long long)TM, a.rows - row0);
       const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
       const float* src = a.obs + (size_t)row0 * O;
-      tc::mbar_wait_relaxed(s.obs_empty, obs_phase ^ 1u);   // the epilogue warps are done with the previous tile's rows
-      obs_phase ^= 1u;
-      if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
-        tc::mbar_arrive_expect_tx(s.obs_full, bytes);
-        tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
+      // The first tile's rows were requested by producer_kickoff(): no wait for it (the epilogue warps may already
+      // have released that buffer by now — waiting for "the phase before" would then wait for the NEXT release).
+      if (kicked == 0) {
+        tc::mbar_wait_relaxed(s.obs_empty, obs_phase);   // the epilogue warps are done with the previous tile's rows
+        obs_phase ^= 1u;
+        if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
+          tc::mbar_arrive_expect_tx(s.obs_full, bytes);
+          tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
+        }
       }
       auto stream = [&](int first, int count) {
         const unsigned char* g = a.wpack + (size_t)first * STAGE;
         for (int i = 0; i < count; ++i, ++gs, g += STAGE) {
+          if (kicked > 0) { --kicked; continue; }
           const uint32_t slot = gs & (NST - 1);
           tc::mbar_wait_relaxed(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
           const uint32_t bar = tc::smem_u32(&s.full[slot]);
@@ -384,6 +442,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
     const uint32_t lane_base = (uint32_t)q * 32u;
     const int r = q * 32 + lane;   // row inside the tile
     uint32_t pd = 0u, obs_phase = 0u;   // bit b of pd = phase of bar_d[b]
+    bool setup_seen = false;
     int ti = 64;
     unsigned long long* etrace = (threadIdx.x == 0) ? a.trace : nullptr;
     auto wait_d = [&](int b) {
@@ -436,6 +495,10 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       fin.obs_consumed(s);
       arrive_a(0);
       fin.early(s, row0, nrows);   // mu-independent work, overlapped with the first MMAs of the tile
+      if (!setup_seen) {           // bias block + tables are complete from here on
+        setup_wait();
+        setup_seen = true;
+      }
 
       // ---- trunk: 4 chunks of layer 1 -> layer-2 K-chunks (32 columns per thread)
 #pragma unroll 1
@@ -498,6 +561,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       }
       if (WANT_V && !WANT_PI) epi_bar_sync();   // vpart is rewritten by the next tile
     }
+    if (!setup_seen) setup_wait();
     fin.finish(s);
   }
 

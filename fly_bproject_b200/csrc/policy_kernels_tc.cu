@@ -111,6 +111,7 @@ struct FwdFinal {
   float* mu_out;
   float* value_out;
   int A;
+  FLYB_D void setup(int) {}
   FLYB_D void begin_tile(const tcm::Smem&, long long, int, int) {}
   FLYB_D void obs_consumed(const tcm::Smem& s) {
     __syncwarp();
@@ -179,6 +180,8 @@ struct ActFinal {
   float* root;
   float* dof_state;
   const ActTables* t;      // shared memory
+  ActTables* tw;           // the same table, writable by setup()
+  const float* action_var;
   long long rst_raw;       // this row's reset flag, fetched at the start of the tile (consumed at its end)
   unsigned long long* trace;   // debug timeline (slots 128..159), thread 0 of CTA 0
   int ti;
@@ -186,6 +189,41 @@ struct ActFinal {
     if (trace != nullptr && threadIdx.x == 0 && blockIdx.x == 0 && ti < 160) trace[ti++] = clock64();
   }
 
+  // per-kernel tables, built by the 32 lanes of the producer warp while the first tile is being staged
+  FLYB_D void setup(int lane) {
+    ActTables& tab = *tw;
+    for (int k = lane; k < A; k += 32) {
+      tab.std[k] = sqrtf(__ldg(action_var + k));
+      tab.inv_std[k] = 1.0f / tab.std[k];
+      if (has_env) {
+        const int d = cfg->action_idx[k];
+        tab.dof[k] = d;
+        tab.lo[k] = cfg->lower[d];
+        tab.hi[k] = cfg->upper[d];
+      }
+    }
+    if (has_env)
+      for (int d = lane; d < cfg->num_dof; d += 32) {
+        int slot = -1;
+        for (int k = 0; k < A; ++k)
+          if (cfg->action_idx[k] == d) slot = k;
+        tab.slot[d] = slot;
+        tab.init_pos[d] = cfg->initial_pos[d];
+        tab.init_vel[d] = cfg->initial_vel[d];
+      }
+    __syncwarp();
+    if (lane == 0) {
+      float hl = 0.0f;
+      for (int k = 0; k < A; ++k) hl += logf(tab.std[k]);
+      tab.half_log_det = hl;
+      int nf = 0;
+      if (has_env)
+        for (int d = 0; d < cfg->num_dof; ++d)
+          if (tab.slot[d] < 0) tab.free_dof[nf++] = d;
+      tab.n_free = nf;
+    }
+    __syncwarp();
+  }
   FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {
     rst_raw = (has_env && r < nrows) ? reset[row0 + r] : 0;
     if (obs_store) {   // rollout row all_obs[i] = obs (ppo.py:226)
@@ -342,37 +380,7 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
                      const __grid_constant__ ActTcArgs x, const __grid_constant__ FlybEnvCfg cfg) {
   __shared__ ActTables tab;
   const int A = net.num_act;
-  for (int k = threadIdx.x; k < A; k += tcm::THREADS) {
-    tab.std[k] = sqrtf(__ldg(x.action_var + k));
-    tab.inv_std[k] = 1.0f / tab.std[k];
-    if (x.has_env) {
-      const int d = cfg.action_idx[k];
-      tab.dof[k] = d;
-      tab.lo[k] = cfg.lower[d];
-      tab.hi[k] = cfg.upper[d];
-    }
-  }
-  if (x.has_env)
-    for (int d = threadIdx.x; d < cfg.num_dof; d += tcm::THREADS) {
-      int slot = -1;
-      for (int k = 0; k < A; ++k)
-        if (cfg.action_idx[k] == d) slot = k;
-      tab.slot[d] = slot;
-      tab.init_pos[d] = cfg.initial_pos[d];
-      tab.init_vel[d] = cfg.initial_vel[d];
-    }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float hl = 0.0f;
-    for (int k = 0; k < A; ++k) hl += logf(tab.std[k]);
-    tab.half_log_det = hl;
-    int nf = 0;
-    if (x.has_env)
-      for (int d = 0; d < cfg.num_dof; ++d)
-        if (tab.slot[d] < 0) tab.free_dof[nf++] = d;
-    tab.n_free = nf;
-  }
-  __syncthreads();
+  if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[190] = clock64();   // kernel entry
   ActFinal fin;
   fin.noise = x.noise; fin.seed = x.seed;
   fin.draw = x.offset + (x.offset_dev ? __ldg(x.offset_dev) : 0ull);
@@ -381,8 +389,9 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
   fin.cfg = &cfg; fin.has_env = x.has_env;
   fin.actions_scaled = x.actions_scaled; fin.dof_targets = x.dof_targets; fin.reset = x.reset; fin.progress = x.progress;
   fin.potentials = x.potentials; fin.prev_potentials = x.prev_potentials; fin.root = x.root; fin.dof_state = x.dof_state;
-  fin.t = &tab; fin.rst_raw = 0; fin.trace = a.trace; fin.ti = 128;
+  fin.t = &tab; fin.tw = &tab; fin.action_var = x.action_var; fin.rst_raw = 0; fin.trace = a.trace; fin.ti = 128;
   tcm::forward_persistent<true, false>(net, a, fin);
+  if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[191] = clock64();       // kernel exit
 }
 
 // ------------------------------------------------------------------------------------------------ host side

@@ -11,8 +11,8 @@
 //           dM1 = dZmu * W4          dH2 = [dZm1 | dZv1] * [W3pi ; W3v]          dH1 = dZh2 * W2  (two N = 128 halves)
 //       and each epilogue multiplies by ELU'(y) = y > 0 ? 1 : y + 1.  Every dZ is written as a row image too.
 //   ppo_dw_tc_kernel       dW_l = dZ_l^T * X_l: the sample dimension is the MMA's K.  Row images are streamed by bulk
-//       TMA, transposed + hi/lo split by 8 warps into K-major UMMA operands in shared memory (SS MMAs), accumulators
-//       stay in TMEM over all tiles of a CTA; bias gradients come from the same MMAs against a constant ones operand.
+//       TMA, transposed + hi/lo split by 16 warps into K-major UMMA operands in shared memory (SS MMAs), accumulators
+//       stay in TMEM over all tiles of a CTA; bias gradients are exact fp32 column sums taken by the transposers.
 //       CTAs alternate between two roles (layers {2,4} and {1,3}) so that a role's accumulators fit 512 columns.
 //   ppo_reduce_tc_kernel   grad = sum over the per-CTA partials in a fixed order (deterministic), loss.
 //
@@ -112,20 +112,8 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
   const int O = a.O, A = a.A;
   const long long ntiles = (a.rows + TM - 1) / TM;
 
-  // ---- one-time setup
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < NST; ++i) {
-      tc::mbar_init(&s.full[i], 1);
-      tc::mbar_init(&s.empty[i], 1);
-    }
-    tc::mbar_init(&s.bar_a[0], EPI_WARPS);
-    tc::mbar_init(&s.bar_a[1], EPI_WARPS);
-    tc::mbar_init(&s.bar_d[0], 1);
-    tc::mbar_init(&s.bar_d[1], 1);
-    tc::mbar_init(s.obs_full, 1);
-    tc::mbar_init(s.obs_empty, EPI_WARPS);
-    tc::fence_mbar_init();
-  }
+  // ---- one-time setup (barriers + the first loads go out first, see producer_kickoff)
+  if (warp == PRODUCER_WARP) producer_kickoff(s, a);
   if (warp == MMA_WARP) tc::tmem_alloc(s.tmem_slot, 512);
   {
     const float* p = a.params;
@@ -164,19 +152,25 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
     const uint32_t leader = tc::elect_one() ? 1u : 0u;
     const uint32_t ring = tc::smem_u32(s.ring);
     uint32_t gs = 0, obs_phase = 0;
+    int kicked = NST;   // stages (and one observation tile) producer_kickoff() already put in flight
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const long long row0 = tile * TM;
       const int nrows = (int)min((long long)TM, a.rows - row0);
       const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
       const float* src = a.obs + (size_t)row0 * O;
-      tc::mbar_wait_relaxed(s.obs_empty, obs_phase ^ 1u);
-      obs_phase ^= 1u;
-      if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
-        tc::mbar_arrive_expect_tx(s.obs_full, bytes);
-        tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
+      // The first tile's rows were requested by producer_kickoff(): no wait for it (the epilogue warps may already
+      // have released that buffer by now — waiting for "the phase before" would then wait for the NEXT release).
+      if (kicked == 0) {
+        tc::mbar_wait_relaxed(s.obs_empty, obs_phase);   // the epilogue warps are done with the previous tile's rows
+        obs_phase ^= 1u;
+        if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
+          tc::mbar_arrive_expect_tx(s.obs_full, bytes);
+          tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
+        }
       }
       const unsigned char* g = a.wpack;
       for (int i = 0; i < ALL_STAGES; ++i, ++gs, g += STAGE) {
+        if (kicked > 0) { --kicked; continue; }
         const uint32_t slot = gs & (NST - 1);
         tc::mbar_wait_relaxed(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
         const uint32_t bar = tc::smem_u32(&s.full[slot]);

@@ -27,3 +27,4 @@ t0 = min(x for x in t if x > 0)
 print("MMA thread :", [x - t0 for x in t[:64] if x > 0])
 print("epilogue w0:", [x - t0 for x in t[64:128] if x > 0])
 print("finaliser  :", [x - t0 for x in t[128:160] if x > 0])
+print("kernel entry / exit (thread 0):", t[190] - t0, t[191] - t0)
