@@ -284,7 +284,7 @@ FLYB_D void producer_kickoff(const Smem& s, const FwdArgs& a) {
 
 // biases + the 64 -> 1 value row -> the shared-memory bias block, by `nthreads` cooperating threads
 FLYB_D void load_bias_block(const Smem& s, const FlybNetLayout& net, const float* p, int A, int first, int nthreads) {
-  constexpr int BATCH = 10;   // loads in flight per thread: the block is filled by one warp, latency is what counts
+  constexpr int BATCH = 20;   // loads in flight per thread: the block is filled by one warp, latency is what counts
   for (int i0 = first; i0 < B_TOTAL; i0 += BATCH * nthreads) {
     float v[BATCH];
 #pragma unroll

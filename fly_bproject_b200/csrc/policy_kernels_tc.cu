@@ -146,8 +146,7 @@ struct ActTables {
   float std[FLYB_MAX_DOF];      // sqrt(action_var[k])
   float inv_std[FLYB_MAX_DOF];
   int dof[FLYB_MAX_DOF];        // action k -> DOF it drives (cfg.action_idx)
-  int free_dof[FLYB_MAX_DOF];   // DOFs no action drives (they keep initial_pos as target, fly.py:626)
-  int n_free;
+  float log_std[FLYB_MAX_DOF];
   float lo[FLYB_MAX_DOF];       // lower limit of the DOF action k drives
   float hi[FLYB_MAX_DOF];
   float init_pos[FLYB_MAX_DOF]; // per DOF
@@ -195,6 +194,7 @@ struct ActFinal {
     for (int k = lane; k < A; k += 32) {
       tab.std[k] = sqrtf(__ldg(action_var + k));
       tab.inv_std[k] = 1.0f / tab.std[k];
+      tab.log_std[k] = logf(tab.std[k]);
       if (has_env) {
         const int d = cfg->action_idx[k];
         tab.dof[k] = d;
@@ -214,13 +214,8 @@ struct ActFinal {
     __syncwarp();
     if (lane == 0) {
       float hl = 0.0f;
-      for (int k = 0; k < A; ++k) hl += logf(tab.std[k]);
+      for (int k = 0; k < A; ++k) hl += tab.log_std[k];   // same summation order as the CUDA-core path
       tab.half_log_det = hl;
-      int nf = 0;
-      if (has_env)
-        for (int d = 0; d < cfg->num_dof; ++d)
-          if (tab.slot[d] < 0) tab.free_dof[nf++] = d;
-      tab.n_free = nf;
     }
     __syncwarp();
   }
