@@ -361,3 +361,18 @@ def test_run_loop_matches_oracle_rollout_and_update():
         assert torch.equal(env.reset_buf.cpu(), s.reset_buf)
         torch.testing.assert_close(agent.action_var.cpu(), var, rtol=1e-6, atol=0)
     assert agent.mini_batch_number == 3 and agent.run_step == 3
+
+
+def test_ppo_grad_is_deterministic():
+    """Fixed-order partial reduction, no float atomics: the same minibatch gives bit-identical gradients and loss."""
+    g = load_golden("ppo_n64_t32.npz")
+    n, t_roll, mc = [int(x) for x in g["meta"]]
+    net = golden_net(g)
+    big = {k: (v.repeat(1, 40, 1) if v.dim() == 3 else v.repeat(1, 40)) for k, v in g.items()
+           if k in ("roll_obs", "roll_acts", "roll_logp", "roll_target", "roll_adv")}
+    outs = []
+    for _ in range(3):
+        grad, loss, *_ = _grad_step(net, big, 0, mc, g["roll_var"])
+        outs.append((grad.clone(), loss.clone()))
+    for grad, loss in outs[1:]:
+        assert torch.equal(grad, outs[0][0]) and torch.equal(loss, outs[0][1])
