@@ -330,13 +330,13 @@ def run_own(args):
             p(agent.all_acts[0:agent.mini_chunk_size]), p(agent.all_log_prob[0:agent.mini_chunk_size]),
             p(agent._target[0:agent.mini_chunk_size]), p(agent.all_advantage[0:agent.mini_chunk_size]),
             p(agent.action_var), agent.mini_chunk_size * NUM_ENVS, p(agent.grad), p(agent.loss), agent._ws_ptr,
-            _lib.current_stream()))
+            None, _lib.current_stream()))
 
     kt = {}
     for name, fn, iters in [("post_physics", k_env, 4 * POOL), ("policy_act", k_act, 4 * POOL), ("gae_scan", k_gae, 32),
                             ("value_forward", k_vfwd, 4), ("ppo_grad", k_gradonly, 8),
                             ("ppo_minibatch_step", k_grad, 8)]:
-        if world > 1 and name == "ppo_minibatch_step":   # contains the NCCL all-reduce: timed eagerly, not captured
+        if world > 1 and name == "ppo_minibatch_step" and agent._peers is None:   # NCCL all-reduce: not captured
             fn(0)
             kt[name] = cuda_time_ms(fn, iters)
         else:
@@ -424,7 +424,7 @@ def run_own(args):
                        "env_steps_per_bench_step": NUM_ENVS * HORIZON,
                        "l2": f"inputs larger than L2: pool of {POOL} synthetic states = {env.state.pool_bytes / 1e6:.0f} MB, "
                              "rotated every env-step", "parallelism": f"dp{world} (independent env shards; gradient "
-                             "all-reduce in the update only)", "rng": "in-kernel Philox4x32-10"},
+                             "sum in the update only)", "rng": "in-kernel Philox4x32-10"},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "steps": ke, "api": "PPO.run() per env-step, state tensors from pinned host memory"},
@@ -432,7 +432,8 @@ def run_own(args):
             "update": {"metric": "ppo_update_samples_per_sec", "value": upd_value, "unit": "samples/s",
                        "ms_per_update": upd_ms, "optimiser_steps": n_minibatches, "samples_per_step": rows_mb,
                        "includes": "value forward over (T+1)N rows + GAE scan + 75 x (fwd/bwd/clip/Adam)" +
-                                   (" + NCCL all-reduce" if world > 1 else "")},
+                                   ("" if world == 1 else " + NCCL all-reduce" if agent._peers is None else
+                                    " with the gradient sum over NVLink peer memory inside the reduce/norm kernels")},
         }
         if cpu_val is not None:
             line["cpu_baseline"] = {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port",
@@ -440,6 +441,7 @@ def run_own(args):
                                               f"{cpu_per * 1e3:.1f} ms/step"}
         print(json.dumps(line), flush=True)
     if world > 1:
+        agent.exit()            # unmaps the peers' exchange buffers (collective)
         dist.destroy_process_group()
 
 

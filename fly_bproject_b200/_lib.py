@@ -35,6 +35,15 @@ class EnvCfg(C.Structure):
     ]
 
 
+MAX_PEERS = 8
+
+
+class PeerGroup(C.Structure):
+    """FlybPeerGroup: the ranks' gradient-exchange buffers as mapped in this process."""
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("total_pad", C.c_int32), ("_pad", C.c_int32),
+                ("base", C.c_void_p * MAX_PEERS)]
+
+
 class StepTail(C.Structure):
     _fields_ = [("action_var", C.c_void_p), ("num_act", C.c_int32), ("decay", C.c_float), ("floor", C.c_float),
                 ("step_counter", C.c_void_p)]
@@ -68,8 +77,16 @@ SIGNATURES = {
     "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, _P]),
     "flyb_gae": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, _P]),
     "flyb_ppo_workspace_bytes": (C.c_size_t, [C.POINTER(NetLayout), C.c_int64]),
-    "flyb_ppo_grad": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 8 + [C.c_int64] + [_P] * 4),
-    "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5 + [C.c_float, _P, _P, _P, _P]),
+    "flyb_ppo_grad": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 8 + [C.c_int64] + [_P] * 3
+                      + [C.POINTER(PeerGroup), _P]),
+    "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5
+                       + [C.c_float, _P, _P, _P, C.POINTER(PeerGroup), _P]),
+    "flyb_peer_total_pad": (C.c_int32, [C.c_int32]),
+    "flyb_peer_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "flyb_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), _P]),
+    "flyb_peer_open": (C.c_int, [_P, C.POINTER(C.c_void_p)]),
+    "flyb_peer_close": (C.c_int, [_P]),
+    "flyb_peer_free": (C.c_int, [_P]),
     "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P, _P]),
 }
 
@@ -89,7 +106,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)  # AttributeError if the .so does not export it
             fn.restype = restype
             fn.argtypes = argtypes
-        if handle.flyb_abi_version() != 4:
+        if handle.flyb_abi_version() != 5:
             raise FlybError("libflyb200.so ABI version mismatch")
         _lib = handle
     return _lib

@@ -214,9 +214,11 @@ class PPO:
 
         # data-parallel: one process per GPU, the only collective is the gradient all-reduce
         self.rank, self.world_size = dp.world()
+        self._peers = None                  # dp.PeerExchange: gradient sum by the library's own kernels over NVLink
         if self.world_size > 1:
             dp.broadcast_params_(self.net.flat, src=0)
             self.net.repack()
+            self._peers = dp.make_exchange(self.net.layout.total, dev)
 
     # ------------------------------------------------------------------ reference-compatible views
     @property
@@ -341,14 +343,18 @@ class PPO:
         p, stream = _lib.ptr, _lib.current_stream()
         rows = (j - k) * self.num_envs
         lay = C.byref(self.net.layout)
+        peers = self._peers.byref() if self._peers is not None else None
         _lib.check(self.lib.flyb_ppo_grad(
             lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.net.wpack), p(self._obs_ring[k:j]), p(self.all_acts[k:j]),
             p(self.all_log_prob[k:j]), p(self._target[k:j]), p(self.all_advantage[k:j]), p(self.action_var), rows,
-            p(self.grad), p(self.loss), self._ws_ptr, stream), "flyb_ppo_grad")
-        grad_scale = dp.grad_all_reduce_(self.grad)          # SUM over ranks; the mean is taken by grad_scale
+            p(self.grad), p(self.loss), self._ws_ptr, peers, stream), "flyb_ppo_grad")
+        if peers is None:
+            grad_scale = dp.grad_all_reduce_(self.grad)      # SUM over ranks (NCCL); the mean is taken by grad_scale
+        else:
+            grad_scale = 1.0 / self.world_size               # the sum happens inside flyb_ppo_apply's first kernel
         _lib.check(self.lib.flyb_ppo_apply(
             lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.grad), p(self.exp_avg), p(self.exp_avg_sq),
-            p(self.adam_step), grad_scale, p(self.grad_norm), self._ws_ptr, p(self.net.wpack), stream),
+            p(self.adam_step), grad_scale, p(self.grad_norm), self._ws_ptr, p(self.net.wpack), peers, stream),
             "flyb_ppo_apply")
 
     def _update_body(self) -> int:
@@ -363,9 +369,10 @@ class PPO:
         return steps
 
     def update(self, use_graph: bool = False) -> None:
-        # data-parallel runs keep the NCCL all-reduce out of graph capture (the kernels are enqueued eagerly; the
-        # host stays ahead of the device because one optimiser step is ~170 us of GPU work)
-        if not use_graph or self.world_size > 1:
+        # a data-parallel run over NCCL keeps the all-reduce out of graph capture (kernels enqueued eagerly; the host
+        # stays ahead of the device because one optimiser step is ~170 us of GPU work); with the peer exchange the
+        # whole update is the library's own stream-ordered kernels and is captured like the single-GPU one
+        if not use_graph or (self.world_size > 1 and self._peers is None):
             self.optim_step += self._update_body()
             return
         g = self._graphs.get("update")
@@ -391,4 +398,7 @@ class PPO:
         self.env.generate_video()
 
     def exit(self) -> None:
+        if self._peers is not None:
+            self._peers.close()
+            self._peers = None
         self.env.exit()

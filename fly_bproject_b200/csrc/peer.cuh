@@ -1,0 +1,97 @@
+// Gradient exchange over NVLink peer memory: device-side helpers shared by the reducing kernels (push) and the norm
+// kernel (wait + sum).  Protocol and buffer layout: include/flyb200.h, FlybPeerGroup.
+#pragma once
+#include "flyb_common.cuh"
+
+namespace flyb {
+
+struct PeerView {   // FlybPeerGroup resolved into typed pointers (kernel argument)
+  int rank, world, total_pad;
+  float* slots[FLYB_MAX_PEERS];        // slots[r]: [2][world][total_pad] in rank r's buffer
+  uint32_t* flags[FLYB_MAX_PEERS];     // flags[r]: [FLYB_MAX_PEERS] in rank r's buffer
+  uint32_t* epoch;                     // own
+  uint32_t* ticket;                    // own
+};
+
+inline size_t peer_slots_bytes(int total_pad, int world) { return (size_t)2 * world * total_pad * sizeof(float); }
+constexpr size_t PEER_CTRL_BYTES = 256;   // flags[8], epoch, ticket
+
+inline PeerView make_peer_view(const FlybPeerGroup& g) {
+  PeerView v{};
+  v.rank = g.rank; v.world = g.world; v.total_pad = g.total_pad;
+  const size_t sb = peer_slots_bytes(g.total_pad, g.world);
+  for (int r = 0; r < g.world; ++r) {
+    v.slots[r] = (float*)g.base[r];
+    v.flags[r] = (uint32_t*)((char*)g.base[r] + sb);
+  }
+  v.epoch = v.flags[g.rank] + FLYB_MAX_PEERS;
+  v.ticket = v.epoch + 1;
+  return v;
+}
+
+FLYB_D uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+FLYB_D void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+FLYB_D float ld_relaxed_sys(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Entry i of this rank's gradient -> slot [parity][rank] of every rank (own one included).
+FLYB_D void peer_push(const PeerView& pv, uint32_t parity, int i, float val) {
+  const size_t at = ((size_t)parity * pv.world + pv.rank) * pv.total_pad + i;
+#pragma unroll
+  for (int r = 0; r < FLYB_MAX_PEERS; ++r)
+    if (r < pv.world) pv.slots[r][at] = val;
+}
+
+// Called by every thread of a pushing CTA after its last peer_push.  The last CTA of the grid raises this rank's
+// flag on every rank and bumps the local epoch; `epoch_before` is the value every CTA read at its start.
+FLYB_D void peer_push_done(const PeerView& pv, uint32_t epoch_before) {
+  __threadfence_system();          // this thread's remote stores before anything that follows, system-wide
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t t = atomicAdd(pv.ticket, 1u);
+    if (t == gridDim.x * gridDim.y - 1) {
+      __threadfence_system();      // every CTA's stores (ordered before its ticket) before the flags
+      *pv.ticket = 0;
+      *pv.epoch = epoch_before + 1;
+      for (int r = 0; r < pv.world; ++r) st_release_sys(pv.flags[r] + pv.rank, epoch_before + 1);
+    }
+  }
+}
+
+// Wait until every rank has pushed epoch `want` into this rank's buffer.  One polling lane per source rank; gives
+// up after ~4 s of spinning (a dead peer must not hang the GPU) and traps.
+FLYB_D void peer_wait_all(const PeerView& pv, uint32_t want) {
+  if (threadIdx.x < pv.world) {
+    const uint32_t* f = pv.flags[pv.rank] + threadIdx.x;
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(f) - want) < 0) {
+      __nanosleep(64);
+      if (clock64() - t0 > 8000000000LL) {
+        printf("flyb200: rank %d gave up waiting for rank %d (epoch %u)\n", pv.rank, (int)threadIdx.x, want);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// Sum of entry i over the ranks' slots, in rank order.
+FLYB_D float peer_sum(const PeerView& pv, uint32_t parity, int i) {
+  const float* s = pv.slots[pv.rank] + (size_t)parity * pv.world * pv.total_pad + i;
+  float acc = ld_relaxed_sys(s);
+  for (int r = 1; r < pv.world; ++r) acc += ld_relaxed_sys(s + (size_t)r * pv.total_pad);
+  return acc;
+}
+
+int peer_validate(const FlybPeerGroup* g, int total);
+
+}  // namespace flyb

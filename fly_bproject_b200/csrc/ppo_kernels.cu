@@ -13,6 +13,7 @@
 //   ppo_norm_kernel / ppo_adam_kernel   clip_grad_norm_ (ppo.py:198) + torch.optim.Adam.step (ppo.py:199).
 #include <algorithm>
 
+#include "peer.cuh"
 #include "mlp_simt.cuh"
 
 namespace flyb {
@@ -25,10 +26,10 @@ size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows);
 int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                 const float* obs, const float* action, const float* old_logp, const float* target,
                 const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
-                void* workspace, cudaStream_t st);
+                void* workspace, const FlybPeerGroup* peers, cudaStream_t st);
 
 constexpr int DW_SPLITS_MAX = 64;
-constexpr int NORM_BLOCKS = 64;
+constexpr int NORM_BLOCKS = 256;
 
 struct PpoWs {   // device pointers into the caller's workspace
   float *h1, *h2, *m1, *v1;            // layer inputs saved by the forward
@@ -327,14 +328,19 @@ ppo_dw_kernel(const __grid_constant__ DwArgs a, float* __restrict__ dw_part) {
   }
 }
 
+template <bool PEERS>
 __global__ void __launch_bounds__(256)
 ppo_reduce_kernel(const float* __restrict__ dw_part, int splits, int total, float* __restrict__ grad,
-                  const float* __restrict__ loss_part, long long ntiles, float inv_rows, float* __restrict__ loss) {
+                  const float* __restrict__ loss_part, long long ntiles, float inv_rows, float* __restrict__ loss,
+                  const __grid_constant__ PeerView pv) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t epoch = 0;
+  if (PEERS) epoch = *(volatile const uint32_t*)pv.epoch;
   if (i < total) {
     float g = 0.0f;
     for (int s2 = 0; s2 < splits; ++s2) g += dw_part[(size_t)s2 * total + i];
     grad[i] = g;
+    if (PEERS) peer_push(pv, epoch & 1u, i, g);
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
     float x = 0.0f, y = 0.0f;
@@ -346,16 +352,33 @@ ppo_reduce_kernel(const float* __restrict__ dw_part, int splits, int total, floa
     y = warp_sum(y);
     if (threadIdx.x == 0) *loss = -x * inv_rows + y * inv_rows;
   }
+  if (PEERS) peer_push_done(pv, epoch);
 }
 
 // ------------------------------------------------------------------------------------------ clip + Adam
+// With PEERS the kernel first completes the data-parallel sum: it waits for every rank's push of this epoch, adds
+// the `world` slots in rank order and stores the result to `grad` (what ppo_adam_kernel reads).
+template <bool PEERS>
 __global__ void __launch_bounds__(256)
-ppo_norm_kernel(const float* __restrict__ grad, int total, float scale, float* __restrict__ norm_part,
-                long long* __restrict__ step) {
+ppo_norm_kernel(float* __restrict__ grad, int total, float scale, float* __restrict__ norm_part,
+                long long* __restrict__ step, const __grid_constant__ PeerView pv) {
   __shared__ float red[8];
+  uint32_t parity = 0;
+  if (PEERS) {
+    const uint32_t epoch = *(volatile const uint32_t*)pv.epoch;   // pushes done by this rank, the last one just now
+    peer_wait_all(pv, epoch);
+    parity = (epoch - 1u) & 1u;
+  }
   float acc = 0.0f;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
-    const float g = grad[i] * scale;
+    float g;
+    if (PEERS) {
+      g = peer_sum(pv, parity, i);
+      grad[i] = g;
+    } else {
+      g = grad[i];
+    }
+    g *= scale;
     acc = fmaf(g, g, acc);
   }
   acc = warp_sum(acc);
@@ -380,18 +403,21 @@ ppo_adam_kernel(float* __restrict__ params, float* __restrict__ grad, float* __r
                 const long long* __restrict__ step, const __grid_constant__ AdamArgs a,
                 float* __restrict__ grad_norm_out) {
   __shared__ float s_coef, s_step_size, s_bc2_sqrt;
-  if (threadIdx.x == 0) {
-    float t = 0.0f;
-    for (int i = 0; i < NORM_BLOCKS; ++i) t += norm_part[i];
-    const float total_norm = sqrtf(t);
-    // torch.nn.utils.clip_grad_norm_: clip_coef = max_norm / (total_norm + 1e-6), clamped to 1.0
-    s_coef = fminf((float)a.max_norm / (total_norm + 1e-6f), 1.0f);
-    const double tstep = (double)*step;
-    const double bc1 = 1.0 - pow(a.beta1, tstep);
-    const double bc2 = 1.0 - pow(a.beta2, tstep);
-    s_step_size = (float)(a.lr / bc1);
-    s_bc2_sqrt = (float)sqrt(bc2);
-    if (blockIdx.x == 0 && grad_norm_out) *grad_norm_out = total_norm;
+  if (threadIdx.x < 32) {
+    float t = 0.0f;   // fixed order: lane l adds partials l, l + 32, ...; then the butterfly
+    for (int i = threadIdx.x; i < NORM_BLOCKS; i += 32) t += norm_part[i];
+    t = warp_sum(t);
+    if (threadIdx.x == 0) {
+      const float total_norm = sqrtf(t);
+      // torch.nn.utils.clip_grad_norm_: clip_coef = max_norm / (total_norm + 1e-6), clamped to 1.0
+      s_coef = fminf((float)a.max_norm / (total_norm + 1e-6f), 1.0f);
+      const double tstep = (double)*step;
+      const double bc1 = 1.0 - pow(a.beta1, tstep);
+      const double bc2 = 1.0 - pow(a.beta2, tstep);
+      s_step_size = (float)(a.lr / bc1);
+      s_bc2_sqrt = (float)sqrt(bc2);
+      if (blockIdx.x == 0 && grad_norm_out) *grad_norm_out = total_norm;
+    }
   }
   __syncthreads();
   const float coef = s_coef, step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
@@ -427,7 +453,7 @@ extern "C" size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t row
 extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                              const float* obs, const float* action, const float* old_logp, const float* target,
                              const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
-                             void* workspace, void* stream) {
+                             void* workspace, const FlybPeerGroup* peers, void* stream) {
   int rc = validate_net(net, params);
   if (rc != FLYB_OK) return rc;
   FLYB_REQUIRE(cfg && obs && action && old_logp && target && advantage && action_var && grad && loss && workspace,
@@ -435,10 +461,11 @@ extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, co
   FLYB_REQUIRE(rows > 0, "flyb_ppo_grad: rows must be > 0");
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_grad: workspace must be 256-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
+  if (peers && (rc = peer_validate(peers, net->total)) != FLYB_OK) return rc;
   if (wpack) {   // tensor-core path (ppo_kernels_tc.cu)
     FLYB_REQUIRE(tc_supported(net), "flyb_ppo_grad: wpack given but the tensor-core path does not cover this shape");
     return tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
-                       workspace, st);
+                       workspace, peers, st);
   }
   const PpoWs w = carve_ws(*net, rows, workspace);
 
@@ -488,22 +515,34 @@ extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, co
   if (rc != FLYB_OK) return rc;
   ppo_dw_kernel<<<dim3(d.total_tiles, w.splits), 256, 0, st>>>(d, w.dw_part);
   FLYB_LAUNCH_CHECK("ppo_dw_kernel");
-  ppo_reduce_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(w.dw_part, w.splits, net->total, grad, w.loss_part,
-                                                              w.ntiles, a.inv_rows, loss);
+  if (peers)
+    ppo_reduce_kernel<true><<<(net->total + 255) / 256, 256, 0, st>>>(w.dw_part, w.splits, net->total, grad, w.loss_part,
+                                                                      w.ntiles, a.inv_rows, loss, make_peer_view(*peers));
+  else
+    ppo_reduce_kernel<false><<<(net->total + 255) / 256, 256, 0, st>>>(w.dw_part, w.splits, net->total, grad,
+                                                                       w.loss_part, w.ntiles, a.inv_rows, loss, PeerView{});
   FLYB_LAUNCH_CHECK("ppo_reduce_kernel");
   return FLYB_OK;
 }
 
 extern "C" int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad,
                               float* exp_avg, float* exp_avg_sq, int64_t* step, float grad_scale,
-                              float* grad_norm_out, void* workspace, void* wpack, void* stream) {
+                              float* grad_norm_out, void* workspace, void* wpack, const FlybPeerGroup* peers,
+                              void* stream) {
   int rc = validate_net(net, params);
   if (rc != FLYB_OK) return rc;
   FLYB_REQUIRE(cfg && grad && exp_avg && exp_avg_sq && step && workspace, "flyb_ppo_apply: NULL argument");
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_apply: workspace must be 256-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   float* norm_part = (float*)workspace;   // first slot of the PPO workspace (see carve_ws)
-  ppo_norm_kernel<<<NORM_BLOCKS, 256, 0, st>>>(grad, net->total, grad_scale, norm_part, (long long*)step);
+  if (peers) {
+    if ((rc = peer_validate(peers, net->total)) != FLYB_OK) return rc;
+    ppo_norm_kernel<true><<<NORM_BLOCKS, 256, 0, st>>>(grad, net->total, grad_scale, norm_part, (long long*)step,
+                                                       make_peer_view(*peers));
+  } else {
+    ppo_norm_kernel<false><<<NORM_BLOCKS, 256, 0, st>>>(grad, net->total, grad_scale, norm_part, (long long*)step,
+                                                        PeerView{});
+  }
   FLYB_LAUNCH_CHECK("ppo_norm_kernel");
   AdamArgs a{cfg->lr, cfg->beta1, cfg->beta2, cfg->eps, cfg->max_grad_norm, grad_scale};
   ppo_adam_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(params, grad, exp_avg, exp_avg_sq, net->total, norm_part,

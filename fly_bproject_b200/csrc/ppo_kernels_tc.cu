@@ -29,6 +29,7 @@
 #include <cstdlib>
 
 #include "mlp_tc.cuh"
+#include "peer.cuh"
 
 namespace flyb {
 
@@ -833,25 +834,39 @@ struct ReduceArgs {
   float inv_rows;
 };
 constexpr int RED_ELEMS = 64, RED_GROUPS = 4;   // 256 threads: 64 gradient entries x 4 interleaved partial groups
+template <bool PEERS>
 __global__ void __launch_bounds__(RED_ELEMS * RED_GROUPS)
 ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restrict__ dw_part,
-                     const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss) {
+                     const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss,
+                     const __grid_constant__ PeerView pv) {
   __shared__ float s_acc[RED_GROUPS][RED_ELEMS];
   const int e = threadIdx.x & (RED_ELEMS - 1), pg = threadIdx.x / RED_ELEMS;
-  const int i = blockIdx.x * RED_ELEMS + e;
-  float acc = 0.0f;
-  if (i < a.total) {
-    bool valid = false;
+  uint32_t epoch = 0;
+  if (PEERS) epoch = *(volatile const uint32_t*)pv.epoch;   // bumped by the grid's last CTA, after every CTA read it
+  // one group of 64 entries per CTA without peers; with peers a one-wave grid walks the groups, so that the
+  // system-scope fence behind the remote stores is paid once per CTA
+  const int ngroups = (a.total + RED_ELEMS - 1) / RED_ELEMS;
+  for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
+    const int i = grp * RED_ELEMS + e;
+    float acc = 0.0f;
+    if (i < a.total) {
+      bool valid = false;
 #pragma unroll
-    for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= a.off[sg] && i < a.off[sg] + a.size[sg]);
-    if (valid) {   // group pg sums partials pg, pg + 4, ... in order; the groups are combined in a fixed order below
+      for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= a.off[sg] && i < a.off[sg] + a.size[sg]);
+      if (valid) {   // group pg sums partials pg, pg + 4, ... in order; the groups are combined in a fixed order below
 #pragma unroll 8
-      for (int p = pg; p < a.nparts; p += RED_GROUPS) acc += dw_part[(size_t)p * a.total + i];
+        for (int p = pg; p < a.nparts; p += RED_GROUPS) acc += dw_part[(size_t)p * a.total + i];
+      }
     }
+    s_acc[pg][e] = acc;
+    __syncthreads();
+    if (pg == 0 && i < a.total) {
+      const float g = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
+      grad[i] = g;
+      if (PEERS) peer_push(pv, epoch & 1u, i, g);   // posted NVLink stores into every rank's slot of this rank
+    }
+    if (PEERS) __syncthreads();                     // s_acc is reused by the next group
   }
-  s_acc[pg][e] = acc;
-  __syncthreads();
-  if (pg == 0 && i < a.total) grad[i] = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
     float x = 0.0f, y = 0.0f;
     for (int t = threadIdx.x; t < a.nloss; t += 32) {
@@ -862,6 +877,7 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
     y = warp_sum(y);
     if (threadIdx.x == 0) *loss = -x * a.inv_rows + y * a.inv_rows;
   }
+  if (PEERS) peer_push_done(pv, epoch);
 }
 
 struct Ws {
@@ -889,7 +905,7 @@ static Ws carve_ws(const FlybNetLayout& net, long long rows, void* basep) {
   const int sms = num_sms();
   w.grid1 = (int)std::min<long long>(ntiles, sms);
   w.ctas_per_role = (int)std::max<long long>(1, std::min<long long>(ntiles, sms / 2));
-  w.norm_part = take(64);
+  w.norm_part = take(256);   // NORM_BLOCKS floats (ppo_kernels.cu)
   w.im.x = take(R * F_X); w.im.h1 = take(R * F_H1); w.im.h2 = take(R * F_H2); w.im.mv = take(R * F_MV);
   w.im.dzmuv = take(R * F_DZMUV + 4096);   // + slack: the M = 128 MMA of the 64-feature operand never reads it, TMA does not either
   w.im.dzmv = take(R * F_DZMV); w.im.dzh2 = take(R * F_DZH2); w.im.dzh1 = take(R * F_DZH1);
@@ -909,7 +925,7 @@ size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows) {
 int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                 const float* obs, const float* action, const float* old_logp, const float* target,
                 const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
-                void* workspace, cudaStream_t st) {
+                void* workspace, const FlybPeerGroup* peers, cudaStream_t st) {
   using namespace tcb;
   const Ws w = carve_ws(*net, rows, workspace);
   const long long ntiles = (rows + TM - 1) / TM;
@@ -949,7 +965,13 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
   for (int i = 0; i < 12; ++i) { r.off[i] = net->off[i]; r.size[i] = sizes[i]; }
   r.total = net->total; r.nparts = w.ctas_per_role; r.nloss = w.grid1; r.inv_rows = ga.inv_rows;
-  ppo_reduce_tc_kernel<<<(net->total + RED_ELEMS - 1) / RED_ELEMS, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss);
+  const int red_grid = (net->total + RED_ELEMS - 1) / RED_ELEMS;
+  if (peers)
+    ppo_reduce_tc_kernel<true><<<std::min(red_grid, 4 * num_sms()), RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+                                                                            make_peer_view(*peers));
+  else
+    ppo_reduce_tc_kernel<false><<<red_grid, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+                                                                             PeerView{});
   FLYB_LAUNCH_CHECK("ppo_reduce_tc_kernel");
   return FLYB_OK;
 }

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FLYB_ABI_VERSION 4
+#define FLYB_ABI_VERSION 5
 #define FLYB_MAX_DOF 64      /* asset DOF count D: 18 (nmf_no_limits_limited_Dofs.urdf) or 42 (nmf_no_limits.urdf) */
 #define FLYB_NUM_ABDOMEN 5   /* reference fly.py:299 */
 #define FLYB_NUM_LEGTIPS 6   /* reference fly.py:300 */
@@ -177,25 +177,57 @@ int flyb_net_forward(const FlybNetLayout* net, const float* params, const void* 
 int flyb_gae(const float* reward, const float* values, const int64_t* reset_last, int32_t horizon, int32_t num_envs,
              float gamma, float lmbda, float* target, float* advantage, void* stream);
 
+/* ---- data-parallel gradient exchange over NVLink peer memory (the one collective of the path).
+ * One process per GPU.  Every rank allocates one exchange buffer with flyb_peer_alloc, publishes its 64-byte IPC
+ * handle to the other ranks (any side channel; the Python host uses torch.distributed.all_gather_object), maps the
+ * others' buffers with flyb_peer_open and fills a FlybPeerGroup.  With a group,
+ *   flyb_ppo_grad  : its last kernel (the fixed-order reduction of the per-CTA partial gradients) stores every
+ *                    gradient entry straight into slot [epoch & 1][rank] of EVERY rank's buffer (posted NVLink
+ *                    writes), and the last CTA to finish raises this rank's flag on every rank;
+ *   flyb_ppo_apply : its first kernel (global norm) waits for all ranks' flags of this epoch, sums the `world` slots
+ *                    in rank order (bit-identical on every rank), writes `grad` and goes on as usual.
+ * No kernel waits for a peer except that norm kernel, and the peers' pushing kernels never wait: no dead-lock however
+ * CTAs are scheduled.  Slots are double-buffered by epoch parity: a rank can be at most one push ahead of the
+ * slowest one.  Everything is stream-ordered device code: a whole data-parallel update is CUDA-graph capturable.
+ * Layout of a buffer of flyb_peer_bytes(total, world) bytes (zero-filled by flyb_peer_alloc):
+ *   float slots[2][world][total_pad]; uint32 flags[FLYB_MAX_PEERS] (one epoch per source rank); uint32 epoch; uint32 ticket. */
+#define FLYB_MAX_PEERS 8
+typedef struct FlybPeerGroup {
+  int32_t rank, world;                 /* world <= FLYB_MAX_PEERS */
+  int32_t total_pad;                   /* slot stride in floats: flyb_peer_total_pad(net->total) */
+  int32_t _pad;
+  void* base[FLYB_MAX_PEERS];          /* base[r]: rank r's buffer as mapped in THIS process (base[rank]: own) */
+} FlybPeerGroup;
+int32_t flyb_peer_total_pad(int32_t total);
+size_t flyb_peer_bytes(int32_t total, int32_t world);
+/* cudaMalloc + zero + cudaIpcGetMemHandle on the current device; handle_out: 64 bytes. */
+int flyb_peer_alloc(size_t bytes, void** ptr_out, void* handle_out);
+int flyb_peer_open(const void* handle, void** ptr_out);   /* cudaIpcOpenMemHandle (enables peer access lazily) */
+int flyb_peer_close(void* ptr);                            /* cudaIpcCloseMemHandle */
+int flyb_peer_free(void* ptr);                             /* cudaFree of an own buffer */
+
 /* ---- agent, kernel (d): one optimiser step of reference PPO.update (ppo.py:183-199), split where a
- *      data-parallel run all-reduces:  flyb_ppo_grad -> [all-reduce(grad)/world] -> flyb_ppo_apply.
+ *      data-parallel run exchanges gradients:  flyb_ppo_grad -> [sum over ranks] -> flyb_ppo_apply.
  * flyb_ppo_grad: forward, clipped-surrogate + SmoothL1 loss, backward.  wpack (nullable): packed weight stream of
  *   the CURRENT params -> tcgen05 3xTF32 forward/backward/weight-gradient GEMMs; NULL -> exact-fp32 CUDA cores.
  *   obs (rows,O), action (rows,A),
  *   old_logp/target/advantage (rows).  Out: grad (net->total) = d(loss.mean())/d(params) over THESE rows,
  *   loss (1).  workspace: flyb_ppo_workspace_bytes(net, rows) bytes.
+ *   peers (nullable): also push the gradient to every rank (see FlybPeerGroup).
  * flyb_ppo_apply: grad *= grad_scale; clip_grad_norm_(max_grad_norm) with torch's coefficient
  *   min(1, max/(norm+1e-6)); Adam (torch defaults, no weight decay).  step (1) i64 device counter, incremented.
- *   grad_norm_out (1) nullable.  workspace: the flyb_ppo_grad workspace (only its first 256 bytes are used).
- *   wpack (nullable): re-packed from the updated parameters in the same call. */
+ *   grad_norm_out (1) nullable.  workspace: the flyb_ppo_grad workspace (only its first 1 KB is used).
+ *   wpack (nullable): re-packed from the updated parameters in the same call.
+ *   peers (nullable): grad <- sum over ranks of the pushed gradients first (pass grad_scale = 1/world);
+ *   NULL: `grad` is taken as it is (single GPU, or the caller all-reduced it, e.g. with NCCL). */
 size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t rows);
 int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                   const float* obs, const float* action, const float* old_logp, const float* target,
                   const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
-                  void* workspace, void* stream);
+                  void* workspace, const FlybPeerGroup* peers, void* stream);
 int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad, float* exp_avg,
                    float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out, void* workspace,
-                   void* wpack, void* stream);
+                   void* wpack, const FlybPeerGroup* peers, void* stream);
 
 /* action_var <- max(floor, action_var - decay) (ppo.py:236-237), on the device so a captured graph can replay it;
  * step_counter (1, nullable) u64 += 1 (the Philox draw number of flyb_policy_act). */

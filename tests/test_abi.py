@@ -25,7 +25,7 @@ def test_header_symbols_are_exported_and_bound(built_lib):
         assert s in _lib.SIGNATURES, f"{s} has no ctypes signature in fly_bproject_b200/_lib.py"
     assert sorted(_lib.SIGNATURES) == syms
     lib = _lib.lib()
-    assert lib.flyb_abi_version() == 4
+    assert lib.flyb_abi_version() == 5
 
 
 def test_library_is_sm100a_only(built_lib):
@@ -39,11 +39,12 @@ def test_struct_sizes_match_header(built_lib, tmp_path):
     from fly_bproject_b200 import _lib
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "flyb200.h"\nint main(){printf("%zu %zu %zu\\n", '
-                   'sizeof(FlybEnvCfg), sizeof(FlybNetLayout), sizeof(FlybPpoCfg));printf("%zu\\n", sizeof(FlybStepTail));return 0;}\n')
+                   'sizeof(FlybEnvCfg), sizeof(FlybNetLayout), sizeof(FlybPpoCfg));printf("%zu %zu\\n", sizeof(FlybStepTail), sizeof(FlybPeerGroup));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
-    assert sizes == [C.sizeof(_lib.EnvCfg), C.sizeof(_lib.NetLayout), C.sizeof(_lib.PpoCfg), C.sizeof(_lib.StepTail)]
+    assert sizes == [C.sizeof(_lib.EnvCfg), C.sizeof(_lib.NetLayout), C.sizeof(_lib.PpoCfg), C.sizeof(_lib.StepTail),
+                     C.sizeof(_lib.PeerGroup)]
 
 
 def test_net_layout_and_argument_errors(built_lib):

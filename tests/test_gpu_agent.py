@@ -196,7 +196,7 @@ def _grad_step(net, g, k, j, var):
     dv = [x.contiguous().to(DEV) for x in (g["roll_obs"][k:j], g["roll_acts"][k:j], g["roll_logp"][k:j],
                                            g["roll_target"][k:j], g["roll_adv"][k:j], var)]
     _lib.check(lib.flyb_ppo_grad(C.byref(net.layout), C.byref(cfg), p(net.flat), p(net.wpack), p(dv[0]), p(dv[1]), p(dv[2]),
-                                 p(dv[3]), p(dv[4]), p(dv[5]), rows, p(grad), p(loss), wsp, _lib.current_stream()))
+                                 p(dv[3]), p(dv[4]), p(dv[5]), rows, p(grad), p(loss), wsp, None, _lib.current_stream()))
     torch.cuda.synchronize()
     return grad, loss, ws, wsp, cfg
 
@@ -223,7 +223,7 @@ def test_ppo_minibatch_step_matches_reference_golden():
     step = torch.zeros(1, dtype=torch.int64, device=DEV)
     gn = torch.zeros(1, device=DEV)
     _lib.check(lib.flyb_ppo_apply(C.byref(net.layout), C.byref(cfg), p(net.flat), p(grad), p(m), p(v), p(step), 1.0,
-                                  p(gn), wsp, p(net.wpack), _lib.current_stream()))
+                                  p(gn), wsp, p(net.wpack), None, _lib.current_stream()))
     torch.cuda.synchronize()
     assert int(step.item()) == 1
     assert float(gn) == pytest.approx(norm, rel=1e-4)
