@@ -47,19 +47,25 @@ def _worker(rank, world, port, out, mode):
 
 
 @pytest.mark.timeout(300)
-def test_two_rank_update_keeps_ranks_identical(tmp_path):
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 CUDA devices")
+def test_data_parallel_update_keeps_ranks_identical(tmp_path):
+    world = int(os.environ.get("FLYB_TEST_WORLD", "2"))       # 4 / 8 for a wider box; more ranks, same checks
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} CUDA devices")
     out = str(tmp_path / "dp")
     res = {}
     for mode in ("peer", "nccl"):
-        mp.spawn(_worker, args=(2, _free_port(), out, mode), nprocs=2, join=True)
-        r0, r1 = torch.load(f"{out}.{mode}.0"), torch.load(f"{out}.{mode}.1")
-        assert r0["steps"] == r1["steps"] == 150
-        for k in ("flat", "m", "v"):
-            assert torch.equal(r0[k], r1[k]), (mode, k)
-        assert bool(torch.isfinite(r0["flat"]).all())
-        assert r0["loss"] != r1["loss"]            # each rank logs its own shard's loss
-        res[mode] = r0
+        mp.spawn(_worker, args=(world, _free_port(), out, mode), nprocs=world, join=True)
+        rs = [torch.load(f"{out}.{mode}.{r}") for r in range(world)]
+        for r in rs[1:]:
+            assert r["steps"] == rs[0]["steps"] == 150
+            for k in ("flat", "m", "v"):
+                assert torch.equal(r[k], rs[0][k]), (mode, k)
+            assert r["loss"] != rs[0]["loss"]          # each rank logs its own shard's loss
+        assert bool(torch.isfinite(rs[0]["flat"]).all())
+        res[mode] = rs[0]
     for k in ("flat", "m", "v"):
-        assert torch.equal(res["peer"][k], res["nccl"][k]), k
+        if world == 2:      # a + b is one rounding in any order
+            assert torch.equal(res["peer"][k], res["nccl"][k]), k
+    # more ranks: NCCL's tree / ring order differs from the rank order, and 150 Adam steps (each ~lr in size whatever
+    # the gradient's magnitude) amplify the reassociation noise: only the bulk has to agree
+    assert float((res["peer"]["flat"] - res["nccl"]["flat"]).abs().mean()) < 1e-3
