@@ -87,6 +87,7 @@ SIGNATURES = {
     "flyb_peer_open": (C.c_int, [_P, C.POINTER(C.c_void_p)]),
     "flyb_peer_close": (C.c_int, [_P]),
     "flyb_peer_free": (C.c_int, [_P]),
+    "flyb_peer_stamps": (C.c_int, [C.POINTER(PeerGroup), C.POINTER(C.c_uint64)]),
     "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P, _P]),
 }
 

@@ -59,3 +59,12 @@ extern "C" int flyb_peer_free(void* ptr) {
   FLYB_REQUIRE(ptr, "flyb_peer_free: NULL");
   return check_cuda(cudaFree(ptr), "cudaFree(peer buffer)");
 }
+
+extern "C" int flyb_peer_stamps(const FlybPeerGroup* g, uint64_t* out8) {
+  FLYB_REQUIRE(g && out8, "flyb_peer_stamps: NULL argument");
+  int rc = peer_validate(g, 1);
+  if (rc != FLYB_OK) return rc;
+  const PeerView v = make_peer_view(*g);
+  if ((rc = check_cuda(cudaDeviceSynchronize(), "cudaDeviceSynchronize")) != FLYB_OK) return rc;
+  return check_cuda(cudaMemcpy(out8, v.stamp, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost), "cudaMemcpy(stamps)");
+}

@@ -9,12 +9,12 @@ struct PeerView {   // FlybPeerGroup resolved into typed pointers (kernel argume
   int rank, world, total_pad;
   float* slots[FLYB_MAX_PEERS];        // slots[r]: [2][world][total_pad] in rank r's buffer
   uint32_t* flags[FLYB_MAX_PEERS];     // flags[r]: [FLYB_MAX_PEERS] in rank r's buffer
-  uint32_t* epoch;                     // own
-  uint32_t* ticket;                    // own
+  uint32_t* epoch;                     // own: exchanges completed by this rank
+  unsigned long long* stamp;           // own: 8 x %globaltimer marks of the last exchange (flyb_peer_stamps)
 };
 
 inline size_t peer_slots_bytes(int total_pad, int world) { return (size_t)2 * world * total_pad * sizeof(float); }
-constexpr size_t PEER_CTRL_BYTES = 256;   // flags[8], epoch, ticket
+constexpr size_t PEER_CTRL_BYTES = 256;   // flags[8], epoch, (pad), 8 x u64 stamps at byte 64
 
 inline PeerView make_peer_view(const FlybPeerGroup& g) {
   PeerView v{};
@@ -25,10 +25,15 @@ inline PeerView make_peer_view(const FlybPeerGroup& g) {
     v.flags[r] = (uint32_t*)((char*)g.base[r] + sb);
   }
   v.epoch = v.flags[g.rank] + FLYB_MAX_PEERS;
-  v.ticket = v.epoch + 1;
+  v.stamp = (unsigned long long*)(v.flags[g.rank] + 16);
   return v;
 }
 
+FLYB_D unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 FLYB_D uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -51,19 +56,13 @@ FLYB_D void peer_push(const PeerView& pv, uint32_t parity, int i, float val) {
     if (r < pv.world) pv.slots[r][at] = val;
 }
 
-// Called by every thread of a pushing CTA after its last peer_push.  The last CTA of the grid raises this rank's
-// flag on every rank and bumps the local epoch; `epoch_before` is the value every CTA read at its start.
-FLYB_D void peer_push_done(const PeerView& pv, uint32_t epoch_before) {
-  __threadfence_system();          // this thread's remote stores before anything that follows, system-wide
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t t = atomicAdd(pv.ticket, 1u);
-    if (t == gridDim.x * gridDim.y - 1) {
-      __threadfence_system();      // every CTA's stores (ordered before its ticket) before the flags
-      *pv.ticket = 0;
-      *pv.epoch = epoch_before + 1;
-      for (int r = 0; r < pv.world; ++r) st_release_sys(pv.flags[r] + pv.rank, epoch_before + 1);
-    }
+// Raise this rank's flag of epoch `want` on every rank.  Called by ONE CTA of the kernel that FOLLOWS the pushing
+// kernel in the stream: a kernel is complete only when its remote stores have been acknowledged, so the pushing
+// kernel needs no fences or tickets of its own and the flag cannot overtake the data.
+FLYB_D void peer_raise_flags(const PeerView& pv, uint32_t want) {
+  if (threadIdx.x < pv.world) {
+    __threadfence_system();
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pv.flags[threadIdx.x] + pv.rank), "r"(want) : "memory");
   }
 }
 

@@ -352,7 +352,6 @@ ppo_reduce_kernel(const float* __restrict__ dw_part, int splits, int total, floa
     y = warp_sum(y);
     if (threadIdx.x == 0) *loss = -x * inv_rows + y * inv_rows;
   }
-  if (PEERS) peer_push_done(pv, epoch);
 }
 
 // ------------------------------------------------------------------------------------------ clip + Adam
@@ -365,9 +364,14 @@ ppo_norm_kernel(float* __restrict__ grad, int total, float scale, float* __restr
   __shared__ float red[8];
   uint32_t parity = 0;
   if (PEERS) {
-    const uint32_t epoch = *(volatile const uint32_t*)pv.epoch;   // pushes done by this rank, the last one just now
-    peer_wait_all(pv, epoch);
-    parity = (epoch - 1u) & 1u;
+    const uint32_t epoch = *(volatile const uint32_t*)pv.epoch;   // exchanges completed before this one
+    if (blockIdx.x == 0) {   // the pushing kernel before this one is complete: its stores have reached every rank
+      if (threadIdx.x == 0) pv.stamp[3] = global_ns();
+      peer_raise_flags(pv, epoch + 1u);
+    }
+    peer_wait_all(pv, epoch + 1u);
+    if (blockIdx.x == 0 && threadIdx.x == 0) pv.stamp[4] = global_ns();
+    parity = epoch & 1u;
   }
   float acc = 0.0f;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
@@ -389,6 +393,7 @@ ppo_norm_kernel(float* __restrict__ grad, int total, float scale, float* __restr
     for (int i = 0; i < 8; ++i) t += red[i];
     norm_part[blockIdx.x] = t;
     if (blockIdx.x == 0) *step += 1;   // Adam's step counter; read by ppo_adam_kernel after this launch
+    if (PEERS && blockIdx.x == 0) pv.stamp[5] = global_ns();
   }
 }
 
@@ -401,7 +406,7 @@ __global__ void __launch_bounds__(256)
 ppo_adam_kernel(float* __restrict__ params, float* __restrict__ grad, float* __restrict__ exp_avg,
                 float* __restrict__ exp_avg_sq, int total, const float* __restrict__ norm_part,
                 const long long* __restrict__ step, const __grid_constant__ AdamArgs a,
-                float* __restrict__ grad_norm_out) {
+                float* __restrict__ grad_norm_out, uint32_t* __restrict__ peer_epoch) {
   __shared__ float s_coef, s_step_size, s_bc2_sqrt;
   if (threadIdx.x < 32) {
     float t = 0.0f;   // fixed order: lane l adds partials l, l + 32, ...; then the butterfly
@@ -417,6 +422,7 @@ ppo_adam_kernel(float* __restrict__ params, float* __restrict__ grad, float* __r
       s_step_size = (float)(a.lr / bc1);
       s_bc2_sqrt = (float)sqrt(bc2);
       if (blockIdx.x == 0 && grad_norm_out) *grad_norm_out = total_norm;
+      if (blockIdx.x == 0 && peer_epoch) *peer_epoch += 1;   // this exchange is over (every norm CTA has read the old value)
     }
   }
   __syncthreads();
@@ -546,7 +552,8 @@ extern "C" int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, f
   FLYB_LAUNCH_CHECK("ppo_norm_kernel");
   AdamArgs a{cfg->lr, cfg->beta1, cfg->beta2, cfg->eps, cfg->max_grad_norm, grad_scale};
   ppo_adam_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(params, grad, exp_avg, exp_avg_sq, net->total, norm_part,
-                                                            (const long long*)step, a, grad_norm_out);
+                                                            (const long long*)step, a, grad_norm_out,
+                                                            peers ? make_peer_view(*peers).epoch : nullptr);
   FLYB_LAUNCH_CHECK("ppo_adam_kernel");
   if (wpack) {   // keep the tensor-core weight stream in step with the parameters
     FLYB_REQUIRE(tc_supported(net), "flyb_ppo_apply: wpack given but the tensor-core path does not cover this shape");

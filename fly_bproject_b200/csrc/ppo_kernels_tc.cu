@@ -841,31 +841,29 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
                      const __grid_constant__ PeerView pv) {
   __shared__ float s_acc[RED_GROUPS][RED_ELEMS];
   const int e = threadIdx.x & (RED_ELEMS - 1), pg = threadIdx.x / RED_ELEMS;
+  const int i = blockIdx.x * RED_ELEMS + e;
   uint32_t epoch = 0;
-  if (PEERS) epoch = *(volatile const uint32_t*)pv.epoch;   // bumped by the grid's last CTA, after every CTA read it
-  // one group of 64 entries per CTA without peers; with peers a one-wave grid walks the groups, so that the
-  // system-scope fence behind the remote stores is paid once per CTA
-  const int ngroups = (a.total + RED_ELEMS - 1) / RED_ELEMS;
-  for (int grp = blockIdx.x; grp < ngroups; grp += gridDim.x) {
-    const int i = grp * RED_ELEMS + e;
-    float acc = 0.0f;
-    if (i < a.total) {
-      bool valid = false;
+  if (PEERS) {
+    epoch = *(volatile const uint32_t*)pv.epoch;   // bumped by ppo_adam_kernel, i.e. after this exchange
+    if (blockIdx.x == 0 && threadIdx.x == 0) pv.stamp[0] = global_ns();
+  }
+  float acc = 0.0f;
+  if (i < a.total) {
+    bool valid = false;
 #pragma unroll
-      for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= a.off[sg] && i < a.off[sg] + a.size[sg]);
-      if (valid) {   // group pg sums partials pg, pg + 4, ... in order; the groups are combined in a fixed order below
+    for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= a.off[sg] && i < a.off[sg] + a.size[sg]);
+    if (valid) {   // group pg sums partials pg, pg + 4, ... in order; the groups are combined in a fixed order below
 #pragma unroll 8
-        for (int p = pg; p < a.nparts; p += RED_GROUPS) acc += dw_part[(size_t)p * a.total + i];
-      }
+      for (int p = pg; p < a.nparts; p += RED_GROUPS) acc += dw_part[(size_t)p * a.total + i];
     }
-    s_acc[pg][e] = acc;
-    __syncthreads();
-    if (pg == 0 && i < a.total) {
-      const float g = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
-      grad[i] = g;
-      if (PEERS) peer_push(pv, epoch & 1u, i, g);   // posted NVLink stores into every rank's slot of this rank
-    }
-    if (PEERS) __syncthreads();                     // s_acc is reused by the next group
+  }
+  s_acc[pg][e] = acc;
+  __syncthreads();
+  if (pg == 0 && i < a.total) {
+    const float g = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
+    grad[i] = g;
+    // posted NVLink stores into this rank's slot on every rank; the flags are raised by the next kernel (peer.cuh)
+    if (PEERS) peer_push(pv, epoch & 1u, i, g);
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
     float x = 0.0f, y = 0.0f;
@@ -877,7 +875,6 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
     y = warp_sum(y);
     if (threadIdx.x == 0) *loss = -x * a.inv_rows + y * a.inv_rows;
   }
-  if (PEERS) peer_push_done(pv, epoch);
 }
 
 struct Ws {
@@ -967,7 +964,7 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   r.total = net->total; r.nparts = w.ctas_per_role; r.nloss = w.grid1; r.inv_rows = ga.inv_rows;
   const int red_grid = (net->total + RED_ELEMS - 1) / RED_ELEMS;
   if (peers)
-    ppo_reduce_tc_kernel<true><<<std::min(red_grid, 4 * num_sms()), RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+    ppo_reduce_tc_kernel<true><<<red_grid, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
                                                                             make_peer_view(*peers));
   else
     ppo_reduce_tc_kernel<false><<<red_grid, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,

@@ -183,14 +183,16 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  * others' buffers with flyb_peer_open and fills a FlybPeerGroup.  With a group,
  *   flyb_ppo_grad  : its last kernel (the fixed-order reduction of the per-CTA partial gradients) stores every
  *                    gradient entry straight into slot [epoch & 1][rank] of EVERY rank's buffer (posted NVLink
- *                    writes), and the last CTA to finish raises this rank's flag on every rank;
- *   flyb_ppo_apply : its first kernel (global norm) waits for all ranks' flags of this epoch, sums the `world` slots
- *                    in rank order (bit-identical on every rank), writes `grad` and goes on as usual.
- * No kernel waits for a peer except that norm kernel, and the peers' pushing kernels never wait: no dead-lock however
- * CTAs are scheduled.  Slots are double-buffered by epoch parity: a rank can be at most one push ahead of the
- * slowest one.  Everything is stream-ordered device code: a whole data-parallel update is CUDA-graph capturable.
+ *                    writes; no fences, the kernel boundary completes them);
+ *   flyb_ppo_apply : its first kernel (global norm) raises this rank's flag on every rank, waits for all ranks'
+ *                    flags of this epoch, sums the `world` slots in rank order (bit-identical on every rank), writes
+ *                    `grad` and goes on as usual; the Adam kernel closes the epoch.
+ * The two calls must alternate, on one stream.  No kernel waits for a peer except that norm kernel, and what it
+ * waits for is raised at the ENTRY of the peers' norm kernels: no dead-lock however CTAs are scheduled.  Slots are
+ * double-buffered by epoch parity: a rank can be at most one push ahead of the slowest one.  Everything is
+ * stream-ordered device code: a whole data-parallel update is CUDA-graph capturable.
  * Layout of a buffer of flyb_peer_bytes(total, world) bytes (zero-filled by flyb_peer_alloc):
- *   float slots[2][world][total_pad]; uint32 flags[FLYB_MAX_PEERS] (one epoch per source rank); uint32 epoch; uint32 ticket. */
+ *   float slots[2][world][total_pad]; uint32 flags[FLYB_MAX_PEERS] (one epoch per source rank); uint32 epoch; time stamps. */
 #define FLYB_MAX_PEERS 8
 typedef struct FlybPeerGroup {
   int32_t rank, world;                 /* world <= FLYB_MAX_PEERS */
@@ -205,6 +207,9 @@ int flyb_peer_alloc(size_t bytes, void** ptr_out, void* handle_out);
 int flyb_peer_open(const void* handle, void** ptr_out);   /* cudaIpcOpenMemHandle (enables peer access lazily) */
 int flyb_peer_close(void* ptr);                            /* cudaIpcCloseMemHandle */
 int flyb_peer_free(void* ptr);                             /* cudaFree of an own buffer */
+/* Debug aid (synchronises the device): %globaltimer marks in ns of this rank's LAST exchange:
+ * [0] reduce kernel entry, [3] norm kernel entry (flags raised), [4] all ranks' flags seen, [5] norm CTA 0 done. */
+int flyb_peer_stamps(const FlybPeerGroup* group, uint64_t* out8);
 
 /* ---- agent, kernel (d): one optimiser step of reference PPO.update (ppo.py:183-199), split where a
  *      data-parallel run exchanges gradients:  flyb_ppo_grad -> [sum over ranks] -> flyb_ppo_apply.
