@@ -343,6 +343,13 @@ class PPO:
         p, stream = _lib.ptr, _lib.current_stream()
         rows = (j - k) * self.num_envs
         lay = C.byref(self.net.layout)
+        if self.world_size == 1:     # nothing happens between the two halves: one call, two launches fewer
+            _lib.check(self.lib.flyb_ppo_step(
+                lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.net.wpack), p(self._obs_ring[k:j]),
+                p(self.all_acts[k:j]), p(self.all_log_prob[k:j]), p(self._target[k:j]), p(self.all_advantage[k:j]),
+                p(self.action_var), rows, p(self.grad), p(self.loss), p(self.exp_avg), p(self.exp_avg_sq),
+                p(self.adam_step), p(self.grad_norm), self._ws_ptr, stream), "flyb_ppo_step")
+            return
         peers = self._peers.byref() if self._peers is not None else None
         _lib.check(self.lib.flyb_ppo_grad(
             lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.net.wpack), p(self._obs_ring[k:j]), p(self.all_acts[k:j]),

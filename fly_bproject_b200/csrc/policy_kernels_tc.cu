@@ -95,6 +95,36 @@ pack_weights_kernel(const __grid_constant__ PackPlan plan, const float* __restri
   }
 }
 
+// Inverse of the mapping above: for every parameter, where its hi copies sit in the weight stream (at most two: the
+// forward operand and the transposed backward operand) and how far behind the lo copy follows.  Built once by
+// flyb_pack_weights; ppo_adam_kernel uses it to refresh the stream in place while it updates the parameters.
+// Entry i = {dst0, delta0, dst1, delta1} in floats, dst = -1: none.
+__global__ void __launch_bounds__(256)
+pack_index_kernel(const __grid_constant__ PackPlan plan, int* __restrict__ inv) {
+  const int total = plan.total_stages * (tcm::STAGE / 4);
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int stage = idx / (tcm::STAGE / 4);
+    int si = 0;
+    for (int i = 1; i < plan.nseg; ++i)
+      if (stage >= plan.seg[i].first_stage) si = i;
+    const PackSeg& s = plan.seg[si];
+    const int li = idx - s.first_stage * (tcm::STAGE / 4);
+    const int slab_floats = s.N * 8;
+    const int slab = li / slab_floats, e = li - slab * slab_floats;
+    if (slab & 1) continue;   // lo slab: reached through delta
+    const int ks = slab >> 1;
+    const int kc = e / (s.N * 4), rem = e - kc * (s.N * 4);
+    const int n = rem >> 2, kk = rem & 3;
+    const int k = s.k0 + ks * 8 + kc * 4 + kk;
+    if (!(n < s.n_rows && k < s.k_cols)) continue;
+    const int src = s.transposed ? s.w_off + k * s.ldw + s.n0 + n : s.w_off + (s.n0 + n) * s.ldw + k;
+    int* ent = inv + 4 * (size_t)src;
+    if (atomicCAS(ent + 0, -1, idx) == -1) ent[1] = slab_floats;
+    else if (atomicCAS(ent + 2, -1, idx) == -1) ent[3] = slab_floats;
+    else __trap();            // a third copy would need a wider table: the plan above never makes one
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ finalisers
 // Cooperative copy of a staged tile to global memory: one bulk TMA store when size and address allow, plain
 // coalesced stores otherwise.  Called by all 256 epilogue threads after the staging writes were fenced + synced.
@@ -394,14 +424,24 @@ static unsigned long long* g_trace = nullptr;   // debug timeline buffer (flyb_d
 void tc_set_trace(void* p) { g_trace = (unsigned long long*)p; }
 bool tc_supported(const FlybNetLayout* net) { return net->k0_pad == tcm::K0 && net->num_act <= tcm::APAD; }
 
+// wpack = [weight stream: total_stages x 8 KB][inverse index: net->total x 4 int32]
 size_t tc_wpack_bytes(const FlybNetLayout* net) {
   if (!tc_supported(net)) return 0;
-  return (size_t)forward_plan(*net).total_stages * tcm::STAGE;
+  return (size_t)forward_plan(*net).total_stages * tcm::STAGE + (size_t)net->total * 16;
+}
+
+const int* tc_wpack_index(const FlybNetLayout* net, const void* wpack) {
+  return (const int*)((const char*)wpack + (size_t)forward_plan(*net).total_stages * tcm::STAGE);
 }
 
 int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st) {
   const PackPlan plan = forward_plan(*net);
   const int total = plan.total_stages * (tcm::STAGE / 4);
+  int* inv = const_cast<int*>(tc_wpack_index(net, wpack));
+  int rc = check_cuda(cudaMemsetAsync(inv, 0xFF, (size_t)net->total * 16, st), "cudaMemsetAsync(pack index)");
+  if (rc != FLYB_OK) return rc;
+  pack_index_kernel<<<std::min((total + 255) / 256, 2 * 148), 256, 0, st>>>(plan, inv);
+  FLYB_LAUNCH_CHECK("pack_index_kernel");
   pack_weights_kernel<<<std::min((total + 255) / 256, 2 * 148), 256, 0, st>>>(plan, params, (float*)wpack);
   FLYB_LAUNCH_CHECK("pack_weights_kernel");
   return FLYB_OK;

@@ -14,6 +14,7 @@
 #include <algorithm>
 
 #include "peer.cuh"
+#include "tc_common.cuh"
 #include "mlp_simt.cuh"
 
 namespace flyb {
@@ -23,10 +24,18 @@ int validate_net(const FlybNetLayout* net, const float* params);
 bool tc_supported(const FlybNetLayout* net);
 int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st);
 size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows);
+// flyb_ppo_step: the gradient reduction also takes the squared norm and bumps Adam's step counter, so that Adam can
+// follow without a norm kernel.  in: step;  out: sq_part [sq_parts]
+struct StepFuse {
+  long long* step;
+  const float* sq_part;
+  int sq_parts;
+};
 int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                 const float* obs, const float* action, const float* old_logp, const float* target,
                 const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
-                void* workspace, const FlybPeerGroup* peers, cudaStream_t st);
+                void* workspace, const FlybPeerGroup* peers, cudaStream_t st, StepFuse* fuse = nullptr);
+const int* tc_wpack_index(const FlybNetLayout* net, const void* wpack);
 
 constexpr int DW_SPLITS_MAX = 64;
 constexpr int NORM_BLOCKS = 256;
@@ -406,11 +415,12 @@ __global__ void __launch_bounds__(256)
 ppo_adam_kernel(float* __restrict__ params, float* __restrict__ grad, float* __restrict__ exp_avg,
                 float* __restrict__ exp_avg_sq, int total, const float* __restrict__ norm_part,
                 const long long* __restrict__ step, const __grid_constant__ AdamArgs a,
-                float* __restrict__ grad_norm_out, uint32_t* __restrict__ peer_epoch) {
+                float* __restrict__ grad_norm_out, uint32_t* __restrict__ peer_epoch, int norm_parts,
+                float* __restrict__ wpack, const int4* __restrict__ wpack_index) {
   __shared__ float s_coef, s_step_size, s_bc2_sqrt;
   if (threadIdx.x < 32) {
     float t = 0.0f;   // fixed order: lane l adds partials l, l + 32, ...; then the butterfly
-    for (int i = threadIdx.x; i < NORM_BLOCKS; i += 32) t += norm_part[i];
+    for (int i = threadIdx.x; i < norm_parts; i += 32) t += norm_part[i];
     t = warp_sum(t);
     if (threadIdx.x == 0) {
       const float total_norm = sqrtf(t);
@@ -436,9 +446,23 @@ ppo_adam_kernel(float* __restrict__ params, float* __restrict__ grad, float* __r
     v = v * b2;                                       // exp_avg_sq.mul_(beta2)
     v = v + (w2 * g) * g;                             //   .addcmul_(grad, grad, value = 1 - beta2)
     const float denom = sqrtf(v) / bc2_sqrt + eps;    // (exp_avg_sq.sqrt() / bias_correction2_sqrt).add_(eps)
-    params[i] = params[i] + (-step_size) * (m / denom);   // param.addcdiv_(exp_avg, denom, value = -step_size)
+    const float p_new = params[i] + (-step_size) * (m / denom);   // param.addcdiv_(exp_avg, denom, value = -step_size)
+    params[i] = p_new;
     exp_avg[i] = m;
     exp_avg_sq[i] = v;
+    if (wpack_index) {   // keep the tensor-core weight stream in step: hi/lo TF32 copies of this parameter, in place
+      const int4 d = wpack_index[i];
+      if (d.x >= 0) {
+        const float hi = __uint_as_float(tc::tf32_rna_bits(p_new));
+        const float lo = __uint_as_float(tc::tf32_rna_bits(p_new - hi));
+        wpack[d.x] = hi;
+        wpack[d.x + d.y] = lo;
+        if (d.z >= 0) {
+          wpack[d.z] = hi;
+          wpack[d.z + d.w] = lo;
+        }
+      }
+    }
   }
 }
 
@@ -531,6 +555,23 @@ extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, co
   return FLYB_OK;
 }
 
+// clip + Adam (+ in-place refresh of the tensor-core weight stream) on `grad`; norm partials come from whoever ran
+// before: ppo_norm_kernel (flyb_ppo_apply) or the gradient reduction itself (flyb_ppo_step)
+static int launch_adam(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad, float* exp_avg,
+                       float* exp_avg_sq, const long long* step, float grad_scale, float* grad_norm_out,
+                       const float* norm_part, int norm_parts, void* wpack, const FlybPeerGroup* peers,
+                       cudaStream_t st) {
+  if (wpack)
+    FLYB_REQUIRE(tc_supported(net), "wpack given but the tensor-core path does not cover this shape");
+  AdamArgs a{cfg->lr, cfg->beta1, cfg->beta2, cfg->eps, cfg->max_grad_norm, grad_scale};
+  ppo_adam_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(
+      params, grad, exp_avg, exp_avg_sq, net->total, norm_part, step, a, grad_norm_out,
+      peers ? make_peer_view(*peers).epoch : nullptr, norm_parts, (float*)wpack,
+      wpack ? (const int4*)tc_wpack_index(net, wpack) : nullptr);
+  FLYB_LAUNCH_CHECK("ppo_adam_kernel");
+  return FLYB_OK;
+}
+
 extern "C" int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad,
                               float* exp_avg, float* exp_avg_sq, int64_t* step, float grad_scale,
                               float* grad_norm_out, void* workspace, void* wpack, const FlybPeerGroup* peers,
@@ -550,14 +591,35 @@ extern "C" int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, f
                                                         PeerView{});
   }
   FLYB_LAUNCH_CHECK("ppo_norm_kernel");
-  AdamArgs a{cfg->lr, cfg->beta1, cfg->beta2, cfg->eps, cfg->max_grad_norm, grad_scale};
-  ppo_adam_kernel<<<(net->total + 255) / 256, 256, 0, st>>>(params, grad, exp_avg, exp_avg_sq, net->total, norm_part,
-                                                            (const long long*)step, a, grad_norm_out,
-                                                            peers ? make_peer_view(*peers).epoch : nullptr);
-  FLYB_LAUNCH_CHECK("ppo_adam_kernel");
-  if (wpack) {   // keep the tensor-core weight stream in step with the parameters
-    FLYB_REQUIRE(tc_supported(net), "flyb_ppo_apply: wpack given but the tensor-core path does not cover this shape");
-    return tc_pack_weights(net, params, wpack, st);
+  return launch_adam(net, cfg, params, grad, exp_avg, exp_avg_sq, (const long long*)step, grad_scale, grad_norm_out,
+                     norm_part, NORM_BLOCKS, wpack, peers, st);
+}
+
+extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack,
+                             const float* obs, const float* action, const float* old_logp, const float* target,
+                             const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
+                             float* exp_avg, float* exp_avg_sq, int64_t* step, float* grad_norm_out, void* workspace,
+                             void* stream) {
+  if (!wpack) {   // CUDA-core path: the two halves as they are
+    int rc = flyb_ppo_grad(net, cfg, params, nullptr, obs, action, old_logp, target, advantage, action_var, rows, grad,
+                           loss, workspace, nullptr, stream);
+    if (rc != FLYB_OK) return rc;
+    return flyb_ppo_apply(net, cfg, params, grad, exp_avg, exp_avg_sq, step, 1.0f, grad_norm_out, workspace, nullptr,
+                          nullptr, stream);
   }
-  return FLYB_OK;
+  int rc = validate_net(net, params);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(cfg && obs && action && old_logp && target && advantage && action_var && grad && loss && exp_avg &&
+                   exp_avg_sq && step && workspace,
+               "flyb_ppo_step: NULL argument");
+  FLYB_REQUIRE(rows > 0, "flyb_ppo_step: rows must be > 0");
+  FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_step: workspace must be 256-byte aligned");
+  FLYB_REQUIRE(tc_supported(net), "flyb_ppo_step: wpack given but the tensor-core path does not cover this shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  StepFuse fuse{(long long*)step, nullptr, 0};
+  rc = tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
+                   workspace, nullptr, st, &fuse);
+  if (rc != FLYB_OK) return rc;
+  return launch_adam(net, cfg, params, grad, exp_avg, exp_avg_sq, (const long long*)step, 1.0f, grad_norm_out,
+                     fuse.sq_part, fuse.sq_parts, wpack, nullptr, st);
 }

@@ -37,6 +37,12 @@ int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
 bool tc_supported(const FlybNetLayout* net);
 
+struct StepFuse {   // see ppo_kernels.cu
+  long long* step;
+  const float* sq_part;
+  int sq_parts;
+};
+
 namespace tcb {
 using namespace tcm;
 
@@ -832,6 +838,8 @@ struct ReduceArgs {
   int off[12], size[12];
   int total, nparts, nloss;
   float inv_rows;
+  float* sq_part;   // nullable: [gridDim.x] sums of squares of this CTA's entries (flyb_ppo_step: saves the norm kernel)
+  long long* step;  // with sq_part: Adam's step counter, += 1 (the norm kernel's other job)
 };
 constexpr int RED_ELEMS = 64, RED_GROUPS = 4;   // 256 threads: 64 gradient entries x 4 interleaved partial groups
 template <bool PEERS>
@@ -840,6 +848,7 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
                      const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss,
                      const __grid_constant__ PeerView pv) {
   __shared__ float s_acc[RED_GROUPS][RED_ELEMS];
+  __shared__ float s_sq[2];
   const int e = threadIdx.x & (RED_ELEMS - 1), pg = threadIdx.x / RED_ELEMS;
   const int i = blockIdx.x * RED_ELEMS + e;
   uint32_t epoch = 0;
@@ -859,11 +868,25 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
   }
   s_acc[pg][e] = acc;
   __syncthreads();
-  if (pg == 0 && i < a.total) {
-    const float g = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
-    grad[i] = g;
-    // posted NVLink stores into this rank's slot on every rank; the flags are raised by the next kernel (peer.cuh)
-    if (PEERS) peer_push(pv, epoch & 1u, i, g);
+  if (pg == 0) {   // warps 0 and 1
+    float g = 0.0f;
+    if (i < a.total) {
+      g = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
+      grad[i] = g;
+      // posted NVLink stores into this rank's slot on every rank; the flags are raised by the next kernel (peer.cuh)
+      if (PEERS) peer_push(pv, epoch & 1u, i, g);
+    }
+    if (a.sq_part) {
+      const float sq = warp_sum(g * g);
+      if ((threadIdx.x & 31) == 0) s_sq[threadIdx.x >> 5] = sq;
+    }
+  }
+  if (a.sq_part) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      a.sq_part[blockIdx.x] = s_sq[0] + s_sq[1];
+      if (blockIdx.x == 0) *a.step += 1;
+    }
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
     float x = 0.0f, y = 0.0f;
@@ -882,7 +905,8 @@ struct Ws {
   Images im;
   float* loss_part;
   float* dw_part;
-  int grid1, ctas_per_role;
+  float* sq_part;     // [red_grid] per-CTA sums of squared gradient entries (flyb_ppo_step)
+  int grid1, ctas_per_role, red_grid;
   size_t bytes;
 };
 
@@ -908,6 +932,8 @@ static Ws carve_ws(const FlybNetLayout& net, long long rows, void* basep) {
   w.im.dzmv = take(R * F_DZMV); w.im.dzh2 = take(R * F_DZH2); w.im.dzh1 = take(R * F_DZH1);
   w.loss_part = take((size_t)sms * 2 + 64);
   w.dw_part = take((size_t)w.ctas_per_role * net.total);
+  w.red_grid = (net.total + RED_ELEMS - 1) / RED_ELEMS;
+  w.sq_part = take((size_t)w.red_grid);
   w.bytes = off;
   return w;
 }
@@ -922,7 +948,7 @@ size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows) {
 int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                 const float* obs, const float* action, const float* old_logp, const float* target,
                 const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
-                void* workspace, const FlybPeerGroup* peers, cudaStream_t st) {
+                void* workspace, const FlybPeerGroup* peers, cudaStream_t st, StepFuse* fuse) {
   using namespace tcb;
   const Ws w = carve_ws(*net, rows, workspace);
   const long long ntiles = (rows + TM - 1) / TM;
@@ -962,7 +988,13 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
   for (int i = 0; i < 12; ++i) { r.off[i] = net->off[i]; r.size[i] = sizes[i]; }
   r.total = net->total; r.nparts = w.ctas_per_role; r.nloss = w.grid1; r.inv_rows = ga.inv_rows;
-  const int red_grid = (net->total + RED_ELEMS - 1) / RED_ELEMS;
+  const int red_grid = w.red_grid;
+  if (fuse) {   // the caller goes straight on to Adam: the reduction also takes the squared norm and counts the step
+    r.sq_part = w.sq_part;
+    r.step = fuse->step;
+    fuse->sq_part = w.sq_part;
+    fuse->sq_parts = red_grid;
+  }
   if (peers)
     ppo_reduce_tc_kernel<true><<<red_grid, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
                                                                             make_peer_view(*peers));

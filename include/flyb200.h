@@ -120,7 +120,9 @@ int flyb_debug_set_trace(void* dev_buffer);
  *      `wpack`: the parameters re-laid as hi/lo TF32 operand slabs in the order the kernel's TMA producer
  *      consumes them.  flyb_wpack_bytes: size of that buffer, 0 when the shape is outside the tensor-core path
  *      (it covers num_obs <= 80 and num_act <= 32; the 42-DOF joint set uses the CUDA-core fp32 path).
- *      flyb_pack_weights must be re-run whenever `params` changes (flyb_ppo_apply does it when given wpack).
+ *      The buffer also holds, behind the slabs, the parameter -> slab index flyb_pack_weights builds.
+ *      flyb_pack_weights must be re-run whenever `params` changes by other hands (flyb_ppo_apply / flyb_ppo_step
+ *      keep a given wpack in step themselves).
  *      Every entry point below that takes `wpack` accepts NULL = exact-fp32 CUDA-core path. */
 size_t flyb_wpack_bytes(const FlybNetLayout* net);
 int flyb_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, void* stream);
@@ -222,7 +224,8 @@ int flyb_peer_stamps(const FlybPeerGroup* group, uint64_t* out8);
  * flyb_ppo_apply: grad *= grad_scale; clip_grad_norm_(max_grad_norm) with torch's coefficient
  *   min(1, max/(norm+1e-6)); Adam (torch defaults, no weight decay).  step (1) i64 device counter, incremented.
  *   grad_norm_out (1) nullable.  workspace: the flyb_ppo_grad workspace (only its first 1 KB is used).
- *   wpack (nullable): re-packed from the updated parameters in the same call.
+ *   wpack (nullable): refreshed from the updated parameters by the Adam kernel itself (it must have been
+ *   initialised by flyb_pack_weights, which also builds the parameter -> stream index behind the slabs).
  *   peers (nullable): grad <- sum over ranks of the pushed gradients first (pass grad_scale = 1/world);
  *   NULL: `grad` is taken as it is (single GPU, or the caller all-reduced it, e.g. with NCCL). */
 size_t flyb_ppo_workspace_bytes(const FlybNetLayout* net, int64_t rows);
@@ -233,6 +236,15 @@ int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* 
 int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, float* grad, float* exp_avg,
                    float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out, void* workspace,
                    void* wpack, const FlybPeerGroup* peers, void* stream);
+/* Single-GPU optimiser step in one call: flyb_ppo_grad followed by flyb_ppo_apply(grad_scale = 1) with nothing in
+ * between, which lets the library drop two launches: the gradient reduction also takes the squared norm and counts
+ * the step, and the Adam kernel refreshes `wpack` in place through the index flyb_pack_weights built (4 launches:
+ * forward/backward chain, weight gradients, reduce, clip + Adam).  Same results as the two calls up to the
+ * association of the norm's partial sums.  `grad` ends as p.grad after clipping, as with flyb_ppo_apply. */
+int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack, const float* obs,
+                  const float* action, const float* old_logp, const float* target, const float* advantage,
+                  const float* action_var, int64_t rows, float* grad, float* loss, float* exp_avg, float* exp_avg_sq,
+                  int64_t* step, float* grad_norm_out, void* workspace, void* stream);
 
 /* action_var <- max(floor, action_var - decay) (ppo.py:236-237), on the device so a captured graph can replay it;
  * step_counter (1, nullable) u64 += 1 (the Philox draw number of flyb_policy_act). */

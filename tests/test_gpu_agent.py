@@ -376,3 +376,63 @@ def test_ppo_grad_is_deterministic():
         outs.append((grad.clone(), loss.clone()))
     for grad, loss in outs[1:]:
         assert torch.equal(grad, outs[0][0]) and torch.equal(loss, outs[0][1])
+
+
+def _fresh_pack(net):
+    """A second weight stream packed from scratch from the net's CURRENT parameters."""
+    lib = _lib.lib()
+    buf = torch.zeros_like(net.wpack)
+    _lib.check(lib.flyb_pack_weights(C.byref(net.layout), _lib.ptr(net.flat), _lib.ptr(buf), _lib.current_stream()))
+    torch.cuda.synchronize()
+    return buf
+
+
+def test_ppo_step_is_grad_plus_apply_and_keeps_the_weight_stream_in_step():
+    """flyb_ppo_step (norm taken by the gradient reduction, weight stream refreshed in place by the Adam kernel)
+    against flyb_ppo_grad + flyb_ppo_apply on the same minibatch, three optimiser steps in a row; after every step the
+    in-place refreshed stream must equal a from-scratch flyb_pack_weights of the new parameters bit for bit."""
+    g = load_golden("ppo_n64_t32.npz")
+    n, t_roll, mc = [int(x) for x in g["meta"]]
+    lib, p = _lib.lib(), _lib.ptr
+    cfg = _lib.PpoCfg(0.2, 1e-3, 0.9, 0.999, 1e-8, 1.0)
+    rows = mc * n
+    dv = [x.contiguous().to(DEV) for x in (g["roll_obs"][0:mc], g["roll_acts"][0:mc], g["roll_logp"][0:mc],
+                                           g["roll_target"][0:mc], g["roll_adv"][0:mc], g["roll_var"])]
+    out = {}
+    for mode in ("split", "fused"):
+        net = golden_net(g)
+        ws = torch.zeros(lib.flyb_ppo_workspace_bytes(C.byref(net.layout), rows) + 256, dtype=torch.uint8, device=DEV)
+        wsp = (ws.data_ptr() + 255) // 256 * 256
+        grad, loss = torch.zeros_like(net.flat), torch.zeros(1, device=DEV)
+        m, v = torch.zeros_like(net.flat), torch.zeros_like(net.flat)
+        step, gn = torch.zeros(1, dtype=torch.int64, device=DEV), torch.zeros(1, device=DEV)
+        lay, st = C.byref(net.layout), _lib.current_stream()
+        norms = []
+        for it in range(3):
+            if mode == "split":
+                _lib.check(lib.flyb_ppo_grad(lay, C.byref(cfg), p(net.flat), p(net.wpack), p(dv[0]), p(dv[1]), p(dv[2]),
+                                             p(dv[3]), p(dv[4]), p(dv[5]), rows, p(grad), p(loss), wsp, None, st))
+                _lib.check(lib.flyb_ppo_apply(lay, C.byref(cfg), p(net.flat), p(grad), p(m), p(v), p(step), 1.0, p(gn),
+                                              wsp, p(net.wpack), None, st))
+            else:
+                _lib.check(lib.flyb_ppo_step(lay, C.byref(cfg), p(net.flat), p(net.wpack), p(dv[0]), p(dv[1]), p(dv[2]),
+                                             p(dv[3]), p(dv[4]), p(dv[5]), rows, p(grad), p(loss), p(m), p(v), p(step),
+                                             p(gn), wsp, st))
+            torch.cuda.synchronize()
+            assert int(step.item()) == it + 1
+            if net.wpack is not None:   # (the CUDA-core variant of this test has no weight stream)
+                slabs = net.wpack.numel() - net.layout.total * 16      # behind them: the parameter -> slab index
+                assert torch.equal(net.wpack[:slabs], _fresh_pack(net)[:slabs]), \
+                    f"{mode}: weight stream out of step after step {it + 1}"
+            norms.append(float(gn))
+            if it == 0:
+                out[mode] = [net.flat.clone(), m.clone(), v.clone(), loss.clone()]
+        out[mode] += [float(loss), norms]
+    a, b = out["split"], out["fused"]
+    # step 1: same gradient bit for bit; the two differ only in how the norm's partial sums are grouped, i.e. the
+    # clip coefficient moves by an ulp or two.  Later steps start from those ulp-apart parameters.
+    assert torch.equal(a[3], b[3])
+    for x, y, name in zip(a[:3], b[:3], ("params", "exp_avg", "exp_avg_sq")):
+        torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-7, msg=name)
+    assert a[4] == pytest.approx(b[4], rel=1e-4)
+    assert a[5] == pytest.approx(b[5], rel=1e-4)
