@@ -422,6 +422,7 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
 // ------------------------------------------------------------------------------------------------ host side
 static unsigned long long* g_trace = nullptr;   // debug timeline buffer (flyb_debug_set_trace), normally NULL
 void tc_set_trace(void* p) { g_trace = (unsigned long long*)p; }
+unsigned long long* tc_get_trace() { return g_trace; }
 bool tc_supported(const FlybNetLayout* net) { return net->k0_pad == tcm::K0 && net->num_act <= tcm::APAD; }
 
 // wpack = [weight stream: total_stages x 8 KB][inverse index: net->total x 4 int32]

@@ -36,6 +36,7 @@ namespace flyb {
 int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
 bool tc_supported(const FlybNetLayout* net);
+unsigned long long* tc_get_trace();
 
 struct StepFuse {   // see ppo_kernels.cu
   long long* step;
@@ -199,8 +200,11 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       pa ^= 1u << b;
       tc::tc_fence_after();
     };
+    int ti = 0;
+    unsigned long long* mtrace = (lane == 0) ? a.trace : nullptr;   // slots [0,64): "operand ready" / "MMAs issued" pairs
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       wait_a(0);   // X staged (and the previous tile's accumulators drained)
+      trace_mark(mtrace, ti, 64);
 #pragma unroll 1
       for (int c = -2; c < NCH; ++c) {
         if (c >= 0) {
@@ -215,24 +219,35 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
         }
       }
       umma_commit_if(m.leader, &s.bar_d[0]);   // D2
+      trace_mark(mtrace, ti, 64);
       wait_a(0);                               // A3
+      trace_mark(mtrace, ti, 64);
       mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3, false);
       mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3 + H3, false);
       umma_commit_if(m.leader, &s.bar_d[0]);   // D3
+      trace_mark(mtrace, ti, 64);
       wait_a(0);                               // A4
+      trace_mark(mtrace, ti, 64);
       mma_segment<APAD, H3 / 8, false>(m, tb + C_A4H, tb + C_A4L, tb + C_D4B, false);
       umma_commit_if(m.leader, &s.bar_d[0]);   // D4
+      trace_mark(mtrace, ti, 64);
       wait_a(0);                               // A5 = dZmu (and dZv1 in its A6 slots)
+      trace_mark(mtrace, ti, 64);
       mma_segment<H3, APAD / 8, false>(m, tb + C_A5H, tb + C_A5L, tb + C_D5, false);
       umma_commit_if(m.leader, &s.bar_d[0]);   // D5 = dM1
+      trace_mark(mtrace, ti, 64);
       wait_a(0);                               // A6 = [dZm1 | dZv1]
+      trace_mark(mtrace, ti, 64);
       mma_segment<H2, 2 * H3 / 8, false>(m, tb + C_A6H, tb + C_A6L, tb + C_D6, false);
       umma_commit_if(m.leader, &s.bar_d[0]);   // D6 = dH2
+      trace_mark(mtrace, ti, 64);
       wait_a(0);                               // A7 = dZh2
+      trace_mark(mtrace, ti, 64);
       mma_segment<128, H2 / 8, false>(m, tb + C_A7H, tb + C_A7L, tb + C_D7, false);
       umma_commit_if(m.leader, &s.bar_d[0]);   // D7, h1 features [0,128)
       mma_segment<128, H2 / 8, false>(m, tb + C_A7H, tb + C_A7L, tb + C_D7 + 128, false);
       umma_commit_if(m.leader, &s.bar_d[1]);   // D7, h1 features [128,256)
+      trace_mark(mtrace, ti, 64);
     }
   } else {
     // =========================================================================== epilogue warps
@@ -243,16 +258,20 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
     uint32_t pd = 0u, obs_phase = 0u;
     float surr_sum = 0.0f, sl1_sum = 0.0f;
     const float a_log_2pi = (float)((double)A * 1.8378770664093453);
+    int ti = 64;
+    unsigned long long* etrace = (threadIdx.x == 0) ? a.trace : nullptr;   // slots [64,128): accumulator seen / operand handed over
     auto wait_d = [&](int b) {
       tc::mbar_wait(&s.bar_d[b], (pd >> b) & 1u);
       pd ^= 1u << b;
       tc::tc_fence_after();
+      trace_mark(etrace, ti, 128);
     };
     auto arrive_a = [&](int b) {
       tc::tmem_wait_st();
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&s.bar_a[b]);
+      trace_mark(etrace, ti, 128);
     };
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const long long row0 = tile * TM;
@@ -952,7 +971,7 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   using namespace tcb;
   const Ws w = carve_ws(*net, rows, workspace);
   const long long ntiles = (rows + TM - 1) / TM;
-  FwdArgs fa{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, 0, nullptr};
+  FwdArgs fa{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, 0, tc_get_trace()};
   GradArgs ga{};
   ga.action = action; ga.old_logp = old_logp; ga.target = target; ga.advantage = advantage; ga.action_var = action_var;
   ga.clip_lo = (float)(1.0 - cfg->clip);
