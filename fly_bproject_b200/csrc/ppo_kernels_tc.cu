@@ -100,8 +100,15 @@ FLYB_D void epi_elu_save(uint32_t d_addr, uint32_t ah_addr, uint32_t al_addr, co
     tc::tmem_ld16(d_addr + c, v);
     tc::tmem_wait_ld();
     float y[16];
+    const float4* b4 = reinterpret_cast<const float4*>(bias + c);   // bias block offsets are multiples of 16 floats
 #pragma unroll
-    for (int j = 0; j < 16; ++j) y[j] = elu_fast(__uint_as_float(v[j]) + bias[c + j]);
+    for (int q4 = 0; q4 < 4; ++q4) {
+      const float4 b = b4[q4];
+      y[4 * q4 + 0] = elu_fast(__uint_as_float(v[4 * q4 + 0]) + b.x);
+      y[4 * q4 + 1] = elu_fast(__uint_as_float(v[4 * q4 + 1]) + b.y);
+      y[4 * q4 + 2] = elu_fast(__uint_as_float(v[4 * q4 + 2]) + b.z);
+      y[4 * q4 + 3] = elu_fast(__uint_as_float(v[4 * q4 + 3]) + b.w);
+    }
     tmem_put16(ah_addr + c, al_addr + c, y);
     img_store16(img + (c >> 2) * 32, y);
   }
@@ -112,7 +119,8 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
                       const __grid_constant__ GradArgs ga, const __grid_constant__ Images im) {
   extern __shared__ unsigned char smem_raw[];
   const Smem s = carve(smem_raw, a.O, 0);
-  __shared__ float s_std[APAD], s_inv_var[APAD];
+  __shared__ float s_std[APAD], s_inv_std[APAD], s_inv_var[APAD];
+  __shared__ __align__(16) float s_act[TM * APAD];   // the tile's actions, row-major with the real stride A
   __shared__ float s_half_log_det;
   __shared__ float s_vp[2 * TM];
   __shared__ float s_red[EPI_WARPS][2];
@@ -140,6 +148,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       const float var = threadIdx.x < A ? __ldg(ga.action_var + threadIdx.x) : 1.0f;
       const float sd = sqrtf(var);
       s_std[threadIdx.x] = sd;
+      s_inv_std[threadIdx.x] = 1.0f / sd;
       s_inv_var[threadIdx.x] = 1.0f / (sd * sd);
     }
   }
@@ -321,6 +330,17 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(s.obs_empty);
       arrive_a(0);
+      // the tile's actions -> shared memory, asynchronously (consumed by the policy head, behind a barrier)
+      {
+        const float* asrc = ga.action + (size_t)row0 * A;
+        const int nfl = nrows * A;
+        if ((nfl & 3) == 0 && (reinterpret_cast<uintptr_t>(asrc) & 15u) == 0) {
+          for (int i = threadIdx.x * 4; i < nfl; i += EPI_THREADS * 4) cp_async16(s_act + i, asrc + i);
+        } else {
+          for (int i = threadIdx.x; i < nfl; i += EPI_THREADS) s_act[i] = __ldg(asrc + i);
+        }
+        cp_async_commit();
+      }
 
       // ---- trunk
 #pragma unroll 1
@@ -362,6 +382,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
         }
         s_vp[h * TM + r] = part;
         const float tgt = live ? __ldg(ga.target + row) : 0.0f;
+        cp_async_wait<0>();   // this thread's share of the action tile has landed; the barrier publishes all of it
         tc::tc_fence_before();
         epi_bar_sync();
         const float value = s_vp[r] + s_vp[TM + r] + s.bias[B_B4V];
@@ -383,7 +404,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       {
         float act[APAD];
 #pragma unroll
-        for (int k = 0; k < APAD; ++k) act[k] = (live && k < A) ? __ldg(ga.action + (size_t)row * A + k) : 0.0f;
+        for (int k = 0; k < APAD; ++k) act[k] = (live && k < A) ? s_act[r * A + k] : 0.0f;
         const float old_lp = live ? __ldg(ga.old_logp + row) : 0.0f;
         const float adv = live ? __ldg(ga.advantage + row) : 0.0f;
         wait_d(0);   // D4
@@ -400,7 +421,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
 #pragma unroll
         for (int k = 0; k < APAD; ++k)
           if (k < A) {
-            const float diff = (act[k] - mu[k]) / s_std[k];
+            const float diff = (act[k] - mu[k]) * s_inv_std[k];
             msum += diff * diff;
           }
         const float logp = -0.5f * (a_log_2pi + msum) - s_half_log_det;
