@@ -631,7 +631,10 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
     if (tc::elect_one()) {
       uint32_t slot = 0, phase = 0;
       int within = 0;
-      long long tile = ci;
+      // Newest tiles first: the chain kernel has just written 153 MB of row images through a 126 MB L2.  Reading them
+      // back oldest-first would miss on everything (each miss evicts the next-oldest lines, the ones wanted next);
+      // youngest-first finds most of them still resident.  CTA ci owns tiles ntiles-1-ci, ntiles-1-ci-cpr, ...
+      long long tile = a.ntiles - 1 - ci;
       for (long long st = 0; st < nstages; ++st) {
         const int pi = within >= (16 / DW_KG) ? 1 : 0, kg = within - pi * (16 / DW_KG);
         const DwPair& p = role.pair[pi];
@@ -644,7 +647,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         tc::tma_load_1d(dst, ga, a_bytes, &raw_full[slot]);
         tc::tma_load_1d(dst + a_bytes, gb, b_bytes, &raw_full[slot]);
         if (++slot == DW_RAW_SLOTS) { slot = 0; phase ^= 1u; }
-        if (++within == stages_per_tile) { within = 0; tile += a.ctas_per_role; }
+        if (++within == stages_per_tile) { within = 0; tile -= a.ctas_per_role; }
       }
     }
   } else if (warp == 1) {
