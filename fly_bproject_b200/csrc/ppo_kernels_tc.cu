@@ -580,6 +580,8 @@ struct DwArgs {
   int off[12];
   int A;
   int dbg;              // timing experiments only (FLYB_DW_DBG): 1 skip transposition, 2 skip MMAs, 4 skip flush
+  unsigned long long* trace;   // debug (flyb_debug_set_trace): CTA 0's clock64 marks, [0,64) producer: slot free seen,
+                               // [64,128) transposer warp 0: stage in hand / handed on, [128,190) MMA warp: operands seen
 };
 
 __global__ void __launch_bounds__(DW_THREADS, 1)
@@ -639,6 +641,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         const int pi = within >= (16 / DW_KG) ? 1 : 0, kg = within - pi * (16 / DW_KG);
         const DwPair& p = role.pair[pi];
         tc::mbar_wait_relaxed(&raw_empty[slot], phase ^ 1u);
+        if (a.trace != nullptr && blockIdx.x == 0 && st < 64) a.trace[st] = clock64();
         const uint32_t a_bytes = (uint32_t)DW_KG * p.MA * 32u, b_bytes = (uint32_t)DW_KG * p.NB * 32u;
         tc::mbar_arrive_expect_tx(&raw_full[slot], a_bytes + b_bytes);
         unsigned char* dst = raw + slot * DW_RAW_SLOT;
@@ -661,6 +664,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
       const DwPair& p = role.pair[pi];
       tc::mbar_wait(&op_full[slot], phase);
       tc::tc_fence_after();
+      if (a.trace != nullptr && blockIdx.x == 0 && lane == 0 && st < 62) a.trace[128 + st] = clock64();
       const uint32_t pa_b = dw_plane_bytes(p.MA), pb_b = dw_plane_bytes(p.NB);
       const uint32_t a_lbo = (uint32_t)p.MA * 16u + 16u, b_lbo = (uint32_t)p.NB * 16u + 16u;
       const uint32_t sbase = tc::smem_u32(ops) + slot * DW_OP_SLOT;
@@ -731,8 +735,10 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
     for (long long st = 0; st < nstages; ++st) {
       const int pi = within >= (16 / DW_KG) ? 1 : 0;
       tc::mbar_wait(&raw_full[rslot], rphase);
+      if (a.trace != nullptr && blockIdx.x == 0 && tid == 0 && st < 21) a.trace[64 + 3 * st] = clock64();
       tc::mbar_wait(&op_empty[oslot], ophase ^ 1u);
       tc::tc_fence_after();
+      if (a.trace != nullptr && blockIdx.x == 0 && tid == 0 && st < 21) a.trace[65 + 3 * st] = clock64();
       const float4* src4 = reinterpret_cast<const float4*>(raw + rslot * DW_RAW_SLOT);
       unsigned char* odst = ops + oslot * DW_OP_SLOT;
 #pragma unroll
@@ -773,6 +779,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         tc::mbar_arrive(&raw_empty[rslot]);
         tc::mbar_arrive(&op_full[oslot]);
       }
+      if (a.trace != nullptr && blockIdx.x == 0 && tid == 0 && st < 21) a.trace[66 + 3 * st] = clock64();
       if (++rslot == DW_RAW_SLOTS) { rslot = 0; rphase ^= 1u; }
       if (++oslot == DW_OP_SLOTS) { oslot = 0; ophase ^= 1u; }
       if (++within == stages_per_tile) within = 0;
@@ -1020,6 +1027,7 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   d.net_total = net->total;
   for (int i = 0; i < 12; ++i) d.off[i] = net->off[i];
   d.A = net->num_act;
+  d.trace = tc_get_trace();
   { const char* e = getenv("FLYB_DW_DBG"); d.dbg = e ? atoi(e) : 0; }
   const size_t smem2 = 1024 + (size_t)DW_RAW_SLOTS * DW_RAW_SLOT + (size_t)DW_OP_SLOTS * DW_OP_SLOT + 512 + 2048 + 256;
   if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel), smem2)) != FLYB_OK) return rc;

@@ -26,6 +26,21 @@ _lib.check(agent.lib.flyb_debug_set_trace(trace.data_ptr()))
 agent._minibatch(0, agent.mini_chunk_size)
 torch.cuda.synchronize()
 agent.lib.flyb_debug_set_trace(None)
+if len(sys.argv) > 1 and sys.argv[1] == "dw":
+    # the weight-gradient kernel ran last and overwrote the buffer: its marks (see DwArgs::trace)
+    t = trace.cpu().tolist()
+    t0 = min(x for x in t if x > 0)
+    prod = [x - t0 for x in t[:64] if x > 0]
+    tr = [x - t0 if x > 0 else -1 for x in t[64:127]]
+    mma = [x - t0 for x in t[128:190] if x > 0]
+    print("producer: raw slot free seen, per stage:", prod)
+    print("transposer w0 (raw full seen, op slot free seen, handed on) per stage:",
+          [tuple(tr[3 * i:3 * i + 3]) for i in range(21)])
+    print("MMA warp: operands seen, per stage:", mma)
+    d = [b - a for a, b in zip(mma, mma[1:])]
+    print("MMA stage period (cycles): min %d median %d max %d; %d stages, last at %d" % (
+        min(d), sorted(d)[len(d) // 2], max(d), len(mma), mma[-1]))
+    sys.exit(0)
 t = trace.cpu().tolist()
 t0 = min(x for x in t[:128] if x > 0)
 mm = [x - t0 for x in t[:64] if x > 0]
