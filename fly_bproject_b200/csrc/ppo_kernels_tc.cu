@@ -1002,7 +1002,9 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   using namespace tcb;
   const Ws w = carve_ws(*net, rows, workspace);
   const long long ntiles = (rows + TM - 1) / TM;
-  FwdArgs fa{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, 0, tc_get_trace()};
+  static const bool trace_dw = getenv("FLYB_TRACE_DW") != nullptr;   // which of the two kernels fills the debug trace
+  FwdArgs fa{obs, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, 0,
+             trace_dw ? nullptr : tc_get_trace()};
   GradArgs ga{};
   ga.action = action; ga.old_logp = old_logp; ga.target = target; ga.advantage = advantage; ga.action_var = action_var;
   ga.clip_lo = (float)(1.0 - cfg->clip);
@@ -1027,7 +1029,7 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   d.net_total = net->total;
   for (int i = 0; i < 12; ++i) d.off[i] = net->off[i];
   d.A = net->num_act;
-  d.trace = tc_get_trace();
+  d.trace = trace_dw ? tc_get_trace() : nullptr;
   { const char* e = getenv("FLYB_DW_DBG"); d.dbg = e ? atoi(e) : 0; }
   const size_t smem2 = 1024 + (size_t)DW_RAW_SLOTS * DW_RAW_SLOT + (size_t)DW_OP_SLOTS * DW_OP_SLOT + 512 + 2048 + 256;
   if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel), smem2)) != FLYB_OK) return rc;

@@ -8,6 +8,9 @@ import ctypes as C
 import os
 import sys
 
+if len(sys.argv) > 1 and sys.argv[1] == "dw":
+    os.environ["FLYB_TRACE_DW"] = "1"      # read by the library at its first PPO gradient call
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
