@@ -342,6 +342,11 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
         cp_async_commit();
       }
 
+      // per-row scalars of the heads, fetched now so that their latency is long gone when the heads need them
+      const float tgt = live ? __ldg(ga.target + row) : 0.0f;
+      const float old_lp = live ? __ldg(ga.old_logp + row) : 0.0f;
+      const float adv = live ? __ldg(ga.advantage + row) : 0.0f;
+
       // ---- trunk
 #pragma unroll 1
       for (int c = 0; c < NCH; ++c) {
@@ -381,7 +386,6 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
           img_store16(img_ptr(mv_t, F_MV, r, H3 + c0), y);
         }
         s_vp[h * TM + r] = part;
-        const float tgt = live ? __ldg(ga.target + row) : 0.0f;
         cp_async_wait<0>();   // this thread's share of the action tile has landed; the barrier publishes all of it
         tc::tc_fence_before();
         epi_bar_sync();
@@ -405,8 +409,6 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
         float act[APAD];
 #pragma unroll
         for (int k = 0; k < APAD; ++k) act[k] = (live && k < A) ? s_act[r * A + k] : 0.0f;
-        const float old_lp = live ? __ldg(ga.old_logp + row) : 0.0f;
-        const float adv = live ? __ldg(ga.advantage + row) : 0.0f;
         wait_d(0);   // D4
         float mu[APAD];
 #pragma unroll
