@@ -606,9 +606,14 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int role_id = blockIdx.x & 1, ci = blockIdx.x >> 1;
   const DwRole& role = a.role[role_id];
-  const long long my_tiles = (a.ntiles - ci + a.ctas_per_role - 1) / a.ctas_per_role;   // >= 1 by construction
-  const int stages_per_tile = 2 * (16 / DW_KG);                    // both pairs
-  const long long nstages = my_tiles * stages_per_tile;
+  // Work is dealt out by STAGE, not by tile: stage g = (tile, pair, k-step group) in a linear order, CTA ci of a role
+  // takes g = ci, ci + cpr, ci + 2 cpr, ...  (4096 stages over 74 CTAs: 55 or 56 each, where whole tiles gave 48 or 64).
+  // Any subset of stages may be summed in any CTA — a pair's accumulator is a sum over rows — and since cpr <= ntiles
+  // every CTA meets at least 16 consecutive residues of g mod 16, i.e. both pairs.
+  constexpr int stages_per_tile = 2 * (16 / DW_KG);                // both pairs
+  static_assert(stages_per_tile == 16, "stage index -> (tile, pair, k-step group) by shifts");
+  const long long total_stages = a.ntiles * stages_per_tile;
+  const long long nstages = (total_stages - ci + a.ctas_per_role - 1) / a.ctas_per_role;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < DW_RAW_SLOTS; ++i) {
@@ -634,12 +639,13 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
     // =========================================================================== TMA producer
     if (tc::elect_one()) {
       uint32_t slot = 0, phase = 0;
-      int within = 0;
       // Newest tiles first: the chain kernel has just written 153 MB of row images through a 126 MB L2.  Reading them
       // back oldest-first would miss on everything (each miss evicts the next-oldest lines, the ones wanted next);
       // youngest-first finds most of them still resident.  CTA ci owns tiles ntiles-1-ci, ntiles-1-ci-cpr, ...
-      long long tile = a.ntiles - 1 - ci;
-      for (long long st = 0; st < nstages; ++st) {
+      long long g = ci;
+      for (long long st = 0; st < nstages; ++st, g += a.ctas_per_role) {
+        const long long tile = a.ntiles - 1 - (g >> 4);
+        const int within = (int)(g & 15);
         const int pi = within >= (16 / DW_KG) ? 1 : 0, kg = within - pi * (16 / DW_KG);
         const DwPair& p = role.pair[pi];
         tc::mbar_wait_relaxed(&raw_empty[slot], phase ^ 1u);
@@ -652,17 +658,16 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         tc::tma_load_1d(dst, ga, a_bytes, &raw_full[slot]);
         tc::tma_load_1d(dst + a_bytes, gb, b_bytes, &raw_full[slot]);
         if (++slot == DW_RAW_SLOTS) { slot = 0; phase ^= 1u; }
-        if (++within == stages_per_tile) { within = 0; tile -= a.ctas_per_role; }
       }
     }
   } else if (warp == 1) {
     // =========================================================================== MMA issuer
     const uint32_t leader = tc::elect_one() ? 1u : 0u;
     uint32_t slot = 0, phase = 0;
-    int within = 0;
-    bool first_tile = true;
-    for (long long st = 0; st < nstages; ++st) {
-      const int pi = within >= (16 / DW_KG) ? 1 : 0;
+    bool seen0 = false, seen1 = false;   // has this CTA already accumulated into the pair?
+    long long g = ci;
+    for (long long st = 0; st < nstages; ++st, g += a.ctas_per_role) {
+      const int pi = (int)(g & 15) >= (16 / DW_KG) ? 1 : 0;
       const DwPair& p = role.pair[pi];
       tc::mbar_wait(&op_full[slot], phase);
       tc::tc_fence_after();
@@ -671,7 +676,8 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
       const uint32_t a_lbo = (uint32_t)p.MA * 16u + 16u, b_lbo = (uint32_t)p.NB * 16u + 16u;
       const uint32_t sbase = tc::smem_u32(ops) + slot * DW_OP_SLOT;
       const uint32_t idesc = tc::umma_idesc_tf32(p.NB);
-      const bool first_stage_of_pair = first_tile && (within == 0 || within == 16 / DW_KG);
+      const bool first_stage_of_pair = pi ? !seen1 : !seen0;
+      if (pi) seen1 = true; else seen0 = true;
 #pragma unroll
       for (int j = 0; j < DW_KG; ++j) {
         const uint32_t a_hi = sbase + (uint32_t)j * 2u * (pa_b + pb_b), a_lo = a_hi + pa_b;
@@ -688,8 +694,8 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
       }
       umma_commit_if(leader, &op_empty[slot]);
       if (++slot == DW_OP_SLOTS) { slot = 0; phase ^= 1u; }
-      if (++within == stages_per_tile) { within = 0; first_tile = false; }
     }
+    if (!(seen0 && seen1)) __trap();   // the host picks cpr so that every CTA meets both pairs (carve_ws)
     umma_commit_if(leader, acc_done);
   } else {
     // =========================================================================== transposers, then flush
@@ -733,9 +739,9 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
     // this spreads a warp's 4-byte stores over all 32 banks.
     const uint32_t eo0 = eoff, eo1 = eoff + 16u, eo2 = eoff ^ 32u, eo3 = (eoff ^ 32u) + 16u;
     uint32_t rslot = 0, rphase = 0, oslot = 0, ophase = 0;
-    int within = 0;
-    for (long long st = 0; st < nstages; ++st) {
-      const int pi = within >= (16 / DW_KG) ? 1 : 0;
+    long long g = ci;
+    for (long long st = 0; st < nstages; ++st, g += a.ctas_per_role) {
+      const int pi = (int)(g & 15) >= (16 / DW_KG) ? 1 : 0;
       tc::mbar_wait(&raw_full[rslot], rphase);
       if (a.trace != nullptr && blockIdx.x == 0 && tid == 0 && st < 21) a.trace[64 + 3 * st] = clock64();
       tc::mbar_wait(&op_empty[oslot], ophase ^ 1u);
@@ -784,7 +790,6 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
       if (a.trace != nullptr && blockIdx.x == 0 && tid == 0 && st < 21) a.trace[66 + 3 * st] = clock64();
       if (++rslot == DW_RAW_SLOTS) { rslot = 0; rphase ^= 1u; }
       if (++oslot == DW_OP_SLOTS) { oslot = 0; ophase ^= 1u; }
-      if (++within == stages_per_tile) within = 0;
     }
     // ---- bias gradients: sum the 8 row lanes of every feature group, then one shared-memory add per contributor
     //      (at most two per slot, so the order cannot change the result)
@@ -978,6 +983,9 @@ static Ws carve_ws(const FlybNetLayout& net, long long rows, void* basep) {
   const int sms = num_sms();
   w.grid1 = (int)std::min<long long>(ntiles, sms);
   w.ctas_per_role = (int)std::max<long long>(1, std::min<long long>(ntiles, sms / 2));
+  // stages are dealt with stride cpr (ppo_dw_tc_kernel): a stride that is a multiple of 16 would pin a CTA to one
+  // (pair, k-step group) and leave its other pair's accumulators untouched
+  if (w.ctas_per_role > 1 && w.ctas_per_role % 16 == 0) w.ctas_per_role -= 1;
   w.norm_part = take(256);   // NORM_BLOCKS floats (ppo_kernels.cu)
   w.im.x = take(R * F_X); w.im.h1 = take(R * F_H1); w.im.h2 = take(R * F_H2); w.im.mv = take(R * F_MV);
   w.im.dzmuv = take(R * F_DZMUV + 4096);   // + slack: the M = 128 MMA of the 64-feature operand never reads it, TMA does not either
