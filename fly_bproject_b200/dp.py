@@ -17,6 +17,7 @@ The plain helpers are device-agnostic (NCCL on the GPUs, gloo in the CPU tests).
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import os
 from typing import List, Optional, Tuple
@@ -85,7 +86,9 @@ class PeerExchange:
         self.error = ""
         self.group = _lib.PeerGroup(self.rank, self.world_size, self._L.flyb_peer_total_pad(total), 0)
         raw: Optional[bytes] = None
-        with torch.cuda.device(device):
+        device = torch.device(device)
+        ctx = torch.cuda.device(device) if device.type == "cuda" else contextlib.nullcontext()
+        with ctx:
             try:
                 if self.world_size > _lib.MAX_PEERS:
                     raise _lib.FlybError(f"covers up to {_lib.MAX_PEERS} ranks of one NVLink domain, got {self.world_size}")

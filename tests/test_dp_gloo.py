@@ -65,6 +65,13 @@ def _worker(rank, world_size, port, steps, out_path):
         for _ in range(steps):
             loss, _, _ = fo.minibatch_step(p, st, obs, act, logp, target, adv, var, grad_hook=hook)
             losses.append(loss)
+        # No CUDA device here: every rank fails to allocate its exchange buffer, the ranks agree on that collectively
+        # (nobody is left waiting in a different mode) and the NCCL/gloo all-reduce path is selected.
+        os.environ.pop("FLYB_DP", None)
+        assert dp.exchange_mode() == "peer"
+        assert dp.make_exchange(1000, torch.device("cpu")) is None
+        os.environ["FLYB_DP"] = "nccl"
+        assert dp.make_exchange(1000, torch.device("cpu")) is None
         torch.save({"p": p, "loss": losses}, f"{out_path}.{rank}")
     finally:
         dist.destroy_process_group()
@@ -86,6 +93,12 @@ def test_env_shard_blocks():
     assert dp.world() == (0, 1)
     g = torch.ones(5)
     assert dp.grad_all_reduce_(g) == 1.0 and torch.equal(g, torch.ones(5))
+    os.environ["FLYB_DP"] = "bogus"
+    try:
+        with pytest.raises(ValueError):
+            dp.exchange_mode()
+    finally:
+        del os.environ["FLYB_DP"]
 
 
 @pytest.mark.timeout(300)
