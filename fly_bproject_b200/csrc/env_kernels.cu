@@ -17,6 +17,7 @@
 #include "env_math.cuh"
 
 namespace flyb {
+unsigned long long* tc_get_trace();
 
 constexpr int ENVS = 64;           // envs per CTA
 constexpr int PP_THREADS = 256;    // 4 threads per env for the load / store sweeps; threads [0, ENVS) own one env each
@@ -53,7 +54,14 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
                     float* __restrict__ up_vec, float* __restrict__ heading_vec, int* __restrict__ reset_ids,
                     int* __restrict__ reset_count, ScanScratch* __restrict__ scratch, float* __restrict__ obs_copy,
                     float* __restrict__ reward_copy, float* __restrict__ reward_sum,
-                    const __grid_constant__ FlybStepTail tail) {
+                    const __grid_constant__ FlybStepTail tail, unsigned long long* __restrict__ trace) {
+  // debug (flyb_debug_set_trace): thread 0 of CTA 0 marks [160..]: entry, loads issued, loads consumed, per-env math
+  // done, reward + masks done, mask published, obs slab out; thread 0 of the LAST CTA marks [170..]: last seen, ids out
+  int tmark = 160;
+  auto mark = [&]() {
+    if (trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && tmark < 170) trace[tmark++] = clock64();
+  };
+  mark();
   extern __shared__ __align__(16) float smem[];
   const int N = cfg.num_envs, D = cfg.num_dof, A = cfg.num_act, B = cfg.num_bodies;
   const int O = 19 + 3 * A;
@@ -146,6 +154,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
       }
     }
   }
+  mark();   // every load of this thread has been issued; the first dependent use follows
   if (tid * 4 + 3 < nroot) reinterpret_cast<float4*>(root_s)[tid] = r4;
   for (int i = (nroot & ~3) + tid; i < nroot; i += PP_THREADS) root_s[i] = __ldg(root + (size_t)env0 * 13 + i);
 #pragma unroll
@@ -154,6 +163,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     if (e_ok && rc < FORCE_VALS) force_s[e * FORCE_VALS + rc] = fv[it];
   }
   __syncthreads();
+  mark();
 
   // ---- per-env math, split over four warp pairs (independent dependency chains instead of one long one; a role is
   //      a whole warp, so nothing diverges):  role 0: potential, heading / up projections, later reward + termination;
@@ -209,6 +219,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     }
   }
   __syncthreads();
+  mark();
   bool flag = false;
   float my_reward = 0.0f;
   if (role == 0 && me_ok) {
@@ -254,6 +265,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     }
   }
   __syncthreads();
+  mark();
   static_assert(ENVS == 64, "one 64-bit reset mask per CTA");
   unsigned long long* bitmap = scratch->status;
   // publish the mask and count this CTA as done BEFORE its obs slab leaves: the CTA that sees the counter complete
@@ -264,6 +276,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     __threadfence();
     done_prev = atomicAdd(&scratch->done, 1u);
   }
+  mark();
 
   // ---- obs slab out: full 128-bit stores (slab base 16B aligned: ENVS*O*4 % 16 == 0)
   {
@@ -282,6 +295,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     }
   }
 
+  mark();
   // ---- the last CTA to finish turns the bitmap into the ascending id list (== reset_buf.nonzero(), fly.py:447)
   if (tid == 0) {
     s_last = (done_prev == gridDim.x - 1) ? 1 : 0;
@@ -289,6 +303,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   }
   __syncthreads();
   if (!s_last) return;
+  if (trace != nullptr && tid == 0) trace[170] = clock64();
   // each thread owns a contiguous run of W masks: one sweep to count, one block scan, one sweep to write its ids
   const int nblk = (int)gridDim.x;
   const int W = (nblk + PP_THREADS - 1) / PP_THREADS;
@@ -321,6 +336,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   if (tid == 0) {
     *reset_count = base;
     scratch->done = 0u;                                 // re-armed for the next launch
+    if (trace != nullptr) trace[171] = clock64();
   }
   if (tail.action_var != nullptr) {   // end-of-step housekeeping (ppo.py:236-237), once per launch
     for (int i = tid; i < tail.num_act; i += PP_THREADS)
@@ -437,7 +453,7 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
   post_physics_kernel<<<grid, PP_THREADS, smem, (cudaStream_t)stream>>>(
       *cfg, root, dof_state, force, actions_scaled, potentials, prev_potentials, (long long*)progress,
       (long long*)reset, obs, reward, up_vec, heading_vec, reset_ids, reset_count, (ScanScratch*)scratch, obs_copy,
-      reward_copy, reward_sum, t);
+      reward_copy, reward_sum, t, tc_get_trace());
   FLYB_LAUNCH_CHECK("post_physics_kernel");
   return FLYB_OK;
 }

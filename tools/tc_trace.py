@@ -23,8 +23,13 @@ agent._step_kernels(0)
 torch.cuda.synchronize()
 agent.lib.flyb_debug_set_trace(None)
 t = trace.cpu().tolist()
-t0 = min(x for x in t if x > 0)
+t0 = min(x for x in t[:160] + t[190:] if x > 0)     # act kernel marks only ([160,172): post_physics)
 print("MMA thread :", [x - t0 for x in t[:64] if x > 0])
 print("epilogue w0:", [x - t0 for x in t[64:128] if x > 0])
 print("finaliser  :", [x - t0 for x in t[128:160] if x > 0])
 print("kernel entry / exit (thread 0):", t[190] - t0, t[191] - t0)
+pp = t[160:172]
+print("post_physics CTA 0 thread 0 (entry, loads issued, loads consumed, math done, reward+masks, mask published, obs out):",
+      [x - pp[0] for x in pp[:7] if x > 0])
+print("post_physics last CTA (becomes last, ids + count out), relative to CTA 0's entry:",
+      [x - pp[0] for x in pp[10:12] if x > 0])
