@@ -56,7 +56,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
                     float* __restrict__ reward_copy, float* __restrict__ reward_sum,
                     const __grid_constant__ FlybStepTail tail, unsigned long long* __restrict__ trace) {
   // debug (flyb_debug_set_trace): thread 0 of CTA 0 marks [160..]: entry, loads issued, loads consumed, per-env math
-  // done, reward + masks done, mask published, obs slab out; thread 0 of the LAST CTA marks [170..]: last seen, ids out
+  // done, reward + masks done, mask published, obs slab out (clock64 is per SM: marks of other CTAs would not compare)
   int tmark = 160;
   auto mark = [&]() {
     if (trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && tmark < 170) trace[tmark++] = clock64();
@@ -303,7 +303,6 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   }
   __syncthreads();
   if (!s_last) return;
-  if (trace != nullptr && tid == 0) trace[170] = clock64();
   // each thread owns a contiguous run of W masks: one sweep to count, one block scan, one sweep to write its ids
   const int nblk = (int)gridDim.x;
   const int W = (nblk + PP_THREADS - 1) / PP_THREADS;
@@ -336,7 +335,6 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   if (tid == 0) {
     *reset_count = base;
     scratch->done = 0u;                                 // re-armed for the next launch
-    if (trace != nullptr) trace[171] = clock64();
   }
   if (tail.action_var != nullptr) {   // end-of-step housekeeping (ppo.py:236-237), once per launch
     for (int i = tid; i < tail.num_act; i += PP_THREADS)

@@ -31,5 +31,3 @@ print("kernel entry / exit (thread 0):", t[190] - t0, t[191] - t0)
 pp = t[160:172]
 print("post_physics CTA 0 thread 0 (entry, loads issued, loads consumed, math done, reward+masks, mask published, obs out):",
       [x - pp[0] for x in pp[:7] if x > 0])
-print("post_physics last CTA (becomes last, ids + count out), relative to CTA 0's entry:",
-      [x - pp[0] for x in pp[10:12] if x > 0])
