@@ -231,9 +231,13 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       trace_mark(mtrace, ti, 64);
       wait_a(0);                               // A3
       trace_mark(mtrace, ti, 64);
+      // D3 = [pi | v]: committed per half, so that the m1 epilogue runs while the value half's MMAs do.  The pi half
+      // goes to bar_d[0] (its next phase, D4, is only issued after every thread has waited for this one), the value half
+      // to bar_d[1] (next phase there: D7b, long after the value head has waited for it).
       mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3, false);
+      umma_commit_if(m.leader, &s.bar_d[0]);   // D3 pi
       mma_segment<H3, H2 / 8, false>(m, tb + C_A3H, tb + C_A3L, tb + C_D3 + H3, false);
-      umma_commit_if(m.leader, &s.bar_d[0]);   // D3
+      umma_commit_if(m.leader, &s.bar_d[1]);   // D3 v
       trace_mark(mtrace, ti, 64);
       wait_a(0);                               // A4
       trace_mark(mtrace, ti, 64);
@@ -360,13 +364,14 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       epi_elu_save(t0 + C_D2 + 64 * h, t0 + C_A3H + 64 * h, t0 + C_A3L + 64 * h, s.bias + B_B2 + 64 * h,
                    img_ptr(h2_t, F_H2, r, 64 * h), 64);
       arrive_a(0);
-      wait_d(0);   // D3
+      wait_d(0);   // D3 pi
       epi_elu_save(t0 + C_D3 + 32 * h, t0 + C_A4H + 32 * h, t0 + C_A4L + 32 * h, s.bias + B_B3PI + 32 * h,
                    img_ptr(mv_t, F_MV, r, 32 * h), 32);
       arrive_a(0);   // -> D4
 
       // ---- value head: v1 = ELU(D3v + b3v) (32 columns per thread), value, dL/dv, dZv1
       float dval;
+      wait_d(1);   // D3 v
       {
         float v1[32];
         float part = 0.0f;
