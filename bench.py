@@ -232,8 +232,12 @@ def run_own(args):
     dev = f"cuda:{local}"
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO") and not os.environ.get("FLYB_KEEP_NCCL_DEBUG"):
-            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL's banner goes to stdout: keep stdout to the ONE JSON line
+        # NCCL writes its banner / debug lines to stdout (the version line even at WARN level): send them to stderr so
+        # that stdout carries the ONE JSON line and nothing else
+        # (NCCL honours NCCL_DEBUG_FILE only above the VERSION level, so VERSION is raised to WARN — same banner)
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device(dev))
     if args.gpus != world and rank == 0 and world > 1:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}", file=sys.stderr)
