@@ -257,7 +257,7 @@ def run_own(args):
     pk = peaks()
     torch.manual_seed(0)
     a = fb.make_args(num_envs=NUM_ENVS, sim_device=dev, horizon=HORIZON, verbose=False, state_pool=POOL,
-                     seed=1234 + rank)
+                     seed=1234)
     agent = fb.PPO(a)
     env = agent.env
     K, W = args.steps, max(3, args.warmup)
@@ -395,7 +395,7 @@ def run_own(args):
             live[k].copy_(hp[k], non_blocking=True)
         step_no[0] += 1
 
-    a2 = fb.make_args(num_envs=NUM_ENVS, sim_device=dev, horizon=HORIZON, verbose=False, testing=True, seed=99 + rank)
+    a2 = fb.make_args(num_envs=NUM_ENVS, sim_device=dev, horizon=HORIZON, verbose=False, testing=True, seed=99)
     src = fb.TensorStateSource(live["root"], live["dof_state"], live["force"], simulate_fn=h2d)
     agent2 = fb.PPO(a2, env=fb.Fly(a2, state_source=src))
     agent2.net.load_state_dict(agent.net.state_dict())

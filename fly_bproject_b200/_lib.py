@@ -40,7 +40,7 @@ MAX_PEERS = 8
 
 class PeerGroup(C.Structure):
     """FlybPeerGroup: the ranks' gradient-exchange buffers as mapped in this process."""
-    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("total_pad", C.c_int32), ("_pad", C.c_int32),
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("total_pad", C.c_int32), ("timeout_ms", C.c_int32),
                 ("base", C.c_void_p * MAX_PEERS)]
 
 
@@ -89,6 +89,7 @@ SIGNATURES = {
     "flyb_peer_close": (C.c_int, [_P]),
     "flyb_peer_free": (C.c_int, [_P]),
     "flyb_peer_stamps": (C.c_int, [C.POINTER(PeerGroup), C.POINTER(C.c_uint64)]),
+    "flyb_peer_status": (C.c_int, [C.POINTER(PeerGroup), C.POINTER(C.c_int32)]),
     "flyb_anneal_var": (C.c_int, [_P, C.c_int32, C.c_float, C.c_float, _P, _P]),
 }
 
@@ -108,7 +109,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)  # AttributeError if the .so does not export it
             fn.restype = restype
             fn.argtypes = argtypes
-        if handle.flyb_abi_version() != 5:
+        if handle.flyb_abi_version() != 6:
             raise FlybError("libflyb200.so ABI version mismatch")
         _lib = handle
     return _lib

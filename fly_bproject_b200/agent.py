@@ -7,7 +7,9 @@ action stored; ``all_done`` = the last step's (N,1) mask; no done mask in the GA
 trained on; the update uses the CURRENT annealed variance; scalar SmoothL1 mean added to every surrogate row).
 
 All tensor math runs in libflyb200.so (csrc/policy_kernels.cu, gae_kernels.cu, ppo_kernels.cu).  PyTorch only owns
-device memory, streams, CUDA graphs and the NCCL gradient all-reduce.
+device memory, streams, CUDA graphs and the process group that carries the IPC handles / the parameter broadcast; the
+data-parallel gradient sum itself is the library's own kernels over NVLink peer memory (dp.PeerExchange; NCCL only as
+`FLYB_DP=nccl` or when peer mapping fails).
 """
 from __future__ import annotations
 
@@ -204,7 +206,8 @@ class PPO:
         self._workspace = torch.zeros(ws_bytes + 256, dtype=torch.uint8, device=dev)
         self._ws_ptr = (self._workspace.data_ptr() + 255) // 256 * 256
 
-        self.seed = int(_get(args, "seed", 0))
+        # data-parallel ranks draw different action noise from identical args (seed + rank)
+        self.seed = dp.rank_seed(int(_get(args, "seed", 0)))
         self._rng_counter = torch.zeros(1, dtype=torch.int64, device=dev)   # Philox draw number, advanced on device
         self._fused_env = isinstance(self.env, Fly)
         testing = bool(_get(args, "testing", False))
@@ -293,6 +296,8 @@ class PPO:
         if self._fused_env:
             self.score = float(self.env.reward_sum.item()) / self.num_envs / self.num_eval_freq
             self.env.reward_sum.zero_()
+        if self._peers is not None:
+            self._peers.check()         # a timed-out exchange sets a sticky word instead of trapping (peer.cuh)
         if self.verbose:
             print('Steps: {:04d} | Opt Step: {:04d} | Reward {:.04f} | Action Var {:.04f}'.format(
                 self.run_step, self.optim_step, self.score, self.action_var[0].item()))
@@ -396,7 +401,7 @@ class PPO:
         self.optim_step += steps
 
     def save(self, endofname: str = "") -> None:
-        if not _get(self.args, "save", False):
+        if not _get(self.args, "save", False) or self.rank != 0:      # ranks hold identical parameters: rank 0 writes
             return
         path = self.args.save_path + endofname + ".pth"
         torch.save(OrderedDict((k, v.cpu()) for k, v in self.net.state_dict().items()), path)   # ppo.py:266-273
@@ -406,6 +411,9 @@ class PPO:
 
     def exit(self) -> None:
         if self._peers is not None:
-            self._peers.close()
-            self._peers = None
+            peers, self._peers = self._peers, None
+            try:
+                peers.check()
+            finally:
+                peers.close()
         self.env.exit()

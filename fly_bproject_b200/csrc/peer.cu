@@ -1,10 +1,21 @@
 // Exchange buffers of the data-parallel gradient sum: allocation and CUDA IPC mapping (include/flyb200.h,
 // FlybPeerGroup).  The kernels that use them are in ppo_kernels*.cu (peer.cuh).
+#include <stdlib.h>
 #include <string.h>
 
 #include "peer.cuh"
 
 namespace flyb {
+
+unsigned long long peer_timeout_ns(const FlybPeerGroup& g) {
+  if (g.timeout_ms > 0) return (unsigned long long)g.timeout_ms * 1000000ull;
+  static const double env_s = [] {
+    const char* e = getenv("FLYB_PEER_TIMEOUT_S");
+    const double v = e ? atof(e) : 0.0;
+    return v > 0.0 ? v : 120.0;
+  }();
+  return (unsigned long long)(env_s * 1e9);
+}
 
 int peer_validate(const FlybPeerGroup* g, int total) {
   FLYB_REQUIRE(g->world >= 1 && g->world <= FLYB_MAX_PEERS, "FlybPeerGroup: world %d out of range", g->world);
@@ -67,4 +78,17 @@ extern "C" int flyb_peer_stamps(const FlybPeerGroup* g, uint64_t* out8) {
   const PeerView v = make_peer_view(*g);
   if ((rc = check_cuda(cudaDeviceSynchronize(), "cudaDeviceSynchronize")) != FLYB_OK) return rc;
   return check_cuda(cudaMemcpy(out8, v.stamp, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost), "cudaMemcpy(stamps)");
+}
+
+extern "C" int flyb_peer_status(const FlybPeerGroup* g, int32_t* status_out) {
+  FLYB_REQUIRE(g && status_out, "flyb_peer_status: NULL argument");
+  int rc = peer_validate(g, 1);
+  if (rc != FLYB_OK) return rc;
+  const PeerView v = make_peer_view(*g);
+  uint32_t word = 0;
+  if ((rc = check_cuda(cudaMemcpy(&word, v.error, sizeof(word), cudaMemcpyDeviceToHost), "cudaMemcpy(peer status)")) !=
+      FLYB_OK)
+    return rc;
+  *status_out = (int32_t)word;
+  return FLYB_OK;
 }

@@ -10,11 +10,14 @@ struct PeerView {   // FlybPeerGroup resolved into typed pointers (kernel argume
   float* slots[FLYB_MAX_PEERS];        // slots[r]: [2][world][total_pad] in rank r's buffer
   uint32_t* flags[FLYB_MAX_PEERS];     // flags[r]: [FLYB_MAX_PEERS] in rank r's buffer
   uint32_t* epoch;                     // own: exchanges completed by this rank
+  uint32_t* error;                     // own: sticky error word (0 = fine, 1 + r = gave up waiting for rank r)
+  unsigned long long timeout_ns;       // how long peer_wait_all spins before it gives up
   unsigned long long* stamp;           // own: 8 x %globaltimer marks of the last exchange (flyb_peer_stamps)
 };
 
 inline size_t peer_slots_bytes(int total_pad, int world) { return (size_t)2 * world * total_pad * sizeof(float); }
-constexpr size_t PEER_CTRL_BYTES = 256;   // flags[8], epoch, (pad), 8 x u64 stamps at byte 64
+constexpr size_t PEER_CTRL_BYTES = 256;   // flags[8], epoch, error, (pad), 8 x u64 stamps at byte 64
+unsigned long long peer_timeout_ns(const FlybPeerGroup& g);   // peer.cu
 
 inline PeerView make_peer_view(const FlybPeerGroup& g) {
   PeerView v{};
@@ -25,6 +28,8 @@ inline PeerView make_peer_view(const FlybPeerGroup& g) {
     v.flags[r] = (uint32_t*)((char*)g.base[r] + sb);
   }
   v.epoch = v.flags[g.rank] + FLYB_MAX_PEERS;
+  v.error = v.epoch + 1;
+  v.timeout_ns = peer_timeout_ns(g);
   v.stamp = (unsigned long long*)(v.flags[g.rank] + 16);
   return v;
 }
@@ -48,35 +53,48 @@ FLYB_D float ld_relaxed_sys(const float* p) {
   return v;
 }
 
-// Entry i of this rank's gradient -> slot [parity][rank] of every rank (own one included).
+// Entry i of this rank's gradient -> slot [parity][rank] of every rank (own one included), followed by a system-scope
+// fence of the WRITING thread: the stores are ordered before anything this thread (and, through the kernel boundary,
+// the flag-raising kernel that follows) does next, whatever the interconnect.  The fence costs nothing measurable: the
+// kernel cannot complete before its remote stores are acknowledged anyway.
 FLYB_D void peer_push(const PeerView& pv, uint32_t parity, int i, float val) {
   const size_t at = ((size_t)parity * pv.world + pv.rank) * pv.total_pad + i;
 #pragma unroll
   for (int r = 0; r < FLYB_MAX_PEERS; ++r)
     if (r < pv.world) pv.slots[r][at] = val;
+  __threadfence_system();
 }
 
 // Raise this rank's flag of epoch `want` on every rank.  Called by ONE CTA of the kernel that FOLLOWS the pushing
-// kernel in the stream: a kernel is complete only when its remote stores have been acknowledged, so the pushing
-// kernel needs no fences or tickets of its own and the flag cannot overtake the data.
+// kernel in the stream: the pushing threads fenced their stores at system scope and the kernel boundary orders them
+// before this release, so the flag cannot overtake the data.
 FLYB_D void peer_raise_flags(const PeerView& pv, uint32_t want) {
   if (threadIdx.x < pv.world) {
     __threadfence_system();
-    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pv.flags[threadIdx.x] + pv.rank), "r"(want) : "memory");
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pv.flags[threadIdx.x] + pv.rank), "r"(want) : "memory");
   }
 }
 
-// Wait until every rank has pushed epoch `want` into this rank's buffer.  One polling lane per source rank; gives
-// up after ~4 s of spinning (a dead peer must not hang the GPU) and traps.
+// Wait until every rank has pushed epoch `want` into this rank's buffer.  One polling lane per source rank.  A peer
+// that does not show up within `timeout_ns` (FlybPeerGroup.timeout_ms / FLYB_PEER_TIMEOUT_S, default 120 s — a rank
+// may be saving, evaluating or loading modules) does NOT kill the context: the lane records a sticky error word in this
+// rank's control block (flyb_peer_status reads it; the host raises and the job restarts with FLYB_DP=nccl), and this and
+// every later wait return at once, so the stream drains instead of hanging.  Results after that are meaningless.
 FLYB_D void peer_wait_all(const PeerView& pv, uint32_t want) {
   if (threadIdx.x < pv.world) {
     const uint32_t* f = pv.flags[pv.rank] + threadIdx.x;
-    const long long t0 = clock64();
+    const unsigned long long t0 = global_ns();
+    unsigned spins = 0;
     while ((int32_t)(ld_acquire_sys(f) - want) < 0) {
       __nanosleep(64);
-      if (clock64() - t0 > 8000000000LL) {
-        printf("flyb200: rank %d gave up waiting for rank %d (epoch %u)\n", pv.rank, (int)threadIdx.x, want);
-        __trap();
+      if ((++spins & 1023u) == 0u) {
+        if (*(volatile uint32_t*)pv.error != 0u) break;
+        if (global_ns() - t0 > pv.timeout_ns) {
+          if (atomicCAS(pv.error, 0u, 1u + threadIdx.x) == 0u)
+            printf("flyb200: rank %d gave up waiting for rank %d (epoch %u); peer exchange disabled\n", pv.rank,
+                   (int)threadIdx.x, want);
+          break;
+        }
       }
     }
   }

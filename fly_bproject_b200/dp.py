@@ -118,6 +118,22 @@ class PeerExchange:
     def byref(self):
         return C.byref(self.group)
 
+    def status(self) -> int:
+        """Sticky error word of this rank's exchange (flyb_peer_status; synchronises): 0 = fine, 1 + r = the norm kernel
+        gave up waiting for rank r."""
+        st = C.c_int32(0)
+        self._lib.check(self._L.flyb_peer_status(self.byref(), C.byref(st)), "flyb_peer_status")
+        return int(st.value)
+
+    def check(self) -> None:
+        """Raise when a wait for a peer timed out (the device did not trap; parameters are meaningless from there on)."""
+        st = self.status() if self._own is not None else 0
+        if st:
+            raise self._lib.FlybError(
+                f"rank {self.rank}: the peer-memory gradient exchange gave up waiting for rank {st - 1} "
+                "(FLYB_PEER_TIMEOUT_S, default 120 s); restart from the last checkpoint, with FLYB_DP=nccl if a rank "
+                "legitimately stalls that long")
+
     def unmap(self) -> None:
         for m in self._opened:
             self._L.flyb_peer_close(m)

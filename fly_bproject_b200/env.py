@@ -16,7 +16,7 @@ import types
 
 import torch
 
-from . import _lib
+from . import _lib, dp
 from .state_source import SyntheticStateSource
 from .tables import make_env_cfg
 
@@ -70,7 +70,7 @@ class Fly:
         self._scratch = torch.zeros(self.lib.flyb_env_scratch_bytes(n), dtype=torch.uint8, device=dev)
 
         self.state = state_source if state_source is not None else SyntheticStateSource(
-            cfg, dev, pool=int(_get(args, "state_pool", 4)), seed=int(_get(args, "seed", 1234)))
+            cfg, dev, pool=int(_get(args, "state_pool", 4)), seed=dp.rank_seed(int(_get(args, "seed", 1234))))
         self.render_count = 0
 
     # ---- reference attribute names for the Isaac Gym views (fly.py:88-100, 395)

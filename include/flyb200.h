@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FLYB_ABI_VERSION 5
+#define FLYB_ABI_VERSION 6
 #define FLYB_MAX_DOF 64      /* asset DOF count D: 18 (nmf_no_limits_limited_Dofs.urdf) or 42 (nmf_no_limits.urdf) */
 #define FLYB_NUM_ABDOMEN 5   /* reference fly.py:299 */
 #define FLYB_NUM_LEGTIPS 6   /* reference fly.py:300 */
@@ -185,7 +185,7 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  * others' buffers with flyb_peer_open and fills a FlybPeerGroup.  With a group,
  *   flyb_ppo_grad  : its last kernel (the fixed-order reduction of the per-CTA partial gradients) stores every
  *                    gradient entry straight into slot [epoch & 1][rank] of EVERY rank's buffer (posted NVLink
- *                    writes; no fences, the kernel boundary completes them);
+ *                    writes, each writing thread ending with a system-scope fence);
  *   flyb_ppo_apply : its first kernel (global norm) raises this rank's flag on every rank, waits for all ranks'
  *                    flags of this epoch, sums the `world` slots in rank order (bit-identical on every rank), writes
  *                    `grad` and goes on as usual; the Adam kernel closes the epoch.
@@ -194,12 +194,13 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  * double-buffered by epoch parity: a rank can be at most one push ahead of the slowest one.  Everything is
  * stream-ordered device code: a whole data-parallel update is CUDA-graph capturable.
  * Layout of a buffer of flyb_peer_bytes(total, world) bytes (zero-filled by flyb_peer_alloc):
- *   float slots[2][world][total_pad]; uint32 flags[FLYB_MAX_PEERS] (one epoch per source rank); uint32 epoch; time stamps. */
+ *   float slots[2][world][total_pad]; uint32 flags[FLYB_MAX_PEERS] (one epoch per source rank); uint32 epoch;
+ *   uint32 error (sticky, see flyb_peer_status); time stamps. */
 #define FLYB_MAX_PEERS 8
 typedef struct FlybPeerGroup {
   int32_t rank, world;                 /* world <= FLYB_MAX_PEERS */
   int32_t total_pad;                   /* slot stride in floats: flyb_peer_total_pad(net->total) */
-  int32_t _pad;
+  int32_t timeout_ms;                  /* how long a rank waits for its peers' pushes; 0 = FLYB_PEER_TIMEOUT_S or 120 s */
   void* base[FLYB_MAX_PEERS];          /* base[r]: rank r's buffer as mapped in THIS process (base[rank]: own) */
 } FlybPeerGroup;
 int32_t flyb_peer_total_pad(int32_t total);
@@ -212,6 +213,11 @@ int flyb_peer_free(void* ptr);                             /* cudaFree of an own
 /* Debug aid (synchronises the device): %globaltimer marks in ns of this rank's LAST exchange:
  * [0] reduce kernel entry, [3] norm kernel entry (flags raised), [4] all ranks' flags seen, [5] norm CTA 0 done. */
 int flyb_peer_stamps(const FlybPeerGroup* group, uint64_t* out8);
+/* Sticky error word of this rank's exchange (synchronises the device): 0 = fine; 1 + r = the norm kernel gave up
+ * waiting for rank r after the timeout.  The wait does not trap (the CUDA context survives): the stream drains, every
+ * later exchange returns at once, results are meaningless from then on and the host must stop — or restart with the
+ * NCCL exchange (FLYB_DP=nccl), which simply waits. */
+int flyb_peer_status(const FlybPeerGroup* group, int32_t* status_out);
 
 /* ---- agent, kernel (d): one optimiser step of reference PPO.update (ppo.py:183-199), split where a
  *      data-parallel run exchanges gradients:  flyb_ppo_grad -> [sum over ranks] -> flyb_ppo_apply.

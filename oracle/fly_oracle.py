@@ -239,8 +239,10 @@ def apply_reset(t: EnvTables, s: EnvState) -> Tensor:
     return env_ids.to(torch.int32)
 
 
-def post_physics(t: EnvTables, s: EnvState, walking: bool = False) -> None:
-    """reference fly.py:676-681 → get_obs (397-411), progress += 1 (678), get_reward (413-443)."""
+def post_physics(t: EnvTables, s: EnvState, walking: bool = False,
+                 energy_cost_scale: float = ENERGY_COST_SCALE) -> None:
+    """reference fly.py:676-681 → get_obs (397-411), progress += 1 (678), get_reward (413-443).
+    ``energy_cost_scale``: 0.005 (fly.py:47) or 1 for the low-gravity variant (flyLowGrav.py:44)."""
     n, d = t.num_envs, t.num_dof
     dof = s.dof_states.view(n, d, 2)
     obs, pot, prev, up, head = observations(
@@ -252,9 +254,37 @@ def post_physics(t: EnvTables, s: EnvState, walking: bool = False) -> None:
     rew, reset = reward_reset(
         s.obs_buf, s.reset_buf, s.progress_buf, s.actions.view(n, -1), s.potentials, s.prev_potentials,
         s.root[:, 3:7], s.force, t.abdomen_ids, t.leg_tip_ids, t.action_idx_one, t.upper, t.lower, t.num_act,
-        UP_WEIGHT, HEADING_WEIGHT, ACTIONS_COST_SCALE, ENERGY_COST_SCALE, JOINTS_AT_LIMIT_COST_SCALE,
+        UP_WEIGHT, HEADING_WEIGHT, ACTIONS_COST_SCALE, energy_cost_scale, JOINTS_AT_LIMIT_COST_SCALE,
         TERMINATION_HEIGHT, TERMINATION_HEIGHT_UP, DEATH_COST, MAX_EPISODE_LENGTH, walking)
     s.reward_buf[:], s.reset_buf[:] = rew, reset
+
+
+ENERGY_COST_SCALE_LOWGRAV = 1.0   # flyLowGrav.py:44
+
+
+def env_step(t: EnvTables, s: EnvState, actions: Tensor, simulate, variant: str = "standard",
+             walking: bool = False) -> Tuple[Tensor, Tensor]:
+    """One ``Fly.step(actions)`` around a caller-supplied physics step ``simulate(s)`` (which refreshes ``s.root``,
+    ``s.dof_states``, ``s.force`` the way gym.simulate + refresh_* do).
+
+    ``variant="standard"``: reference fly.py:624-681 — scale, set targets, ``reset()``, simulate, obs / reward.
+    ``variant="lowgrav"``: reference flyLowGrav.py:617-683 — scale, set targets, simulate, THEN ``reset()``
+    (flyLowGrav.py:657-663), obs / reward with ``energy_cost_scale = 1`` (flyLowGrav.py:44): the reset rows written
+    into the state tensors are what the observation of the same step reads.
+    Returns (dof position targets, int32 reset ids)."""
+    scaled, targets = scale_actions(t, actions)
+    s.actions = scaled
+    if variant == "standard":
+        ids = apply_reset(t, s)
+        simulate(s)
+        post_physics(t, s, walking)
+    elif variant == "lowgrav":
+        simulate(s)
+        ids = apply_reset(t, s)
+        post_physics(t, s, walking, ENERGY_COST_SCALE_LOWGRAV)
+    else:
+        raise ValueError(f"variant {variant!r}")
+    return targets, ids
 
 
 # --------------------------------------------------------------------------- actor-critic net

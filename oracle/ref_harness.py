@@ -1,10 +1,13 @@
 """Import the reference's own ``fly.py`` / ``ppo.py`` unmodified, on CPU torch.
 
-TEST INFRASTRUCTURE (see oracle/__init__.py).  Only usable where the read-only
-reference checkout exists (``/root/reference`` in the build container); it does
-not travel to the GPU box.  It is used to (1) validate the travelling
-restatement in ``oracle/fly_oracle.py`` and (2) generate the golden vectors
-under ``tests/golden/`` (``tests/golden/make_golden.py``).
+TEST INFRASTRUCTURE (see oracle/__init__.py).  Usable where the reference's files
+exist: the read-only checkout ``/root/reference`` in the build container, or the
+byte-for-byte staged copy ``oracle/_ref`` (``oracle/make_ref.py``; git-ignored,
+travels with the gpurun snapshot) on the GPU box.  It is used to (1) validate the
+travelling restatement in ``oracle/fly_oracle.py``
+(``tests/test_oracle_vs_reference.py``), (2) generate the golden vectors under
+``tests/golden/`` (``tests/golden/make_golden.py``) and (3) time the reference's
+unmodified code as the CPU arm of ``bench.py``.
 
 Recipe: put stub modules for ``isaacgym*`` /
 ``isaacgymenvs*`` into ``sys.modules`` whose ``*``-exports are the restated
@@ -23,7 +26,18 @@ import types
 import numpy as np
 import torch
 
-REFERENCE_ROOT = os.environ.get("FLYB200_REFERENCE_ROOT", "/root/reference")
+def _find_root() -> str:
+    env = os.environ.get("FLYB200_REFERENCE_ROOT")
+    if env:
+        return env
+    staged = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+    for cand in ("/root/reference", staged):
+        if os.path.isfile(os.path.join(cand, "fly.py")):
+            return cand
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _find_root()
 
 _STUB_NAMES = [
     "isaacgym", "isaacgym.gymapi", "isaacgym.gymtorch", "isaacgym.torch_utils",
@@ -57,6 +71,7 @@ def _install_stubs() -> None:
 
 _fly = None
 _ppo = None
+_lowgrav = None
 
 
 def load_fly():
@@ -71,6 +86,15 @@ def load_fly():
             sys.path.insert(0, REFERENCE_ROOT)
         _fly = importlib.import_module("fly")
     return _fly
+
+
+def load_fly_lowgrav():
+    """The reference ``flyLowGrav`` module (same two TorchScript functions, low-gravity constants and step order)."""
+    global _lowgrav
+    if _lowgrav is None:
+        load_fly()
+        _lowgrav = importlib.import_module("flyLowGrav")
+    return _lowgrav
 
 
 def load_ppo(env_cls):

@@ -32,15 +32,17 @@ def _worker(rank, world, port, out, mode):
     try:
         torch.manual_seed(100 + rank)          # different initial nets per rank: the broadcast must align them
         args = fb.make_args(num_envs=2048, sim_device=f"cuda:{rank}", horizon=16, verbose=False, state_pool=4,
-                            seed=1234 + rank)
+                            seed=1234)           # IDENTICAL args on every rank: the library decorrelates the shards
         agent = fb.PPO(args)
         assert agent.world_size == world and (agent._peers is not None) == (mode == "peer")
         agent.collect_rollout(use_graph=False)
+        acts_sum, obs_sum = float(agent.all_acts.double().sum()), float(agent._obs_ring.double().sum())
         for _ in range(2):      # peer mode: eager warm-up + capture, then a replay; NCCL mode: eager twice
             agent.update(use_graph=(mode == "peer"))
         torch.cuda.synchronize()
         torch.save({"flat": agent.net.flat.cpu(), "m": agent.exp_avg.cpu(), "v": agent.exp_avg_sq.cpu(),
-                    "steps": agent.optim_step, "loss": float(agent.loss)}, f"{out}.{mode}.{rank}")
+                    "steps": agent.optim_step, "loss": float(agent.loss), "acts_sum": acts_sum, "obs_sum": obs_sum,
+                    "peer_status": agent._peers.status() if agent._peers is not None else 0}, f"{out}.{mode}.{rank}")
         agent.exit()
     finally:
         dist.destroy_process_group()
@@ -61,6 +63,9 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
             for k in ("flat", "m", "v"):
                 assert torch.equal(r[k], rs[0][k]), (mode, k)
             assert r["loss"] != rs[0]["loss"]          # each rank logs its own shard's loss
+            # same args on every rank, different state pool and action noise (dp.rank_seed): no duplicated shards
+            assert r["acts_sum"] != rs[0]["acts_sum"] and r["obs_sum"] != rs[0]["obs_sum"]
+        assert all(r["peer_status"] == 0 for r in rs)
         assert bool(torch.isfinite(rs[0]["flat"]).all())
         res[mode] = rs[0]
     for k in ("flat", "m", "v"):
@@ -69,3 +74,51 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
     # more ranks: NCCL's tree / ring order differs from the rank order, and 150 Adam steps (each ~lr in size whatever
     # the gradient's magnitude) amplify the reassociation noise: only the bulk has to agree
     assert float((res["peer"]["flat"] - res["nccl"]["flat"]).abs().mean()) < 1e-3
+
+
+def _soak_worker(rank, world, port, out, exchanges):
+    import torch.distributed as dist
+    import fly_bproject_b200 as fb
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    os.environ["FLYB_DP"] = "peer"
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{rank}"))
+    try:
+        torch.manual_seed(7)
+        args = fb.make_args(num_envs=1024, sim_device=f"cuda:{rank}", horizon=16, verbose=False, state_pool=2, seed=1)
+        agent = fb.PPO(args)
+        assert agent._peers is not None
+        agent.collect_rollout(use_graph=False)
+        updates = (exchanges + 74) // 75
+        for u in range(updates):          # one captured graph of 75 exchanges, replayed; ranks drift freely in between
+            agent.update(use_graph=True)
+            if u % 16 == rank:            # deliberate skew: one rank at a time stalls its host (and so its stream)
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
+        st = agent._peers.status()
+        torch.save({"flat": agent.net.flat.cpu(), "m": agent.exp_avg.cpu(), "v": agent.exp_avg_sq.cpu(),
+                    "steps": agent.optim_step, "status": st}, f"{out}.soak.{rank}")
+        agent.exit()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_peer_exchange_soak(tmp_path):
+    """>= 10 000 gradient exchanges over peer memory (FLYB_SOAK_EXCHANGES), every rank bit-identical at the end, no
+    exchange timed out (sticky status word 0)."""
+    world = int(os.environ.get("FLYB_TEST_WORLD", "2"))
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} CUDA devices")
+    exchanges = int(os.environ.get("FLYB_SOAK_EXCHANGES", "10000"))
+    out = str(tmp_path / "dp")
+    mp.spawn(_soak_worker, args=(world, _free_port(), out, exchanges), nprocs=world, join=True)
+    rs = [torch.load(f"{out}.soak.{r}") for r in range(world)]
+    assert rs[0]["steps"] >= exchanges
+    for r in rs:
+        assert r["status"] == 0
+        assert r["steps"] == rs[0]["steps"]
+        for k in ("flat", "m", "v"):
+            assert torch.equal(r[k], rs[0][k]), k
+    assert bool(torch.isfinite(rs[0]["flat"]).all())
+    print(f"soak: {rs[0]['steps']} exchanges x {world} ranks, parameters / Adam state bit-identical on every rank")
