@@ -72,6 +72,7 @@ SIGNATURES = {
     "flyb_env_scratch_bytes": (C.c_size_t, [C.c_int32]),
     "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 18 + [C.POINTER(StepTail), _P]),
     "flyb_env_pre_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 10),
+    "flyb_env_reset": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 7),
     "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64, _P,
                                   _P, _P, _P, _P, C.POINTER(EnvCfg)] + [_P] * 9),
     "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, _P]),

@@ -19,7 +19,7 @@ from typing import Optional
 
 import torch
 
-from . import _lib, dp
+from . import _lib, checkpoint, dp
 from .env import Fly, _get
 
 PARAM_NAMES = [
@@ -185,10 +185,14 @@ class PPO:
         self.optim_step = 0
 
         self.net = Net(o, a, dev, tensor_cores=bool(_get(args, "tensor_cores", True)))
+        resume_state = None
         if _get(args, "load", False):
             if self.verbose:
                 print("loaded from: ", str(args.load_path))
-            self.net.load_state_dict(torch.load(args.load_path, map_location="cpu"))   # ppo.py:147-149
+            # ppo.py:147-149; a `.flyb.pt` sidecar next to the file (checkpoint.py) also brings back what the reference
+            # loses on resume, unless args.resume is False
+            sd, resume_state = checkpoint.load_checkpoint(args.load_path, o, a, want_sidecar=bool(_get(args, "resume", True)))
+            self.net.load_state_dict(sd)
 
         action_var = 0.01 if _get(args, "testing", False) else 0.2                    # ppo.py:151-152
         self.action_var = torch.full((a,), action_var, **f32)
@@ -214,6 +218,8 @@ class PPO:
         self._tail = _lib.StepTail(self.action_var.data_ptr(), a, 0.0 if testing else 0.00001, 0.0 if testing else 0.01,
                                    self._rng_counter.data_ptr())
         self._graphs = {}
+        if resume_state is not None:
+            self._restore(resume_state)
 
         # data-parallel: one process per GPU, the only collective is the gradient all-reduce
         self.rank, self.world_size = dp.world()
@@ -248,11 +254,14 @@ class PPO:
                 lay, p(self.net.flat), p(self.net.wpack), p(env.obs_buf), self.num_envs, p(self.action_var), p(noise), self.seed, 0,
                 p(self._rng_counter), p(self.all_acts[i]), p(self.all_log_prob[i]), None,
                 p(self._obs_ring[0]) if i == 0 else None, C.byref(env.cfg), p(env._actions_scaled),
-                p(env.dof_targets), p(env.reset_buf), p(env.progress_buf), p(env.potentials),
-                p(env.prev_potentials), p(st.root), p(st.dof_state), stream), "flyb_policy_act")
+                p(env.dof_targets), None if env.reset_after_simulate else p(env.reset_buf), p(env.progress_buf),
+                p(env.potentials), p(env.prev_potentials), p(st.root), p(st.dof_state), stream), "flyb_policy_act")
             st.set_dof_position_targets(env.dof_targets)
-            st.set_reset_ids(env.reset_ids, env.reset_count)
+            if not env.reset_after_simulate:
+                st.set_reset_ids(env.reset_ids, env.reset_count)
             env.simulate()
+            if env.reset_after_simulate:        # low-gravity step order (flyLowGrav.py:657-663)
+                env.reset_async()
             env.render_count += 1
             # ppo.py:236-237 (variance annealing, skipped in testing mode) and the Philox draw counter ride on the
             # step's last launch
@@ -400,11 +409,31 @@ class PPO:
         graph.replay()
         self.optim_step += steps
 
+    def _restore(self, side: dict) -> None:
+        """Adam moments, annealed variance, counters and the Philox draw number from a checkpoint sidecar."""
+        if side["exp_avg"].numel() != self.exp_avg.numel():
+            raise _lib.FlybError("checkpoint sidecar was written under a different parameter layout")
+        self.exp_avg.copy_(side["exp_avg"])
+        self.exp_avg_sq.copy_(side["exp_avg_sq"])
+        self.adam_step.fill_(int(side["adam_step"]))
+        self.action_var.copy_(side["action_var"])
+        self._rng_counter.fill_(int(side["rng_counter"]))
+        self.optim_step = int(side["optim_step"])
+        self.run_step = int(side["run_step"])
+
     def save(self, endofname: str = "") -> None:
+        """ppo.py:266-273: `save_path + endofname + ".pth"` in the reference's layout (loads in the reference), plus —
+        unless args.save_sidecar is False — `<that>.flyb.pt` with Adam's moments and step, `action_var`, `optim_step`,
+        `run_step` and the Philox draw counter, so that `args.load` resumes the run instead of restarting them."""
         if not _get(self.args, "save", False) or self.rank != 0:      # ranks hold identical parameters: rank 0 writes
             return
         path = self.args.save_path + endofname + ".pth"
-        torch.save(OrderedDict((k, v.cpu()) for k, v in self.net.state_dict().items()), path)   # ppo.py:266-273
+        extras = None
+        if _get(self.args, "save_sidecar", True):
+            extras = {"exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "adam_step": int(self.adam_step.item()),
+                      "action_var": self.action_var, "optim_step": self.optim_step, "run_step": self.run_step,
+                      "rng_counter": int(self._rng_counter.item())}
+        checkpoint.save_checkpoint(path, self.net.state_dict(), extras)
 
     def generate_video(self) -> None:
         self.env.generate_video()

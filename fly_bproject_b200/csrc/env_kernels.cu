@@ -363,15 +363,17 @@ pre_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restri
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int env = (int)(i / D);
     const int d = (int)(i - (size_t)env * D);
-    const int k = s_slot[d];
-    float tgt = cfg.initial_pos[d];                                  // fly.py:626
-    if (k >= 0) {
-      const float a = __ldg(actions + (size_t)env * A + k);
-      tgt = scale_action(a, cfg.lower[d], cfg.upper[d]);             // fly.py:629-630
-      actions_scaled[(size_t)env * A + k] = tgt;                     // fly.py:633-636
+    if (actions != nullptr) {
+      const int k = s_slot[d];
+      float tgt = cfg.initial_pos[d];                                  // fly.py:626
+      if (k >= 0) {
+        const float a = __ldg(actions + (size_t)env * A + k);
+        tgt = scale_action(a, cfg.lower[d], cfg.upper[d]);             // fly.py:629-630
+        actions_scaled[(size_t)env * A + k] = tgt;                     // fly.py:633-636
+      }
+      dof_targets[i] = tgt;                                            // fly.py:648-651
     }
-    dof_targets[i] = tgt;                                            // fly.py:648-651
-    if (reset[env] != 0) {                                           // fly.py:446-480
+    if (reset != nullptr && reset[env] != 0) {                       // fly.py:446-480
       reinterpret_cast<float2*>(dof_state)[i] = make_float2(cfg.initial_pos[d], cfg.initial_vel[d]);
       if (d < 13) root[(size_t)env * 13 + d] = cfg.origin_root[d];
       if (D < 13 && d == 0)
@@ -461,16 +463,34 @@ extern "C" int flyb_env_pre_physics(const FlybEnvCfg* cfg, const float* actions,
                                     float* prev_potentials, float* root, float* dof_state, void* stream) {
   int rc = validate_cfg(cfg);
   if (rc != FLYB_OK) return rc;
-  FLYB_REQUIRE(actions && actions_scaled && dof_targets && reset && progress && potentials && prev_potentials &&
-                   root && dof_state,
-               "flyb_env_pre_physics: NULL buffer");
-  FLYB_REQUIRE((reinterpret_cast<uintptr_t>(dof_state) & 7u) == 0, "dof_state must be 8-byte aligned");
+  FLYB_REQUIRE(actions && actions_scaled && dof_targets, "flyb_env_pre_physics: NULL buffer");
+  FLYB_REQUIRE(!reset || (progress && potentials && prev_potentials && root && dof_state),
+               "flyb_env_pre_physics: the reset half needs progress, potentials, prev_potentials, root and dof_state");
+  FLYB_REQUIRE(!reset || (reinterpret_cast<uintptr_t>(dof_state) & 7u) == 0, "dof_state must be 8-byte aligned");
   const size_t total = (size_t)cfg->num_envs * cfg->num_dof;
   const int grid = (int)((total + 255) / 256);
   pre_physics_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*cfg, actions, actions_scaled, dof_targets,
                                                             (long long*)reset, (long long*)progress, potentials,
                                                             prev_potentials, root, dof_state);
   FLYB_LAUNCH_CHECK("pre_physics_kernel");
+  if (!reset) return FLYB_OK;   // low-gravity step order: Fly.reset() runs after simulate() (flyb_env_reset)
+  pre_physics_finish_kernel<<<(cfg->num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      *cfg, (long long*)reset, (long long*)progress, potentials, prev_potentials);
+  FLYB_LAUNCH_CHECK("pre_physics_finish_kernel");
+  return FLYB_OK;
+}
+
+extern "C" int flyb_env_reset(const FlybEnvCfg* cfg, int64_t* reset, int64_t* progress, float* potentials,
+                              float* prev_potentials, float* root, float* dof_state, void* stream) {
+  int rc = validate_cfg(cfg);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(reset && progress && potentials && prev_potentials && root && dof_state, "flyb_env_reset: NULL buffer");
+  FLYB_REQUIRE((reinterpret_cast<uintptr_t>(dof_state) & 7u) == 0, "dof_state must be 8-byte aligned");
+  const size_t total = (size_t)cfg->num_envs * cfg->num_dof;
+  pre_physics_kernel<<<(int)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      *cfg, nullptr, nullptr, nullptr, (long long*)reset, (long long*)progress, potentials, prev_potentials, root,
+      dof_state);
+  FLYB_LAUNCH_CHECK("pre_physics_kernel(reset)");
   pre_physics_finish_kernel<<<(cfg->num_envs + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
       *cfg, (long long*)reset, (long long*)progress, potentials, prev_potentials);
   FLYB_LAUNCH_CHECK("pre_physics_finish_kernel");

@@ -106,7 +106,7 @@ policy_act_kernel(const __grid_constant__ FlybNetLayout net, const float* __rest
       if (a.has_env) {
         __syncwarp();
         const int D = cfg.num_dof;
-        const bool rst = a.reset[row] != 0;
+        const bool rst = a.reset != nullptr && a.reset[row] != 0;
         for (int d = lane; d < D; d += 32) {
           const int k = s_slot[d];
           a.dof_targets[(size_t)row * D + d] = (k >= 0) ? mu[k] : cfg.initial_pos[d];    // fly.py:626, 648-651
@@ -251,8 +251,9 @@ extern "C" int flyb_policy_act(const FlybNetLayout* net, const float* params, co
                  net->num_act);
     FLYB_REQUIRE(cfg->num_envs == rows, "flyb_policy_act: rows (%lld) != cfg.num_envs (%d)", (long long)rows, cfg->num_envs);
     FLYB_REQUIRE(cfg->num_dof > 0 && cfg->num_dof <= FLYB_MAX_DOF, "num_dof out of range");
-    FLYB_REQUIRE(actions_scaled && dof_targets && reset && progress && potentials && prev_potentials && root && dof_state,
-                 "flyb_policy_act: fused pre-physics needs every env buffer");
+    FLYB_REQUIRE(actions_scaled && dof_targets, "flyb_policy_act: fused pre-physics needs actions_scaled and dof_targets");
+    FLYB_REQUIRE(!reset || (progress && potentials && prev_potentials && root && dof_state),
+                 "flyb_policy_act: the fused reset half needs progress, potentials, prev_potentials, root and dof_state");
     c = *cfg;
     a.has_env = 1;
     a.actions_scaled = actions_scaled; a.dof_targets = dof_targets; a.reset = (long long*)reset;

@@ -250,7 +250,7 @@ struct ActFinal {
     __syncwarp();
   }
   FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {
-    rst_raw = (has_env && r < nrows) ? reset[row0 + r] : 0;
+    rst_raw = (has_env && reset != nullptr && r < nrows) ? reset[row0 + r] : 0;
     if (obs_store) {   // rollout row all_obs[i] = obs (ppo.py:226)
       store_tile(obs_store + (size_t)row0 * O, s.obs, nrows * O);
       if (threadIdx.x == 0) tc::tma_store_commit();

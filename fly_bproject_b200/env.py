@@ -8,6 +8,10 @@ reference's dtypes (``reset_buf`` / ``progress_buf`` int64, ``reset_buf`` initia
 
 ``step`` is two launches around the physics step: ``flyb_env_pre_physics`` (fly.py:626-660) and
 ``flyb_env_post_physics`` (fly.py:676-681).  No host synchronisation happens inside (the reference has three per step).
+
+``args.variant = "lowgrav"`` selects the reference's low-gravity twin (flyLowGrav.py): ``energy_cost_scale = 1``
+(flyLowGrav.py:44) and ``reset()`` moved AFTER ``simulate()`` (flyLowGrav.py:657-663), i.e. scale + targets ->
+simulate -> reset -> obs / reward, so the observation of a step already sees the reset rows.
 """
 from __future__ import annotations
 
@@ -35,8 +39,11 @@ class Fly:
         if self.device.type != "cuda":
             raise _lib.FlybError(f"flyb200.Fly runs on CUDA devices only (sim_device={self.device}); no CPU fallback")
         torch.cuda.set_device(self.device)
+        self.variant = str(_get(args, "variant", "standard"))
+        self.reset_after_simulate = self.variant == "lowgrav"      # flyLowGrav.py:657-663
         self.cfg = make_env_cfg(n, asset=_get(args, "asset", "limited_18"),
-                                full_actions=_get(args, "full_actions", None), walking=bool(_get(args, "walking", False)))
+                                full_actions=_get(args, "full_actions", None), walking=bool(_get(args, "walking", False)),
+                                variant=self.variant)
         cfg = self.cfg
         self.num_envs, self.num_dof, self.num_act, self.num_bodies = n, cfg.num_dof, cfg.num_act, cfg.num_bodies
         self.num_obs = 19 + 3 * self.num_act                    # fly.py:32
@@ -100,18 +107,21 @@ class Fly:
 
     # ---- the two halves of step()
     def pre_physics(self, actions: torch.Tensor) -> None:
-        """fly.py:626-660: scale + scatter to DOF targets, then reset() of the envs whose mask is set."""
+        """fly.py:626-660: scale + scatter to DOF targets, then reset() of the envs whose mask is set (the low-gravity
+        variant leaves the reset to `reset()` after `simulate()`)."""
         if actions.shape != (self.num_envs, self.num_act) or actions.dtype != torch.float32:
             raise _lib.FlybError(f"actions must be float32 ({self.num_envs}, {self.num_act}); got "
                                  f"{actions.dtype} {tuple(actions.shape)}")
         p = _lib.ptr
         st = self.state
         _lib.check(self.lib.flyb_env_pre_physics(
-            C.byref(self.cfg), p(actions), p(self._actions_scaled), p(self.dof_targets), p(self.reset_buf),
+            C.byref(self.cfg), p(actions), p(self._actions_scaled), p(self.dof_targets),
+            None if self.reset_after_simulate else p(self.reset_buf),
             p(self.progress_buf), p(self.potentials), p(self.prev_potentials), p(st.root), p(st.dof_state),
             _lib.current_stream()), "flyb_env_pre_physics")
         st.set_dof_position_targets(self.dof_targets)
-        st.set_reset_ids(self.reset_ids, self.reset_count)
+        if not self.reset_after_simulate:
+            st.set_reset_ids(self.reset_ids, self.reset_count)
 
     def simulate(self) -> None:
         self.state.simulate()
@@ -132,13 +142,28 @@ class Fly:
     def step(self, actions: torch.Tensor) -> None:
         self.pre_physics(actions)
         self.simulate()
+        if self.reset_after_simulate:       # flyLowGrav.py:657-663
+            self.reset_async()
         self.render_count += 1
         self.post_physics()
 
+    def reset_async(self) -> None:
+        """Fly.reset() (fly.py:446-480) without the host round trip: flagged envs get the default DOF state and the
+        origin root row, potentials re-initialised, mask / progress cleared — one stream-ordered call."""
+        p = _lib.ptr
+        st = self.state
+        _lib.check(self.lib.flyb_env_reset(
+            C.byref(self.cfg), p(self.reset_buf), p(self.progress_buf), p(self.potentials), p(self.prev_potentials),
+            p(st.root), p(st.dof_state), _lib.current_stream()), "flyb_env_reset")
+        st.set_reset_ids(self.reset_ids, self.reset_count)
+
     def reset(self) -> bool:
-        """fly.py:446-480 on its own is part of `pre_physics`; kept for API parity (returns whether any env is flagged
-        — this one call does synchronise, like the reference's `len(env_ids)`)."""
-        return bool(int(self.reset_buf.sum().item()) > 0)
+        """fly.py:446-480: resets the flagged envs and returns whether there were any (this call synchronises, like the
+        reference's `len(env_ids)`; `step` never calls it — it uses the fused / asynchronous forms)."""
+        any_flagged = bool(int(self.reset_buf.sum().item()) > 0)
+        if any_flagged:
+            self.reset_async()
+        return any_flagged
 
     def generate_video(self) -> None:
         """Viewer / camera recording (fly.py:350-376, 487-615) needs a graphics stack: unavailable on this box."""
@@ -152,5 +177,7 @@ def make_args(**kw):
     base = dict(sim_device="cuda:0", compute_device_id=0, graphics_device_id=0, num_envs=1000, headless=True,
                 save=False, save_path=None, save_freq=100, load=False, load_path=None, record=False,
                 record_dir_name=None, time_steps_per_recorded_frame=2, testing=False)
+    # beyond trainer.py: variant = "standard" | "lowgrav" (flyLowGrav.py), asset, full_actions, walking, horizon, seed,
+    # state_pool, tensor_cores, verbose — all optional, read with defaults by Fly / PPO
     base.update(kw)
     return types.SimpleNamespace(**base)

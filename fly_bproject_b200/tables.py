@@ -24,6 +24,7 @@ HEADING_WEIGHT = 0.5
 UP_WEIGHT = 0.75
 ACTIONS_COST_SCALE = 0.005
 ENERGY_COST_SCALE = 0.005
+ENERGY_COST_SCALE_LOWGRAV = 1.0        # reference flyLowGrav.py:44
 JOINTS_AT_LIMIT_COST_SCALE = 0.1
 DEATH_COST = -2.0
 TERMINATION_HEIGHT = 1.1
@@ -37,12 +38,17 @@ def load_asset(asset: str = "limited_18") -> dict:
 
 
 def make_env_cfg(num_envs: int, asset: str = "limited_18", full_actions: Optional[bool] = None,
-                 walking: bool = False, action_index: Optional[Sequence[int]] = None) -> EnvCfg:
+                 walking: bool = False, action_index: Optional[Sequence[int]] = None,
+                 variant: str = "standard") -> EnvCfg:
     """Build the FlybEnvCfg for `num_envs` envs of the named asset.
 
     full_actions: actuate every DOF of the asset (A = D) instead of the reference's 18 named joints
     (reference fly.py:23-31).  Defaults to True only when the asset has exactly those 18 DOFs.
+    variant: "standard" (fly.py) or "lowgrav" (flyLowGrav.py: energy_cost_scale = 1, line 44; its gravity, substeps,
+    friction and joint stiffness, lines 36-37, 148-151, 222, configure PhysX, which is not part of this path).
     """
+    if variant not in ("standard", "lowgrav"):
+        raise ValueError(f"variant {variant!r}: expected 'standard' or 'lowgrav'")
     t = load_asset(asset)
     d = t["num_dof"]
     if d > MAX_DOF:
@@ -83,7 +89,7 @@ def make_env_cfg(num_envs: int, asset: str = "limited_18", full_actions: Optiona
     cfg.heading_weight = HEADING_WEIGHT
     cfg.up_weight = UP_WEIGHT
     cfg.actions_cost_scale = ACTIONS_COST_SCALE
-    cfg.energy_cost_scale = ENERGY_COST_SCALE
+    cfg.energy_cost_scale = ENERGY_COST_SCALE_LOWGRAV if variant == "lowgrav" else ENERGY_COST_SCALE
     cfg.joints_at_limit_cost_scale = JOINTS_AT_LIMIT_COST_SCALE
     cfg.death_cost = DEATH_COST
     cfg.termination_height = TERMINATION_HEIGHT

@@ -147,14 +147,25 @@ int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, const float*
 /* ---- env: reference Fly.step up to simulate() (fly.py:626-660): scale policy actions to the joint range,
  *      scatter into the DOF position-target vector, then Fly.reset() (fly.py:446-480) for envs whose mask is set.
  * In:  actions (N,A) in [-1,1].  Out: actions_scaled (N,A), dof_targets (N*D).
- * In/out (reset): reset, progress, potentials, prev_potentials, root (N,13), dof_state (N,D,2). */
+ * In/out (reset): reset, progress, potentials, prev_potentials, root (N,13), dof_state (N,D,2).
+ * reset == NULL: the scaling half only (the other reset-side buffers may then be NULL) — the low-gravity variant
+ * resets AFTER simulate() (reference flyLowGrav.py:657-663): flyb_env_pre_physics(reset = NULL) -> simulate ->
+ * flyb_env_reset -> flyb_env_post_physics. */
 int flyb_env_pre_physics(const FlybEnvCfg* cfg, const float* actions, float* actions_scaled, float* dof_targets,
                          int64_t* reset, int64_t* progress, float* potentials, float* prev_potentials, float* root,
                          float* dof_state, void* stream);
 
+/* ---- env: reference Fly.reset() on its own (fly.py:446-480; flyLowGrav.py:661-663 calls it after simulate()):
+ *      envs whose mask is set get the default DOF state and the origin root row, potentials re-initialised,
+ *      reset / progress cleared.  The compacted ids for the `_indexed` setters are those flyb_env_post_physics left in
+ *      reset_ids / reset_count. */
+int flyb_env_reset(const FlybEnvCfg* cfg, int64_t* reset, int64_t* progress, float* potentials,
+                   float* prev_potentials, float* root, float* dof_state, void* stream);
+
 /* ---- agent, kernel (b): reference PPO.run act block (ppo.py:213-220): mu = Net.pi(obs); a = mu + sqrt(var)*eps;
  *      logp = MVN(mu, diag(var)).log_prob(a); a = clip(a,-1,1) — optionally fused with flyb_env_pre_physics
- *      (pass cfg != NULL and the env buffers) so that one launch covers act + Fly.step's pre-physics half.
+ *      (pass cfg != NULL and the env buffers) so that one launch covers act + Fly.step's pre-physics half
+ *      (reset == NULL with cfg != NULL: scaling + DOF targets only, no Fly.reset — low-gravity step order).
  * noise (rows,A) nullable: explicit eps (parity mode); NULL -> in-kernel Philox4x32-10 keyed by
  *   (seed, offset + *offset_dev); offset_dev (nullable) is a device counter flyb_anneal_var advances once per
  *   step, so that a captured CUDA graph draws fresh noise at every replay.

@@ -64,6 +64,43 @@ def env_case(fly, asset: str, n: int, full_actions: bool, seed: int, prev_reset_
     }
 
 
+def lowgrav_case(mod, asset: str, n: int, full_actions: bool, seed: int, prev_reset_frac: float):
+    """One `Fly.step` of the low-gravity variant (flyLowGrav.py:617-683) on a synthetic post-simulate state: scale
+    actions, [simulate], reset() of the flagged envs (oracle restatement of flyLowGrav.py:446-480 — the method itself
+    needs gymapi), then flyLowGrav.compute_fly_observations / compute_fly_reward2 EXECUTED from the reference with
+    energy_cost_scale = 1 (flyLowGrav.py:44): the observation sees the reset rows."""
+    t = tables_for(asset, n, full_actions)
+    st = fo.synth_state(t, seed)
+    g = torch.Generator().manual_seed(seed + 99)
+    reset_prev = (torch.rand(n, generator=g) < prev_reset_frac).long()
+    potentials = -torch.rand(n, generator=g) * 60000.0
+    s = fo.EnvState(t)
+    s.root, s.dof_states, s.force = st["root"].clone(), st["dof_states"].clone(), st["force"].clone()
+    s.progress_buf, s.reset_buf, s.potentials = st["progress"].clone(), reset_prev.clone(), potentials.clone()
+    s.prev_potentials = potentials.clone()
+    scaled, targets = fo.scale_actions(t, st["actions"])
+    ids = fo.apply_reset(t, s)                                              # after simulate (flyLowGrav.py:661-663)
+    dof = s.dof_states.view(n, t.num_dof, 2)
+    a, o = t.num_act, t.num_obs
+    obs, pot, prev, up, head = mod.compute_fly_observations(
+        torch.zeros(n, o), s.root, t.targets, s.potentials.clone(), t.inv_start_rot, dof[..., 0], dof[..., 1],
+        t.lower, t.upper, 0.2, scaled.view(n, -1), 1 / 60, t.basis0, t.basis1, 2, t.action_idx_one, s.force,
+        t.leg_tip_ids, n)
+    progress = s.progress_buf.clone() + 1
+    progress[progress == 0] = 1
+    rew, reset = mod.compute_fly_reward2(
+        obs, s.reset_buf.clone(), progress, scaled.view(n, -1), 0.75, 0.5, pot, prev, 0.005, 1, 0.1, 1.1, 6, -2.0,
+        1500, t.action_idx_one, t.upper, t.lower, n, s.root[:, 3:7], a, s.force, t.abdomen_ids, t.leg_tip_ids)
+    return {
+        "root": st["root"], "dof_states": st["dof_states"], "force": st["force"], "progress_in": st["progress"],
+        "reset_in": reset_prev, "potentials_in": potentials, "actions_in": st["actions"],
+        "actions_scaled": scaled.view(n, a), "dof_targets": targets, "reset_ids": ids,
+        "root_after": s.root, "dof_states_after": s.dof_states,
+        "obs": obs, "potentials": pot, "prev_potentials": prev, "up_vec": up, "heading_vec": head,
+        "progress": progress, "reward": rew, "reset": reset,
+    }
+
+
 def save(name, d):
     arrs = {k: (v.detach().numpy() if isinstance(v, torch.Tensor) else np.asarray(v)) for k, v in d.items()}
     path = os.path.join(HERE, name)
@@ -179,6 +216,11 @@ def main():
     assert ref_harness.available(), "reference checkout missing"
     torch.manual_seed(0)
     fly = ref_harness.load_fly()
+    if "--lowgrav-only" in sys.argv:        # later addition: leaves the round-1 fixtures byte-identical
+        save("env_lowgrav_d18_a18_n193.npz",
+             lowgrav_case(ref_harness.load_fly_lowgrav(), "limited_18", 193, True, 2024, 0.25))
+        return
+    save("env_lowgrav_d18_a18_n193.npz", lowgrav_case(ref_harness.load_fly_lowgrav(), "limited_18", 193, True, 2024, 0.25))
     save("env_d18_a18_n257.npz", env_case(fly, "limited_18", 257, True, 1234, 0.2))
     save("env_d42_a18_n131.npz", env_case(fly, "full_42", 131, False, 4321, 0.1))
     save("env_d42_a42_n131.npz", env_case(fly, "full_42", 131, True, 999, 0.0))

@@ -294,8 +294,62 @@ def test_full_update_matches_reference_golden_75_steps():
     assert agent.optim_step == 75 and int(agent.adam_step.item()) == 75
     sd = agent.net.state_dict()
     for k in fo.PARAM_ORDER:
-        torch.testing.assert_close(sd[k].cpu(), g["w3/" + k] if False else g["w75/" + k], rtol=2e-3, atol=2e-4,
-                                   msg="param " + k)
+        torch.testing.assert_close(sd[k].cpu(), g["w75/" + k], rtol=2e-3, atol=2e-4, msg="param " + k)
+
+
+def test_three_minibatch_steps_match_reference_golden():
+    """Optimiser steps 1-3 of the reference update (minibatches [0:mc], [mc:2mc], [2mc:3mc] of the golden rollout,
+    ppo.py:178-202) through flyb_ppo_step, against the frozen w3 / m3 / v3 at 1e-4.  Same carve-out as the one-step
+    test: Adam moves a parameter by ~lr * sign(g) while |g| >> eps, so elements whose gradient sat inside the rounding
+    band (1e-4 of the tensor's largest gradient) in ANY of the three steps may land up to 3 * lr away; they are counted
+    and bounded, every other element is held to 1e-4."""
+    g = load_golden("ppo_n64_t32.npz")
+    n, t_roll, mc = [int(x) for x in g["meta"]]
+    net = golden_net(g)
+    lib, p = _lib.lib(), _lib.ptr
+    cfg = _lib.PpoCfg(0.2, 1e-3, 0.9, 0.999, 1e-8, 1.0)
+    rows = mc * n
+    ws = torch.zeros(lib.flyb_ppo_workspace_bytes(C.byref(net.layout), rows) + 256, dtype=torch.uint8, device=DEV)
+    wsp = (ws.data_ptr() + 255) // 256 * 256
+    grad, loss = torch.zeros_like(net.flat), torch.zeros(1, device=DEV)
+    m, v = torch.zeros_like(net.flat), torch.zeros_like(net.flat)
+    step, gn = torch.zeros(1, dtype=torch.int64, device=DEV), torch.zeros(1, device=DEV)
+    var = g["roll_var"].to(DEV)
+    # oracle on the same three minibatches: the well-conditioned mask of every step, and a cross-check of w3 itself
+    p_or = {k: g["w0/" + k].clone() for k in fo.PARAM_ORDER}
+    st_or = fo.AdamState(p_or)
+    well = {k: torch.ones_like(p_or[k], dtype=torch.bool) for k in fo.PARAM_ORDER}
+    keep = []
+    for i in range(3):
+        k0, k1 = i * mc, (i + 1) * mc
+        dv = [x.contiguous().to(DEV) for x in (g["roll_obs"][k0:k1], g["roll_acts"][k0:k1], g["roll_logp"][k0:k1],
+                                               g["roll_target"][k0:k1], g["roll_adv"][k0:k1])]
+        keep.append(dv)
+        _lib.check(lib.flyb_ppo_step(C.byref(net.layout), C.byref(cfg), p(net.flat), p(net.wpack), p(dv[0]), p(dv[1]),
+                                     p(dv[2]), p(dv[3]), p(dv[4]), p(var), rows, p(grad), p(loss), p(m), p(v), p(step),
+                                     p(gn), wsp, _lib.current_stream()))
+        _, _, grads = fo.minibatch_step(p_or, st_or, g["roll_obs"][k0:k1], g["roll_acts"][k0:k1], g["roll_logp"][k0:k1],
+                                        g["roll_target"][k0:k1], g["roll_adv"][k0:k1], g["roll_var"])
+        for k in fo.PARAM_ORDER:
+            well[k] &= grads[k].abs() > RTOL_PPO * float(grads[k].abs().max())
+    torch.cuda.synchronize()
+    assert int(step.item()) == 3
+    sd, mv, vv = net.state_dict(), net.make_views(m), net.make_views(v)
+    ill = 0
+    for k in fo.PARAM_ORDER:
+        torch.testing.assert_close(p_or[k], g["w3/" + k], rtol=1e-5, atol=1e-6, msg="oracle w3 " + k)
+        got, want = sd[k].cpu(), g["w3/" + k]
+        err = (got - want).abs()
+        tol = 1e-6 + RTOL_PPO * want.abs()
+        bad = (err > tol) & well[k]
+        assert not bad.any(), f"param {k}: {int(bad.sum())} well-conditioned elements off, worst {float(err[well[k]].max()):.3e}"
+        assert float(err.max()) <= 3.0 * 2.0 * 1e-3 + 1e-6, "param " + k
+        ill += int(((err > tol) & ~well[k]).sum())
+        torch.testing.assert_close(mv[k].cpu(), g["m3/" + k], rtol=RTOL_PPO,
+                                   atol=RTOL_PPO * float(g["m3/" + k].abs().max()), msg="exp_avg " + k)
+        torch.testing.assert_close(vv[k].cpu(), g["v3/" + k], rtol=2 * RTOL_PPO,
+                                   atol=2 * RTOL_PPO * float(g["v3/" + k].abs().max()), msg="exp_avg_sq " + k)
+    assert ill <= 0.01 * 69587, f"{ill} near-zero-gradient elements moved differently"
 
 
 @pytest.mark.parametrize("o,a,rows", [(145, 42, 1000), (73, 18, 32768), (73, 18, 100)])

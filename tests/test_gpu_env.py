@@ -165,3 +165,58 @@ def test_step_tail_rides_on_post_physics():
         assert int(counter.item()) == 5
         torch.testing.assert_close(var.cpu(), want, rtol=0, atol=0)
         assert float(var[3]) == pytest.approx(0.01)
+
+
+def test_lowgrav_variant_matches_reference_golden():
+    """args.variant = "lowgrav": Fly.step = scale -> simulate -> reset -> obs / reward (flyLowGrav.py:617-683) with
+    energy_cost_scale = 1 (flyLowGrav.py:44), against outputs of the executed flyLowGrav.compute_fly_* functions."""
+    g = load_golden("env_lowgrav_d18_a18_n193.npz")
+    n = 193
+    src = fb.TensorStateSource(g["root"].to(DEV).contiguous(), g["dof_states"].to(DEV).contiguous(),
+                               g["force"].to(DEV).contiguous())
+    env = fb.Fly(fb.make_args(num_envs=n, sim_device=DEV, variant="lowgrav"), state_source=src)
+    assert env.cfg.energy_cost_scale == 1.0 and env.reset_after_simulate
+    env.reset_buf.copy_(g["reset_in"])
+    env.progress_buf.copy_(g["progress_in"])
+    env.potentials.copy_(g["potentials_in"])
+    env.prev_potentials.copy_(g["potentials_in"])
+    env.step(g["actions_in"].to(DEV))
+    torch.cuda.synchronize()
+    torch.testing.assert_close(env.dof_targets.cpu(), g["dof_targets"], rtol=1e-6, atol=1e-6)
+    assert torch.equal(env.state.root.cpu(), g["root_after"])
+    torch.testing.assert_close(env.state.dof_state.cpu(), g["dof_states_after"], rtol=1e-6, atol=1e-7)
+    assert torch.equal(env.reset_buf.cpu(), g["reset"])
+    assert torch.equal(env.progress_buf.cpu(), g["progress"])
+    assert_obs_close(env.obs_buf.cpu(), g["obs"], env.num_act)
+    torch.testing.assert_close(env.reward_buf.cpu(), g["reward"], rtol=RTOL_ENV, atol=ATOL_ENV)
+    torch.testing.assert_close(env.potentials.cpu(), g["potentials"], rtol=1e-6, atol=0)
+    torch.testing.assert_close(env.prev_potentials.cpu(), g["prev_potentials"], rtol=1e-6, atol=0)
+    want_ids = g["reset"].nonzero().squeeze(-1).to(torch.int32)
+    cnt = int(env.reset_count.item())
+    assert cnt == want_ids.numel() and torch.equal(env.reset_ids[:cnt].cpu(), want_ids)
+
+
+def test_reset_method_resets_flagged_envs():
+    """Fly.reset() (fly.py:446-480) performs the reset and reports whether any env was flagged."""
+    n = 500
+    t = oracle_tables("limited_18", n, True)
+    st = fo.synth_state(t, seed=77)
+    env = make_env(n, "limited_18", True, st["root"], st["dof_states"], st["force"])
+    s = fo.EnvState(t)
+    s.root, s.dof_states = st["root"].clone(), st["dof_states"].clone()
+    g = torch.Generator().manual_seed(9)
+    s.reset_buf = (torch.rand(n, generator=g) < 0.3).long()
+    s.progress_buf = st["progress"].clone()
+    s.potentials = -torch.rand(n, generator=g) * 1000.0
+    s.prev_potentials = s.potentials.clone()
+    env.reset_buf.copy_(s.reset_buf); env.progress_buf.copy_(s.progress_buf)
+    env.potentials.copy_(s.potentials); env.prev_potentials.copy_(s.prev_potentials)
+    fo.apply_reset(t, s)
+    assert env.reset() is True
+    torch.cuda.synchronize()
+    assert int(env.reset_buf.sum()) == 0 and env.reset() is False
+    assert torch.equal(env.progress_buf.cpu(), s.progress_buf)
+    assert torch.equal(env.state.root.cpu(), s.root)
+    torch.testing.assert_close(env.state.dof_state.cpu(), s.dof_states, rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(env.potentials.cpu(), s.potentials, rtol=1e-6, atol=0)
+    torch.testing.assert_close(env.prev_potentials.cpu(), s.prev_potentials, rtol=1e-6, atol=0)

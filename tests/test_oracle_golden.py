@@ -74,6 +74,22 @@ def test_update_matches_reference_golden():
         torch.testing.assert_close(st.v[k], g["v1/" + k], rtol=1e-4, atol=1e-12, msg="exp_avg_sq " + k)
 
 
+def test_three_steps_match_reference_golden():
+    """w3 / m3 / v3: the reference's parameters and Adam moments after optimiser steps 1-3 (ppo.py:178-202)."""
+    g = load_golden("ppo_n64_t32.npz")
+    n, t_roll, mc = [int(x) for x in g["meta"]]
+    p = _params(g)
+    st = fo.AdamState(p)
+    for i in range(3):
+        k0, k1 = i * mc, (i + 1) * mc
+        fo.minibatch_step(p, st, g["roll_obs"][k0:k1], g["roll_acts"][k0:k1], g["roll_logp"][k0:k1],
+                          g["roll_target"][k0:k1], g["roll_adv"][k0:k1], g["roll_var"])
+    for k in fo.PARAM_ORDER:
+        torch.testing.assert_close(p[k], g["w3/" + k], rtol=1e-5, atol=1e-6, msg="param " + k)
+        torch.testing.assert_close(st.m[k], g["m3/" + k], rtol=1e-4, atol=1e-8, msg="exp_avg " + k)
+        torch.testing.assert_close(st.v[k], g["v3/" + k], rtol=1e-4, atol=1e-12, msg="exp_avg_sq " + k)
+
+
 def test_full_update_75_steps_matches_reference_golden():
     g = load_golden("ppo_n64_t32.npz")
     n, t_roll, mc = [int(x) for x in g["meta"]]
@@ -84,3 +100,37 @@ def test_full_update_75_steps_matches_reference_golden():
     assert len(losses) == 75 and st.step == 75           # log.txt:49: 5 epochs x 15 minibatches
     for k in fo.PARAM_ORDER:
         torch.testing.assert_close(p[k], g["w75/" + k], rtol=2e-3, atol=2e-4, msg="param " + k)
+
+
+def test_lowgrav_step_matches_reference_golden():
+    """Low-gravity variant: reset AFTER simulate (flyLowGrav.py:657-663), energy_cost_scale = 1 (flyLowGrav.py:44);
+    the fixture's obs / reward are outputs of flyLowGrav.compute_fly_* executed from the reference."""
+    g = load_golden("env_lowgrav_d18_a18_n193.npz")
+    n = 193
+    t = oracle_tables("limited_18", n, True)
+    s = fo.EnvState(t)
+    s.progress_buf, s.reset_buf = g["progress_in"].clone(), g["reset_in"].clone()
+    s.potentials, s.prev_potentials = g["potentials_in"].clone(), g["potentials_in"].clone()
+
+    def simulate(state):
+        state.root, state.dof_states, state.force = g["root"].clone(), g["dof_states"].clone(), g["force"].clone()
+
+    targets, ids = fo.env_step(t, s, g["actions_in"], simulate, variant="lowgrav")
+    assert torch.equal(targets, g["dof_targets"]) and torch.equal(ids, g["reset_ids"])
+    assert torch.equal(s.root, g["root_after"]) and torch.equal(s.dof_states, g["dof_states_after"])
+    for key, got in [("obs", s.obs_buf), ("potentials", s.potentials), ("prev_potentials", s.prev_potentials),
+                     ("reward", s.reward_buf), ("up_vec", s.up_vec), ("heading_vec", s.heading_vec)]:
+        torch.testing.assert_close(got, g[key], rtol=1e-6, atol=1e-6, msg=key)
+    assert torch.equal(s.reset_buf, g["reset"]) and torch.equal(s.progress_buf, g["progress"])
+    # the envs reset inside this step start their episode here: progress 1, origin height 2.0 in the observation
+    flagged = g["reset_in"].bool()
+    assert int(flagged.sum()) > 10
+    assert torch.equal(g["progress"][flagged], torch.ones_like(g["progress"][flagged]))
+    assert torch.equal(g["obs"][flagged, 0], torch.full((int(flagged.sum()),), 2.0))
+    # standard order on the same inputs differs exactly on those envs (reset before simulate: the obs sees the raw state)
+    s2 = fo.EnvState(t)
+    s2.progress_buf, s2.reset_buf = g["progress_in"].clone(), g["reset_in"].clone()
+    s2.potentials, s2.prev_potentials = g["potentials_in"].clone(), g["potentials_in"].clone()
+    fo.env_step(t, s2, g["actions_in"], simulate, variant="standard")
+    assert torch.equal(s2.obs_buf[~flagged], s.obs_buf[~flagged])
+    assert not torch.equal(s2.obs_buf[flagged], s.obs_buf[flagged])
