@@ -214,6 +214,7 @@ class PPO:
         self.seed = dp.rank_seed(int(_get(args, "seed", 0)))
         self._rng_counter = torch.zeros(1, dtype=torch.int64, device=dev)   # Philox draw number, advanced on device
         self._fused_env = isinstance(self.env, Fly)
+        self._foreign_reward_sum = torch.zeros((), **f32)
         testing = bool(_get(args, "testing", False))
         self._tail = _lib.StepTail(self.action_var.data_ptr(), a, 0.0 if testing else 0.00001, 0.0 if testing else 0.01,
                                    self._rng_counter.data_ptr())
@@ -276,6 +277,7 @@ class PPO:
             env.step(self.all_acts[i])
             self._obs_ring[i + 1].copy_(env.obs_buf)
             self.all_reward[i].copy_(env.reward_buf.unsqueeze(-1))
+            self._foreign_reward_sum += env.reward_buf.sum()           # ppo.py:233, without its per-step .item()
         testing = bool(_get(self.args, "testing", False))
         # ppo.py:236-237 (skipped in testing mode); the same launch advances the Philox draw counter
         _lib.check(self.lib.flyb_anneal_var(p(self.action_var), self.num_acts, 0.0 if testing else 0.00001,
@@ -305,6 +307,9 @@ class PPO:
         if self._fused_env:
             self.score = float(self.env.reward_sum.item()) / self.num_envs / self.num_eval_freq
             self.env.reward_sum.zero_()
+        else:
+            self.score = float(self._foreign_reward_sum.item()) / self.num_envs / self.num_eval_freq
+            self._foreign_reward_sum.zero_()
         if self._peers is not None:
             self._peers.check()         # a timed-out exchange sets a sticky word instead of trapping (peer.cuh)
         if self.verbose:

@@ -283,7 +283,10 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     const int n = nenv * O;
     const int n4 = n >> 2;
     float4* dst4 = reinterpret_cast<float4*>(obs + (size_t)env0 * O);
-    float4* cpy4 = obs_copy ? reinterpret_cast<float4*>(obs_copy + (size_t)env0 * O) : nullptr;
+    // the rollout ring row (obs_copy) starts at (i + 1) * N * O floats: 16-byte aligned only when N * O is a multiple
+    // of 4 (N = 1001, O = 73 is not) -> that copy then leaves as scalar stores
+    const bool cpy_vec = obs_copy != nullptr && (reinterpret_cast<uintptr_t>(obs_copy) & 15u) == 0;
+    float4* cpy4 = cpy_vec ? reinterpret_cast<float4*>(obs_copy + (size_t)env0 * O) : nullptr;
     for (int i = tid; i < n4; i += PP_THREADS) {
       const float4 v = reinterpret_cast<const float4*>(obs_s)[i];
       dst4[i] = v;
@@ -291,8 +294,10 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     }
     for (int i = (n4 << 2) + tid; i < n; i += PP_THREADS) {
       obs[(size_t)env0 * O + i] = obs_s[i];
-      if (obs_copy) obs_copy[(size_t)env0 * O + i] = obs_s[i];
+      if (cpy_vec) obs_copy[(size_t)env0 * O + i] = obs_s[i];
     }
+    if (obs_copy != nullptr && !cpy_vec)
+      for (int i = tid; i < n; i += PP_THREADS) obs_copy[(size_t)env0 * O + i] = obs_s[i];
   }
 
   mark();
@@ -438,7 +443,7 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
   FLYB_REQUIRE(root && dof_state && force && actions_scaled && potentials && prev_potentials && progress && reset &&
                    obs && reward && up_vec && heading_vec && reset_ids && reset_count && scratch,
                "flyb_env_post_physics: NULL buffer");
-  FLYB_REQUIRE(aligned16(root) && aligned16(obs) && aligned16(dof_state) && (!obs_copy || aligned16(obs_copy)),
+  FLYB_REQUIRE(aligned16(root) && aligned16(obs) && aligned16(dof_state),
                "flyb_env_post_physics: root/dof_state/obs must be 16-byte aligned");
   const int O = 19 + 3 * cfg->num_act;
   const size_t smem = (size_t)ENVS * (O + 13 + FORCE_VALS) * sizeof(float);

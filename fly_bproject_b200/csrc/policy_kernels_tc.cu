@@ -297,6 +297,8 @@ struct ActFinal {
     const int n = nrows * A;
     const size_t g0 = (size_t)row0 * A;
     const int kstep = (2 * tcm::EPI_THREADS) % A;
+    // float2 stores need 8-byte aligned rows: all_acts[i] starts at i * N * A floats (odd for odd N and odd A)
+    const bool pair_ok = ((reinterpret_cast<uintptr_t>(action) | (has_env ? reinterpret_cast<uintptr_t>(actions_scaled) : 0)) & 7u) == 0;
     int e = 2 * threadIdx.x;
     int k = e % A;
     for (; e < n; e += 2 * tcm::EPI_THREADS) {
@@ -317,7 +319,11 @@ struct ActFinal {
           if (mu_out) mu_out[g0 + ee] = mu_k;
         }
       }
-      if (e + 1 < n) {
+      if (e + 1 < n && !pair_ok) {
+        action[g0 + e] = cl[0];
+        action[g0 + e + 1] = cl[1];
+        if (has_env) { actions_scaled[g0 + e] = sc[0]; actions_scaled[g0 + e + 1] = sc[1]; }
+      } else if (e + 1 < n) {
         *reinterpret_cast<float2*>(action + g0 + e) = make_float2(cl[0], cl[1]);
         if (has_env) *reinterpret_cast<float2*>(actions_scaled + g0 + e) = make_float2(sc[0], sc[1]);   // fly.py:633-636
       } else {

@@ -8,7 +8,10 @@ source synthesises those tensors at the named shapes: ``root (N,13)``, ``dof_sta
 
 `SyntheticStateSource` holds a POOL of pre-generated states and `simulate()` rotates through it (a pointer swap, no
 copy), so that consecutive steps read different HBM lines; with pool bytes > L2 (126 MB) every step streams its
-state from HBM.  Writes the env makes into the live state (reset rows, fly.py:454-459) land in the pool entry.
+state from HBM.  Writes the env makes into the live state (reset rows, fly.py:454-459) land in the pool entry; a real
+physics step would overwrite them, so every time the rotation wraps around the root / DOF slabs of all entries are
+restored from a pristine copy (two flat device copies per `pool` steps) — otherwise every row that ever triggered a
+reset would stay healed and the termination mix would drift from ~50 % of the envs to the abdomen hits and time-outs.
 """
 from __future__ import annotations
 
@@ -70,10 +73,19 @@ def synth_state(cfg, seed: int, device, progress: bool = False):
 class SyntheticStateSource:
     """Pool of synthetic Isaac Gym states; `simulate()` advances to the next pool entry."""
 
-    def __init__(self, cfg, device, pool: int = 4, seed: int = 1234):
+    def __init__(self, cfg, device, pool: int = 4, seed: int = 1234, restore: bool = True):
         self.cfg = cfg
         self.device = torch.device(device)
-        self.pool: List[dict] = [synth_state(cfg, seed + 7919 * i, self.device) for i in range(max(1, pool))]
+        npool = max(1, pool)
+        states = [synth_state(cfg, seed + 7919 * i, self.device) for i in range(npool)]
+        # root / dof_state of all entries live in ONE slab each (entries are views), so that the restore is two copies
+        self._root_all = torch.stack([s["root"] for s in states]).contiguous()
+        self._dof_all = torch.stack([s["dof_state"] for s in states]).contiguous()
+        self.pool: List[dict] = [{"root": self._root_all[i], "dof_state": self._dof_all[i], "force": states[i]["force"]}
+                                 for i in range(npool)]
+        self.restore = bool(restore)
+        self._root_pristine = self._root_all.clone() if self.restore else None
+        self._dof_pristine = self._dof_all.clone() if self.restore else None
         self.index = 0
 
     @property
@@ -101,6 +113,9 @@ class SyntheticStateSource:
     def simulate(self) -> None:
         """gym.simulate + fetch_results + refresh_* (fly.py:482-485, 401-403)."""
         self.index = (self.index + 1) % len(self.pool)
+        if self.index == 0 and self.restore:      # the "physics" overwrites what Fly.reset wrote into the state
+            self._root_all.copy_(self._root_pristine)
+            self._dof_all.copy_(self._dof_pristine)
 
 
 class TensorStateSource:

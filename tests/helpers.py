@@ -58,3 +58,26 @@ def assert_obs_close(got: torch.Tensor, want: torch.Tensor, num_act: int, rtol=R
     assert not bad.any(), (f"{int(bad.sum())} obs entries out of tolerance; worst abs diff {float(diff.max()):.3e} "
                            f"at {np.unravel_index(int(diff.argmax()), diff.shape)}")
     return seam_hits
+
+
+class OraclePool:
+    """CPU mirror of `SyntheticStateSource`: the same pool entries, the same rotation and the same restore of the
+    root / DOF slabs whenever the rotation wraps around (what a real physics step overwriting the reset rows does)."""
+
+    def __init__(self, source):
+        self.entries = [{k: v.cpu().clone() for k, v in e.items()} for e in source.pool]
+        self.pristine = [{k: e[k].clone() for k in ("root", "dof_state")} for e in self.entries]
+        self.restore = bool(getattr(source, "restore", False))
+        self.index = 0
+
+    def bind(self, s):
+        e = self.entries[self.index]
+        s.root, s.dof_states, s.force = e["root"], e["dof_state"], e["force"]
+
+    def simulate(self, s):
+        self.index = (self.index + 1) % len(self.entries)
+        if self.index == 0 and self.restore:
+            for e, p0 in zip(self.entries, self.pristine):
+                e["root"].copy_(p0["root"])
+                e["dof_state"].copy_(p0["dof_state"])
+        self.bind(s)

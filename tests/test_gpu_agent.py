@@ -10,7 +10,7 @@ import torch
 import fly_bproject_b200 as fb
 from fly_bproject_b200 import _lib
 from oracle import fly_oracle as fo
-from tests.helpers import RTOL_PPO, load_golden, oracle_tables
+from tests.helpers import RTOL_PPO, OraclePool, load_golden, oracle_tables
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -390,10 +390,9 @@ def test_run_loop_matches_oracle_rollout_and_update():
     p0 = {k: v.cpu() for k, v in agent.net.state_dict().items()}
     # oracle env on the same synthetic pool
     s = fo.EnvState(t)
-    pool = [{k: v.cpu().clone() for k, v in e.items()} for e in env.state.pool]
+    pool = OraclePool(env.state)
     var = torch.full((18,), 0.2)
-    idx = 0
-    s.root, s.dof_states, s.force = pool[0]["root"], pool[0]["dof_state"], pool[0]["force"]
+    pool.bind(s)
     gen = torch.Generator().manual_seed(0)
     for i in range(3):
         noise = torch.randn(n, 18, generator=gen)
@@ -402,8 +401,7 @@ def test_run_loop_matches_oracle_rollout_and_update():
         scaled, targets = fo.scale_actions(t, a)
         s.actions = scaled
         fo.apply_reset(t, s)
-        idx = (idx + 1) % 2
-        s.root, s.dof_states, s.force = pool[idx]["root"], pool[idx]["dof_state"], pool[idx]["force"]
+        pool.simulate(s)
         fo.post_physics(t, s)
         var = fo.anneal_var(var)
         agent.run(noise=noise.to(DEV))
@@ -490,3 +488,38 @@ def test_ppo_step_is_grad_plus_apply_and_keeps_the_weight_stream_in_step():
         torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-7, msg=name)
     assert a[4] == pytest.approx(b[4], rel=1e-4)
     assert a[5] == pytest.approx(b[5], rel=1e-4)
+
+
+@pytest.mark.parametrize("n", [1001, 301])
+def test_env_counts_that_misalign_the_rollout_rows(n):
+    """N * O not a multiple of 4 (N = 1001 or 301, O = 73): the rollout-ring rows obs_copy / all_acts[i] are then only
+    4- or 8-byte aligned.  The reference accepts any N; the kernels must fall back to narrower stores."""
+    t = oracle_tables("limited_18", n, True)
+    args = fb.make_args(num_envs=n, sim_device=DEV, horizon=16, verbose=False, state_pool=2, seed=n, tensor_cores=TC)
+    agent = fb.PPO(args)
+    env = agent.env
+    p0 = {k: v.cpu() for k, v in agent.net.state_dict().items()}
+    s = fo.EnvState(t)
+    pool = OraclePool(env.state)
+    pool.bind(s)
+    var = torch.full((18,), 0.2)
+    gen = torch.Generator().manual_seed(n)
+    for i in range(5):
+        noise = torch.randn(n, 18, generator=gen)
+        a, logp, _ = fo.act(p0, s.obs_buf.clone(), var, noise)
+        s.actions, _ = fo.scale_actions(t, a)
+        fo.apply_reset(t, s)
+        pool.simulate(s)
+        fo.post_physics(t, s)
+        var = fo.anneal_var(var)
+        agent.run(noise=noise.to(DEV))
+        torch.cuda.synchronize()
+        assert torch.equal(env.reset_buf.cpu(), s.reset_buf)
+        assert torch.equal(agent._obs_ring[i + 1], env.obs_buf)            # the (possibly misaligned) ring copy
+        torch.testing.assert_close(agent.all_acts[i].cpu(), a, rtol=1e-5, atol=2e-6)
+        torch.testing.assert_close(env._actions_scaled.cpu(), s.actions.view(n, -1), rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(agent.all_reward[i].squeeze(-1).cpu(), s.reward_buf, rtol=1e-5, atol=1e-5)
+    for i in range(5, 16):
+        agent.run()                                                        # the 16th step triggers the update
+    torch.cuda.synchronize()
+    assert agent.optim_step == 75 and bool(torch.isfinite(agent.net.flat).all())

@@ -17,7 +17,7 @@ import torch
 
 import fly_bproject_b200 as fb
 from oracle import fly_oracle as fo
-from tests.helpers import ATOL_ENV, RTOL_ENV, RTOL_PPO, assert_obs_close, oracle_tables
+from tests.helpers import ATOL_ENV, RTOL_ENV, RTOL_PPO, OraclePool, assert_obs_close, oracle_tables
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -46,15 +46,14 @@ def test_whole_config_rollout_gae_and_one_minibatch_step(asset, full, walking, n
     p0 = {k: v.cpu() for k, v in agent.net.state_dict().items()}
 
     s = fo.EnvState(t)
-    pool = [{k: v.cpu().clone() for k, v in e.items()} for e in env.state.pool]
-    s.root, s.dof_states, s.force = pool[0]["root"], pool[0]["dof_state"], pool[0]["force"]
+    pool = OraclePool(env.state)
+    pool.bind(s)
     var = torch.full((a_dim,), 0.2)
     gen = torch.Generator().manual_seed(1)
     ring = torch.zeros(horizon + 1, n, o_dim)
     acts, logps = torch.zeros(horizon, n, a_dim), torch.zeros(horizon, n)
     rews = torch.zeros(horizon, n, 1)
     check_at = {0, 1, horizon // 2, horizon - 1}
-    idx = 0
     for i in range(horizon):
         noise = torch.randn(n, a_dim, generator=gen)
         ring[i] = s.obs_buf
@@ -63,8 +62,7 @@ def test_whole_config_rollout_gae_and_one_minibatch_step(asset, full, walking, n
         scaled, targets = fo.scale_actions(t, a)                           # fly.py:626-657
         s.actions = scaled
         fo.apply_reset(t, s)                                               # fly.py:446-480
-        idx = (idx + 1) % 2
-        s.root, s.dof_states, s.force = pool[idx]["root"], pool[idx]["dof_state"], pool[idx]["force"]
+        pool.simulate(s)
         fo.post_physics(t, s, walking=walking)                             # fly.py:676-681
         rews[i] = s.reward_buf.unsqueeze(-1)
         var = fo.anneal_var(var)
