@@ -46,7 +46,22 @@ class PeerGroup(C.Structure):
 
 class StepTail(C.Structure):
     _fields_ = [("action_var", C.c_void_p), ("num_act", C.c_int32), ("decay", C.c_float), ("floor", C.c_float),
-                ("step_counter", C.c_void_p)]
+                ("step_counter", C.c_void_p), ("steps", C.c_int32)]
+
+
+class StepIO(C.Structure):
+    """FlybStepIO: buffers of one fused env-step launch (flyb_env_step_fused)."""
+    _fields_ = [
+        ("root", C.c_void_p), ("dof_state", C.c_void_p), ("force", C.c_void_p),
+        ("actions_scaled", C.c_void_p), ("potentials", C.c_void_p), ("prev_potentials", C.c_void_p),
+        ("progress", C.c_void_p), ("reset", C.c_void_p),
+        ("obs", C.c_void_p), ("obs_ring", C.c_void_p), ("reward", C.c_void_p), ("reward_ring", C.c_void_p),
+        ("reward_sum", C.c_void_p), ("up_vec", C.c_void_p), ("heading_vec", C.c_void_p),
+        ("reset_ids", C.c_void_p), ("reset_count", C.c_void_p), ("scratch", C.c_void_p),
+        ("action_var", C.c_void_p), ("noise", C.c_void_p), ("seed", C.c_uint64), ("offset", C.c_uint64),
+        ("offset_dev", C.c_void_p), ("action", C.c_void_p), ("logp", C.c_void_p), ("dof_targets", C.c_void_p),
+        ("anneal_steps", C.c_int32), ("anneal_decay", C.c_float), ("anneal_floor", C.c_float),
+    ]
 
 
 class NetLayout(C.Structure):
@@ -73,6 +88,8 @@ SIGNATURES = {
     "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 18 + [C.POINTER(StepTail), _P]),
     "flyb_env_pre_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 10),
     "flyb_env_reset": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 7),
+    "flyb_env_step_fused_supported": (C.c_int, [C.POINTER(NetLayout), C.POINTER(EnvCfg)]),
+    "flyb_env_step_fused": (C.c_int, [C.POINTER(NetLayout), _P, _P, C.POINTER(EnvCfg), C.POINTER(StepIO), _P]),
     "flyb_policy_act": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, C.c_uint64, C.c_uint64, _P,
                                   _P, _P, _P, _P, C.POINTER(EnvCfg)] + [_P] * 9),
     "flyb_net_forward": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P, C.c_int64, _P, _P, _P]),

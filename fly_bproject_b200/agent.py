@@ -216,8 +216,13 @@ class PPO:
         self._fused_env = isinstance(self.env, Fly)
         self._foreign_reward_sum = torch.zeros((), **f32)
         testing = bool(_get(args, "testing", False))
-        self._tail = _lib.StepTail(self.action_var.data_ptr(), a, 0.0 if testing else 0.00001, 0.0 if testing else 0.01,
-                                   self._rng_counter.data_ptr())
+        self._decay, self._floor = (0.0, 0.0) if testing else (0.00001, 0.01)             # ppo.py:236-237
+        self._tail = _lib.StepTail(self.action_var.data_ptr(), a, self._decay, self._floor, self._rng_counter.data_ptr(), 1)
+        # one launch per env step inside collect_rollout (flyb_env_step_fused): tensor-core path, standard step order
+        self._fused_steps = bool(
+            self._fused_env and self.net.wpack is not None and not self.env.reset_after_simulate
+            and _get(args, "fused_steps", True)
+            and self.lib.flyb_env_step_fused_supported(C.byref(self.net.layout), C.byref(self.env.cfg)))
         self._graphs = {}
         if resume_state is not None:
             self._restore(resume_state)
@@ -317,15 +322,60 @@ class PPO:
                 self.run_step, self.optim_step, self.score, self.action_var[0].item()))
         self.score = 0
 
+    # ------------------------------------------------------------------ rollout with one launch per env step
+    def _fused_step(self, i: int, noise: Optional[torch.Tensor] = None) -> None:
+        """Launch i (1 <= i < T) of a fused rollout: obs + reward + reset of env step i-1, then act + pre-physics of env
+        step i, for the same envs in the same CTA (flyb_env_step_fused)."""
+        env, p, st = self.env, _lib.ptr, self.env.state
+        io = _lib.StepIO(
+            p(st.root), p(st.dof_state), p(st.force), p(env._actions_scaled), p(env.potentials), p(env.prev_potentials),
+            p(env.progress_buf), p(env.reset_buf), None, p(self._obs_ring[i]), p(env.reward_buf),
+            p(self.all_reward[i - 1]), p(env.reward_sum), p(env.up_vec), p(env.heading_vec), p(env.reset_ids),
+            p(env.reset_count), p(env._scratch), p(self.action_var), p(noise), self.seed, i, p(self._rng_counter),
+            p(self.all_acts[i]), p(self.all_log_prob[i]), p(env.dof_targets), i, self._decay, self._floor)
+        _lib.check(self.lib.flyb_env_step_fused(C.byref(self.net.layout), p(self.net.flat), p(self.net.wpack),
+                                                C.byref(env.cfg), C.byref(io), _lib.current_stream()),
+                   "flyb_env_step_fused")
+        st.set_dof_position_targets(env.dof_targets)
+        st.set_reset_ids(env.reset_ids, env.reset_count)
+        env.simulate()
+        env.render_count += 1
+
+    def _rollout_kernels(self, noise: Optional[torch.Tensor] = None) -> None:
+        """The T env steps of one rollout.  Fused schedule (tensor-core path): act of step 0, T-1 fused launches, one
+        closing obs + reward + reset launch whose tail applies the rollout's T annealing steps — T + 1 launches.  Same
+        buffers, bit for bit, as T x `_step_kernels` (2T launches), which every other configuration uses.
+        `noise` (T, N, A): explicit eps per step (parity tests)."""
+        t = self.rollout_size
+        if not self._fused_steps:
+            for i in range(t):
+                self._step_kernels(i, None if noise is None else noise[i])
+            return
+        env, p, st = self.env, _lib.ptr, self.env.state
+        _lib.check(self.lib.flyb_policy_act(
+            C.byref(self.net.layout), p(self.net.flat), p(self.net.wpack), p(env.obs_buf), self.num_envs,
+            p(self.action_var), p(None if noise is None else noise[0]), self.seed, 0, p(self._rng_counter),
+            p(self.all_acts[0]), p(self.all_log_prob[0]), None, p(self._obs_ring[0]), C.byref(env.cfg),
+            p(env._actions_scaled), p(env.dof_targets), p(env.reset_buf), p(env.progress_buf), p(env.potentials),
+            p(env.prev_potentials), p(st.root), p(st.dof_state), _lib.current_stream()), "flyb_policy_act")
+        st.set_dof_position_targets(env.dof_targets)
+        st.set_reset_ids(env.reset_ids, env.reset_count)
+        env.simulate()
+        env.render_count += 1
+        for i in range(1, t):
+            self._fused_step(i, None if noise is None else noise[i])
+        tail = _lib.StepTail(self.action_var.data_ptr(), self.num_acts, self._decay, self._floor,
+                             self._rng_counter.data_ptr(), t)
+        env.post_physics(obs_copy=self._obs_ring[t], reward_copy=self.all_reward[t - 1], tail=tail)
+
     # ------------------------------------------------------------------ rollout as one CUDA graph
-    def collect_rollout(self, use_graph: bool = True) -> None:
-        """T env steps (act + pre-physics, state source, obs + reward + reset).  With `use_graph` the T x 3 launches
-        are captured once and replayed: the per-step pointers (rollout rows, state-pool entries) are baked in, the
+    def collect_rollout(self, use_graph: bool = True, noise: Optional[torch.Tensor] = None) -> None:
+        """T env steps (act + pre-physics, state source, obs + reward + reset).  With `use_graph` the launches are
+        captured once and replayed: the per-step pointers (rollout rows, state-pool entries) are baked in, the
         Philox draw number and action_var advance on the device."""
         t = self.rollout_size
         if not use_graph:
-            for i in range(t):
-                self._step_kernels(i)
+            self._rollout_kernels(noise)
             self.run_step += t
             return
         g = self._graphs.get("rollout")
@@ -333,13 +383,11 @@ class PPO:
             pool = len(getattr(self.env.state, "pool", [None]))
             if t % pool != 0:
                 raise _lib.FlybError(f"graph capture needs rollout_size ({t}) to be a multiple of the state pool ({pool})")
-            for i in range(t):          # warm-up outside capture (also sets the kernels' smem attributes)
-                self._step_kernels(i)
+            self._rollout_kernels()     # warm-up outside capture (also sets the kernels' smem attributes)
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                for i in range(t):
-                    self._step_kernels(i)
+                self._rollout_kernels()
             self._graphs["rollout"] = g
             self.run_step += t
             return

@@ -15,6 +15,7 @@
 //     one 64-bit mask per CTA -> the last CTA to finish scans the bitmap and writes the id list; the count
 //     stays on the device — the reference's host sync at fly.py:447-450 is gone.
 #include "env_math.cuh"
+#include "env_scan.cuh"
 
 namespace flyb {
 unsigned long long* tc_get_trace();
@@ -22,22 +23,6 @@ unsigned long long* tc_get_trace();
 constexpr int ENVS = 64;           // envs per CTA
 constexpr int PP_THREADS = 256;    // 4 threads per env for the load / store sweeps; threads [0, ENVS) own one env each
 constexpr int PP_WARPS = PP_THREADS / 32;
-
-// cross-CTA scratch: `done` counts finished CTAs (re-armed by the last one), status[b] = 64-bit reset mask of CTA b
-struct ScanScratch {
-  unsigned int ticket;   // unused (kept so that the scratch size / zeroing contract of ABI v2 stands)
-  unsigned int done;
-  unsigned long long status[1];
-};
-
-FLYB_D unsigned long long ld_status(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-FLYB_D void st_status(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
 
 // The kernel is latency-bound at the env counts of the reference's configs (16384 envs = 12.5 MB per launch), so
 // every thread issues ALL its global loads before the first dependent shared-memory store, with as little address
@@ -342,9 +327,13 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     scratch->done = 0u;                                 // re-armed for the next launch
   }
   if (tail.action_var != nullptr) {   // end-of-step housekeeping (ppo.py:236-237), once per launch
-    for (int i = tid; i < tail.num_act; i += PP_THREADS)
-      tail.action_var[i] = fmaxf(tail.floor, tail.action_var[i] - tail.decay);
-    if (tid == 0 && tail.step_counter != nullptr) *tail.step_counter += 1ull;
+    const int steps = tail.steps > 0 ? tail.steps : 1;   // a fused rollout applies its T annealing steps at its end
+    for (int i = tid; i < tail.num_act; i += PP_THREADS) {
+      float v = tail.action_var[i];
+      for (int j = 0; j < steps; ++j) v = fmaxf(tail.floor, v - tail.decay);   // iterated: bit-identical to T launches
+      tail.action_var[i] = v;
+    }
+    if (tid == 0 && tail.step_counter != nullptr) *tail.step_counter += (unsigned long long)steps;
   }
 }
 
@@ -412,7 +401,7 @@ using namespace flyb;
 
 extern "C" size_t flyb_env_scratch_bytes(int32_t num_envs) {
   const size_t nblk = num_envs > 0 ? (size_t)(num_envs + ENVS - 1) / ENVS : 1;
-  return 16 + nblk * sizeof(unsigned long long);
+  return 16 + (nblk + 1) * sizeof(unsigned long long);   // + 1: the fused step publishes two words per 128-env tile
 }
 
 static int validate_cfg(const FlybEnvCfg* cfg) {

@@ -253,7 +253,7 @@ FLYB_D void trace_mark(unsigned long long* trace, int& idx, int limit) {
 // first tile's observation rows and the first NST stages of the weight stream are put in flight.  The producer loop
 // later skips exactly these (it still does its barrier bookkeeping).  Call once, by all 32 lanes of warp
 // PRODUCER_WARP, at kernel start; every other thread must pass a __syncthreads() before touching a barrier.
-FLYB_D void producer_kickoff(const Smem& s, const FwdArgs& a) {
+FLYB_D void producer_kickoff(const Smem& s, const FwdArgs& a, bool load_obs = true) {
   if (tc::elect_one()) {
     for (int i = 0; i < NST; ++i) {
       tc::mbar_init(&s.full[i], 1);
@@ -272,7 +272,7 @@ FLYB_D void producer_kickoff(const Smem& s, const FwdArgs& a) {
       const int nrows = (int)min((long long)TM, a.rows - row0);
       const uint32_t bytes = (uint32_t)nrows * (uint32_t)a.O * 4u;
       const float* src = a.obs + (size_t)row0 * a.O;
-      if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+      if (load_obs && (bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
         tc::mbar_arrive_expect_tx(s.obs_full, bytes);
         tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
       }
@@ -329,6 +329,11 @@ FLYB_D void setup_wait() { asm volatile("bar.sync 2, %0;" ::"n"(SETUP_BAR_THREAD
 //   pi(s, row0, r, h, nrows, mu[32])       both column halves call it with the full mu row (ELU applied)
 //   value(row0, r, nrows, v)               half 0 only
 //   finish(s)                              once, after the last tile
+//   Final::kBuildsObs (static constexpr bool)   true: the observation tile is not loaded from `a.obs` but BUILT by the
+//                                          epilogue warps — build_obs(s, row0, nrows) must leave the tile's rows in
+//                                          s.obs (row-major, O floats per row), fenced for the async proxy and with all
+//                                          256 threads synchronised (the fused env step: obs + reward + reset + act)
+//   aux_warp(s, ntiles)                    body of any warp beyond the ten above (a kernel launched with more threads)
 // Implementations: policy_kernels_tc.cu.
 // KICKED: producer_kickoff() already ran (at the top of the kernel); otherwise it runs here.
 template <bool WANT_PI, bool WANT_V, class Final, bool KICKED = false>
@@ -340,7 +345,8 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
   const long long ntiles = (a.rows + TM - 1) / TM;
 
   // ---- one-time setup
-  if (!KICKED && warp == PRODUCER_WARP) producer_kickoff(s, a);
+  constexpr bool BUILD = Final::kBuildsObs;
+  if (!KICKED && warp == PRODUCER_WARP) producer_kickoff(s, a, !BUILD);
   if (warp == MMA_WARP) tc::tmem_alloc(s.tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
@@ -364,7 +370,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       const float* src = a.obs + (size_t)row0 * O;
       // The first tile's rows were requested by producer_kickoff(): no wait for it (the epilogue warps may already
       // have released that buffer by now — waiting for "the phase before" would then wait for the NEXT release).
-      if (kicked == 0) {
+      if (kicked == 0 && !BUILD) {
         tc::mbar_wait_relaxed(s.obs_empty, obs_phase);   // the epilogue warps are done with the previous tile's rows
         obs_phase ^= 1u;
         if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
@@ -439,7 +445,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
         trace_mark(mtrace, ti, 64);
       }
     }
-  } else {
+  } else if (warp < EPI_WARPS) {
     // =========================================================================== epilogue warps
     const int q = warp & 3, h = warp >> 2;
     const uint32_t lane_base = (uint32_t)q * 32u;
@@ -465,7 +471,9 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
       const float* src = a.obs + (size_t)row0 * O;
       const bool by_tma = (bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0;
-      if (by_tma) {
+      if constexpr (BUILD) {
+        fin.build_obs(s, row0, nrows);
+      } else if (by_tma) {
         tc::mbar_wait(s.obs_full, obs_phase);
         obs_phase ^= 1u;
       } else {   // ragged / unaligned tile: cooperative loads
@@ -566,6 +574,8 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
     }
     if (!setup_seen) setup_wait();
     fin.finish(s);
+  } else {
+    fin.aux_warp(s, ntiles);
   }
 
   // ---- teardown

@@ -198,6 +198,9 @@ int validate_net(const FlybNetLayout* net, const float* params) {
 // tensor-core path (policy_kernels_tc.cu)
 bool tc_supported(const FlybNetLayout* net);
 bool tc_act_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg);
+bool tc_step_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg);
+int tc_launch_step(const FlybNetLayout* net, const float* params, const void* wpack, const FlybEnvCfg* cfg,
+                   const FlybStepIO* io, cudaStream_t st);
 size_t tc_wpack_bytes(const FlybNetLayout* net);
 int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st);
 int tc_launch_forward(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs,
@@ -228,6 +231,37 @@ extern "C" int flyb_pack_weights(const FlybNetLayout* net, const float* params, 
   FLYB_REQUIRE(wpack != nullptr && aligned16(wpack), "flyb_pack_weights: wpack must be a 16-byte aligned buffer");
   FLYB_REQUIRE(tc_supported(net), "flyb_pack_weights: the tensor-core path needs num_obs <= 80 and num_act <= 32");
   return tc_pack_weights(net, params, wpack, (cudaStream_t)stream);
+}
+
+extern "C" int flyb_env_step_fused_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg) {
+  return (net && cfg && tc_step_supported(net, cfg)) ? 1 : 0;
+}
+
+extern "C" int flyb_env_step_fused(const FlybNetLayout* net, const float* params, const void* wpack,
+                                   const FlybEnvCfg* cfg, const FlybStepIO* io, void* stream) {
+  int rc = validate_net(net, params);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(cfg && io && wpack, "flyb_env_step_fused: NULL cfg / io / wpack (the fused step runs on the tensor-core path only)");
+  FLYB_REQUIRE(cfg->num_envs > 0 && cfg->num_dof > 0 && cfg->num_dof <= FLYB_MAX_DOF && cfg->num_bodies > 0,
+               "flyb_env_step_fused: bad env cfg");
+  FLYB_REQUIRE(cfg->num_act == net->num_act && 19 + 3 * cfg->num_act == net->num_obs,
+               "flyb_env_step_fused: env cfg (A=%d) does not match the net (O=%d, A=%d)", cfg->num_act, net->num_obs,
+               net->num_act);
+  for (int k = 0; k < cfg->num_act; ++k)
+    FLYB_REQUIRE(cfg->action_idx[k] >= 0 && cfg->action_idx[k] < cfg->num_dof, "action_idx[%d] out of range", k);
+  for (int b = 0; b < FLYB_NUM_ABDOMEN; ++b)
+    FLYB_REQUIRE(cfg->abdomen_local[b] >= 0 && cfg->abdomen_local[b] < cfg->num_bodies, "abdomen_local[%d] out of range", b);
+  for (int b = 0; b < FLYB_NUM_LEGTIPS; ++b)
+    FLYB_REQUIRE(cfg->legtip_local[b] >= 0 && cfg->legtip_local[b] < cfg->num_bodies, "legtip_local[%d] out of range", b);
+  FLYB_REQUIRE(tc_step_supported(net, cfg), "flyb_env_step_fused: shape outside the fused path (needs num_obs <= 80, num_act <= 20)");
+  FLYB_REQUIRE(io->root && io->dof_state && io->force && io->actions_scaled && io->potentials && io->prev_potentials &&
+                   io->progress && io->reset && io->reward && io->up_vec && io->heading_vec && io->reset_ids &&
+                   io->reset_count && io->scratch && io->action_var && io->action && io->logp && io->dof_targets,
+               "flyb_env_step_fused: NULL buffer");
+  FLYB_REQUIRE(aligned16(io->root) && aligned16(wpack) && (reinterpret_cast<uintptr_t>(io->dof_state) & 7u) == 0,
+               "flyb_env_step_fused: root / wpack must be 16-byte, dof_state 8-byte aligned");
+  FLYB_REQUIRE(io->anneal_steps >= 0, "flyb_env_step_fused: anneal_steps < 0");
+  return tc_launch_step(net, params, wpack, cfg, io, (cudaStream_t)stream);
 }
 
 extern "C" int flyb_policy_act(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs,

@@ -8,6 +8,7 @@
 #include <algorithm>
 
 #include "env_math.cuh"
+#include "env_scan.cuh"
 #include "mlp_tc.cuh"
 #include "philox.cuh"
 
@@ -138,9 +139,12 @@ FLYB_D void store_tile(float* dst, const float* src_smem, int nfloats) {
 }
 
 struct FwdFinal {
+  static constexpr bool kBuildsObs = false;
   float* mu_out;
   float* value_out;
   int A;
+  FLYB_D void build_obs(const tcm::Smem&, long long, int) {}
+  FLYB_D void aux_warp(const tcm::Smem&, long long) {}
   FLYB_D void setup(int) {}
   FLYB_D void begin_tile(const tcm::Smem&, long long, int, int) {}
   FLYB_D void obs_consumed(const tcm::Smem& s) {
@@ -190,6 +194,11 @@ struct ActTables {
 // per-row quantities (log-prob, reset bookkeeping) are finished by the thread that owns the row.
 // Staging in s.out (floats): mu_s [TM*A] | eps_s, later scaled_s [TM*A] | dsq_s [TM*A].
 struct ActFinal {
+  static constexpr bool kBuildsObs = false;
+  FLYB_D void build_obs(const tcm::Smem&, long long, int) {}
+  FLYB_D void aux_warp(const tcm::Smem&, long long) {}
+  int anneal_steps;        // variance annealing steps applied on the fly to action_var (fused rollout, ppo.py:236-237)
+  float anneal_decay, anneal_floor;
   const float* noise;
   unsigned long long seed, draw;
   float* action;
@@ -222,7 +231,9 @@ struct ActFinal {
   FLYB_D void setup(int lane) {
     ActTables& tab = *tw;
     for (int k = lane; k < A; k += 32) {
-      tab.std[k] = sqrtf(__ldg(action_var + k));
+      float var = __ldg(action_var + k);
+      for (int j = 0; j < anneal_steps; ++j) var = fmaxf(anneal_floor, var - anneal_decay);   // iterated: same bits
+      tab.std[k] = sqrtf(var);
       tab.inv_std[k] = 1.0f / tab.std[k];
       tab.log_std[k] = logf(tab.std[k]);
       if (has_env) {
@@ -377,6 +388,306 @@ struct ActFinal {
   }
 };
 
+
+// ------------------------------------------------------------------------------------------------ fused env step
+// ONE launch per env step of a rollout: [get_obs + progress += 1 + get_reward of step i-1 (fly.py:676-681)] followed by
+// [act + action scaling + DOF targets + Fly.reset bookkeeping of step i (ppo.py:213-220, fly.py:626-660, 446-480)] for
+// the same 128 envs, in the CTA that owns them.  The epilogue warps build their tile's observation rows from the
+// physics state straight into the shared-memory tile the MLP reads (while the weight stream is already in flight);
+// the rows leave once, for the rollout ring.  Reset ids: the tile's 128-bit mask is published by a spare warp, and
+// the spare warp of the tile that finishes last scans the bitmap — the MLP warps never wait for it.
+struct StepTables {
+  int foff[FORCE_VALS];     // float offset of gathered contact value rc inside one env's force block
+  int aidx[FLYB_MAX_DOF];   // action k -> DOF
+  float lo[FLYB_MAX_DOF], hi[FLYB_MAX_DOF];
+  unsigned mask[2][4];      // [tile parity][32-env group]: reset flags of the tile
+};
+
+struct StepEnvArgs {
+  const float* force;
+  float* obs_out;        // nullable: env.obs_buf
+  float* reward;
+  float* reward_ring;    // nullable
+  float* reward_sum;     // nullable
+  float* up_vec;
+  float* heading_vec;
+  int* reset_ids;
+  int* reset_count;
+  ScanScratch* scratch;
+};
+
+constexpr int STEP_THREADS = tcm::THREADS + 32;   // + the mask / scan warp
+constexpr int STEP_AUX_WARP = tcm::THREADS / 32;
+constexpr int STEP_AUX_BAR_THREADS = tcm::EPI_THREADS + 32;
+constexpr size_t STEP_ENV_STAGE_BYTES = (size_t)tcm::TM * (13 + FORCE_VALS + 2) * 4;   // root, force rows, two scalars
+
+FLYB_D float4 ld_global4(const float4* p) {   // coherent 128-bit load (the same kernel later rewrites reset rows)
+  float4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
+struct StepFinal : ActFinal {
+  static constexpr bool kBuildsObs = true;
+  StepEnvArgs e;
+  StepTables* st;
+  bool tables_built;
+  unsigned parity;
+
+  FLYB_D void build_obs(const tcm::Smem& s, long long row0, int nrows) {
+    constexpr int TM = tcm::TM;
+    const FlybEnvCfg& c = *cfg;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int B = c.num_bodies;
+    float* obs_s = s.obs;                              // [TM][O]
+    float* root_s = s.out;                             // [TM][13]
+    float* force_s = root_s + TM * 13;                 // [TM][33]
+    int* cnt_s = reinterpret_cast<int*>(force_s + TM * FORCE_VALS);   // legs | at_limit << 8 | abdomen_hit << 16
+    float* sq_s = reinterpret_cast<float*>(cnt_s + TM);
+    tcm::epi_bar_sync();   // the previous tile's pi() is done with s.out; its ring store has drained s.obs (obs_consumed)
+    if (!tables_built) {
+      if (tid < FORCE_VALS) {
+        const int r = tid / 3;
+        const int body = (r < FLYB_NUM_ABDOMEN) ? c.abdomen_local[r] : c.legtip_local[r - FLYB_NUM_ABDOMEN];
+        st->foff[tid] = body * 3 + (tid - r * 3);
+      }
+      if (tid >= 64 && tid < 64 + A) {
+        const int d = c.action_idx[tid - 64];
+        st->aidx[tid - 64] = d;
+        st->lo[tid - 64] = c.lower[d];
+        st->hi[tid - 64] = c.upper[d];
+      }
+      tables_built = true;
+      tcm::epi_bar_sync();
+    }
+    // ---- every global load of the tile is issued before the first dependent shared-memory store
+    const int en = tid >> 1, qd = tid & 1;             // two threads per env for the gathers
+    const bool e_ok = en < nrows;
+    const long long env = row0 + en;
+    const int nroot = nrows * 13;
+    const float4* root4 = reinterpret_cast<const float4*>(root + (size_t)row0 * 13);   // row0 % 128 == 0: 16-byte aligned
+    float4 r4[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int idx = tid + tcm::EPI_THREADS * u;
+      r4[u] = (idx * 4 + 3 < nroot) ? ld_global4(root4 + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float pot_in[2] = {0.f, 0.f};
+    long long prog_in[2] = {0, 0}, reset_in[2] = {0, 0};
+    if (tid < 64) {
+#pragma unroll
+      for (int p = 0; p < 2; ++p)
+        if (p * 64 + tid < nrows) {
+          pot_in[p] = potentials[row0 + p * 64 + tid];
+          prog_in[p] = progress[row0 + p * 64 + tid];
+          reset_in[p] = reset[row0 + p * 64 + tid];
+        }
+    }
+    constexpr int FITER = (FORCE_VALS + 1) / 2;   // 17
+    float fv[FITER];
+    {
+      const float* fe = e.force + (size_t)env * B * 3;
+#pragma unroll
+      for (int it = 0; it < FITER; ++it) {
+        const int rc = qd + 2 * it;
+        fv[it] = (e_ok && rc < FORCE_VALS) ? __ldg(fe + st->foff[rc]) : 0.0f;
+      }
+    }
+    constexpr int DU = 10;                        // A <= 20 on this path (O = 19 + 3A <= 80)
+    float2 pv[DU];
+    float cmd[DU];
+    {
+      const float2* de = reinterpret_cast<const float2*>(dof_state) + (size_t)env * D;
+      const float* ae = actions_scaled + (size_t)env * A;
+#pragma unroll
+      for (int u = 0; u < DU; ++u) {
+        const int k = qd + 2 * u;
+        pv[u] = make_float2(0.f, 0.f);
+        cmd[u] = 0.0f;
+        if (e_ok && k < A) {
+          pv[u] = de[st->aidx[k]];
+          cmd[u] = ae[k];
+        }
+      }
+    }
+    // ---- stage: obs[12 : 12+3A] (fly.py:795, 801, 802), root rows, gathered contact rows
+    {
+      float* oe = obs_s + en * O + 12;
+#pragma unroll
+      for (int u = 0; u < DU; ++u) {
+        const int k = qd + 2 * u;
+        if (e_ok && k < A) {
+          oe[k] = unscale(pv[u].x, st->lo[k], st->hi[k]);
+          oe[A + k] = pv[u].y * c.dof_vel_scale;
+          oe[2 * A + k] = cmd[u];
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int idx = tid + tcm::EPI_THREADS * u;
+      if (idx * 4 + 3 < nroot) reinterpret_cast<float4*>(root_s)[idx] = r4[u];
+    }
+    for (int i = (nroot & ~3) + tid; i < nroot; i += tcm::EPI_THREADS) root_s[i] = root[(size_t)row0 * 13 + i];
+#pragma unroll
+    for (int it = 0; it < FITER; ++it) {
+      const int rc = qd + 2 * it;
+      if (e_ok && rc < FORCE_VALS) force_s[en * FORCE_VALS + rc] = fv[it];
+    }
+    tcm::epi_bar_sync();
+
+    // ---- per-env math: four roles (warp pairs), each over the tile's two 64-env halves.  role 0: potential, heading /
+    //      up projections, later reward + termination; 1: local velocities; 2: Euler angles; 3: contact flags, sums
+    const int role = warp >> 1;
+    const int me0 = ((warp & 1) << 5) | lane;
+    float k_hproj[2], k_pot[2], k_h[2], k_qz[2], k_qw[2];
+    Vec3 k_up[2], k_head[2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const int me = p * 64 + me0;
+      const bool me_ok = me < nrows;
+      float r[13];
+#pragma unroll
+      for (int j = 0; j < 13; ++j) r[j] = me_ok ? root_s[me * 13 + j] : (j == 6 ? 1.0f : 0.0f);
+      float* o = obs_s + me * O;
+      const Quat tq = env_torso_quat(r, c);
+      EnvObsHead h;
+      h.heading_proj = 0.0f; h.potential = 0.0f;
+      if (role == 0) {
+        env_head_heading(r, c, tq, h);
+        if (me_ok) { o[10] = h.up_proj; o[11] = h.heading_proj; }
+        k_hproj[p] = h.heading_proj; k_pot[p] = h.potential; k_h[p] = r[2]; k_qz[p] = r[5]; k_qw[p] = r[6];
+        k_up[p] = h.up_vec; k_head[p] = h.heading_vec;
+      } else if (role == 1) {
+        env_head_vel(r, tq, h);
+        if (me_ok) {
+          o[0] = h.height;
+          o[1] = h.vel_loc.x; o[2] = h.vel_loc.y; o[3] = h.vel_loc.z;
+          o[4] = h.angvel_loc.x; o[5] = h.angvel_loc.y; o[6] = h.angvel_loc.z;
+        }
+      } else if (role == 2) {
+        env_head_euler(r, c, tq, h);
+        if (me_ok) { o[7] = h.yaw; o[8] = h.roll; o[9] = h.angle_to_target; o[12 + 3 * A] = h.pitch; }
+      } else if (me_ok) {
+        const float* f = force_s + me * FORCE_VALS;
+        float abdomen = 0.0f;
+#pragma unroll
+        for (int b = 0; b < FLYB_NUM_ABDOMEN; ++b) abdomen += (f[b * 3] + f[b * 3 + 1]) + f[b * 3 + 2];
+        int legs = 0, at_limit = 0;
+#pragma unroll
+        for (int b = 0; b < FLYB_NUM_LEGTIPS; ++b) {
+          const float* fr = f + (FLYB_NUM_ABDOMEN + b) * 3;
+          const bool touch = ((fr[0] + fr[1]) + fr[2]) > 0.0f;
+          o[13 + 3 * A + b] = touch ? 1.0f : 0.0f;    // fly.py:797, 803
+          legs += touch ? 1 : 0;
+        }
+        float actions_sq_sum = 0.0f;
+        const float* cm = o + 12 + 2 * A;
+        for (int k = 0; k < A; ++k) {
+          const float av = cm[k];
+          actions_sq_sum += av * av;                    // fly.py:731
+          at_limit += (av > st->hi[k] * 0.9f) ? 1 : 0;  // fly.py:736-737
+          at_limit += (av < st->lo[k] * 0.9f) ? 1 : 0;
+        }
+        cnt_s[me] = legs | (at_limit << 8) | ((abdomen > 0.0f ? 1 : 0) << 16);
+        sq_s[me] = actions_sq_sum;
+      }
+    }
+    tcm::epi_bar_sync();
+    if (role == 0) {
+      float my_reward = 0.0f;
+#pragma unroll
+      for (int p = 0; p < 2; ++p) {
+        const int me = p * 64 + me0;
+        const bool me_ok = me < nrows;
+        bool flag = false;
+        if (me_ok) {
+          const long long gi = row0 + me;
+          const int packed = cnt_s[me];
+          EnvRewardIn in;
+          in.actions_sq_sum = sq_s[me];
+          in.electricity = 0.0f;
+          in.at_limit = (packed >> 8) & 0xff;
+          in.height = k_h[p];
+          in.heading_proj = k_hproj[p];
+          in.qz = k_qz[p];
+          in.qw = k_qw[p];
+          in.prev_potential = pot_in[p];    // fly.py:780
+          in.potential = k_pot[p];
+          in.legs_touching = packed & 0xff;
+          in.abdomen_hit = (packed >> 16) != 0;
+          long long prog = prog_in[p] + 1;  // fly.py:678
+          if (prog == 0) prog = 1;          // fly.py:415-416
+          in.progress = prog;
+          in.reset_prev = reset_in[p];
+          float rew;
+          long long rst;
+          env_reward_reset(in, c, &rew, &rst);
+          potentials[gi] = k_pot[p];
+          prev_potentials[gi] = pot_in[p];
+          progress[gi] = prog;
+          reset[gi] = rst;                  // read back by this tile's act half (begin_tile), behind the barrier below
+          e.reward[gi] = rew;
+          if (e.reward_ring) e.reward_ring[gi] = rew;
+          my_reward += rew;
+          e.up_vec[gi * 3 + 0] = k_up[p].x; e.up_vec[gi * 3 + 1] = k_up[p].y; e.up_vec[gi * 3 + 2] = k_up[p].z;
+          e.heading_vec[gi * 3 + 0] = k_head[p].x; e.heading_vec[gi * 3 + 1] = k_head[p].y;
+          e.heading_vec[gi * 3 + 2] = k_head[p].z;
+          flag = rst != 0;
+        }
+        const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+        if (lane == 0) st->mask[parity][p * 2 + (warp & 1)] = ballot;
+      }
+      if (e.reward_sum) {   // score accumulator (ppo.py:233), one atomic per warp
+        const float ws = warp_sum(my_reward);
+        if (lane == 0) atomicAdd(e.reward_sum, ws);
+      }
+    }
+    tc::fence_proxy_async();   // the tile's rows in s.obs -> visible to the bulk stores of begin_tile
+    tcm::epi_bar_sync();
+    asm volatile("bar.arrive 3, %0;" ::"n"(STEP_AUX_BAR_THREADS) : "memory");   // masks are in shared memory: wake the spare warp
+    parity ^= 1u;
+  }
+
+  FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {
+    rst_raw = (r < nrows) ? reset[row0 + r] : 0;
+    if (obs_store) store_tile(obs_store + (size_t)row0 * O, s.obs, nrows * O);      // rollout row (ppo.py:226, 228)
+    if (e.obs_out) store_tile(e.obs_out + (size_t)row0 * O, s.obs, nrows * O);      // env.obs_buf
+    if ((obs_store || e.obs_out) && threadIdx.x == 0) tc::tma_store_commit();
+  }
+  FLYB_D void obs_consumed(const tcm::Smem& s) {
+    if ((obs_store || e.obs_out) && threadIdx.x == 0) tc::tma_store_wait_read<0>();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) tc::mbar_arrive(s.obs_empty);
+  }
+
+  // the spare warp: publish the tile's masks, count the tile as done, scan the bitmap if it was the last one
+  FLYB_D void aux_warp(const tcm::Smem&, long long ntiles) {
+    if ((threadIdx.x >> 5) != STEP_AUX_WARP) return;
+    const int lane = threadIdx.x & 31;
+    unsigned par = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1u) {
+      asm volatile("bar.sync 3, %0;" ::"n"(STEP_AUX_BAR_THREADS) : "memory");
+      unsigned last = 0;
+      if (lane == 0) {
+        unsigned long long* bitmap = e.scratch->status;
+        const unsigned* m = st->mask[par];
+        st_status(bitmap + 2 * tile, ((unsigned long long)m[1] << 32) | (unsigned long long)m[0]);
+        st_status(bitmap + 2 * tile + 1, ((unsigned long long)m[3] << 32) | (unsigned long long)m[2]);
+        __threadfence();
+        const unsigned prev = atomicAdd(&e.scratch->done, 1u);
+        last = (prev == (unsigned)(ntiles - 1)) ? 1u : 0u;
+        if (last) __threadfence();
+      }
+      last = __shfl_sync(0xffffffffu, last, 0);
+      if (last) scan_masks_warp(e.scratch, (int)(2 * ntiles), e.reset_ids, e.reset_count);
+    }
+  }
+};
+
 // ------------------------------------------------------------------------------------------------ kernels
 template <bool WANT_PI, bool WANT_V>
 __global__ void __launch_bounds__(tcm::THREADS, 1)
@@ -421,8 +732,37 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
   fin.actions_scaled = x.actions_scaled; fin.dof_targets = x.dof_targets; fin.reset = x.reset; fin.progress = x.progress;
   fin.potentials = x.potentials; fin.prev_potentials = x.prev_potentials; fin.root = x.root; fin.dof_state = x.dof_state;
   fin.t = &tab; fin.tw = &tab; fin.action_var = x.action_var; fin.rst_raw = 0; fin.trace = a.trace; fin.ti = 128;
+  fin.anneal_steps = 0; fin.anneal_decay = 0.0f; fin.anneal_floor = 0.0f;
   tcm::forward_persistent<true, false>(net, a, fin);
   if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[191] = clock64();       // kernel exit
+}
+
+
+struct StepTcArgs {
+  ActTcArgs act;
+  StepEnvArgs env;
+  int anneal_steps;
+  float anneal_decay, anneal_floor;
+};
+
+__global__ void __launch_bounds__(STEP_THREADS, 1)
+env_step_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_constant__ tcm::FwdArgs a,
+                   const __grid_constant__ StepTcArgs y, const __grid_constant__ FlybEnvCfg cfg) {
+  __shared__ ActTables tab;
+  __shared__ StepTables stab;
+  const ActTcArgs& x = y.act;
+  StepFinal fin;
+  fin.noise = x.noise; fin.seed = x.seed;
+  fin.draw = x.offset + (x.offset_dev ? __ldg(x.offset_dev) : 0ull);
+  fin.action = x.action; fin.logp = x.logp; fin.mu_out = x.mu_out; fin.obs_store = x.obs_store;
+  fin.A = net.num_act; fin.O = net.num_obs; fin.D = cfg.num_dof;
+  fin.cfg = &cfg; fin.has_env = 1;
+  fin.actions_scaled = x.actions_scaled; fin.dof_targets = x.dof_targets; fin.reset = x.reset; fin.progress = x.progress;
+  fin.potentials = x.potentials; fin.prev_potentials = x.prev_potentials; fin.root = x.root; fin.dof_state = x.dof_state;
+  fin.t = &tab; fin.tw = &tab; fin.action_var = x.action_var; fin.rst_raw = 0; fin.trace = a.trace; fin.ti = 128;
+  fin.anneal_steps = y.anneal_steps; fin.anneal_decay = y.anneal_decay; fin.anneal_floor = y.anneal_floor;
+  fin.e = y.env; fin.st = &stab; fin.tables_built = false; fin.parity = 0u;
+  tcm::forward_persistent<true, false>(net, a, fin);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -514,6 +854,42 @@ int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpa
   if ((rc = prepare(policy_act_tc_kernel, smem)) != FLYB_OK) return rc;
   policy_act_tc_kernel<<<grid, tcm::THREADS, smem, st>>>(*net, a, x, c);
   FLYB_LAUNCH_CHECK("policy_act_tc_kernel");
+  return FLYB_OK;
+}
+
+
+// fused env step (flyb_env_step_fused): shapes the tensor-core act path covers, with the env staging next to the ring
+bool tc_step_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg) {
+  if (!tc_supported(net) || cfg == nullptr || net->num_act > 20) return false;
+  const size_t out = std::max((size_t)tcm::TM * 3 * net->num_act * 4, STEP_ENV_STAGE_BYTES);
+  return tcm::smem_bytes(net->num_obs, out) <= 227u * 1024u - 3072u;   // static tables of the kernel
+}
+
+int tc_launch_step(const FlybNetLayout* net, const float* params, const void* wpack, const FlybEnvCfg* cfg,
+                   const FlybStepIO* io, cudaStream_t st) {
+  const size_t out = std::max((size_t)tcm::TM * 3 * net->num_act * 4, STEP_ENV_STAGE_BYTES);
+  const long long rows = cfg->num_envs;
+  tcm::FwdArgs a{nullptr, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, out, g_trace};
+  StepTcArgs y{};
+  ActTcArgs& x = y.act;
+  x.action_var = io->action_var; x.noise = io->noise; x.seed = io->seed; x.offset = io->offset;
+  x.offset_dev = (const unsigned long long*)io->offset_dev;
+  x.action = io->action; x.logp = io->logp; x.mu_out = nullptr; x.obs_store = io->obs_ring;
+  x.has_env = 1;
+  x.actions_scaled = io->actions_scaled; x.dof_targets = io->dof_targets; x.reset = (long long*)io->reset;
+  x.progress = (long long*)io->progress; x.potentials = io->potentials; x.prev_potentials = io->prev_potentials;
+  x.root = io->root; x.dof_state = io->dof_state;
+  y.env.force = io->force; y.env.obs_out = io->obs; y.env.reward = io->reward; y.env.reward_ring = io->reward_ring;
+  y.env.reward_sum = io->reward_sum; y.env.up_vec = io->up_vec; y.env.heading_vec = io->heading_vec;
+  y.env.reset_ids = io->reset_ids; y.env.reset_count = io->reset_count; y.env.scratch = (ScanScratch*)io->scratch;
+  y.anneal_steps = io->anneal_steps; y.anneal_decay = io->anneal_decay; y.anneal_floor = io->anneal_floor;
+  const size_t smem = tcm::smem_bytes(net->num_obs, out);
+  const long long ntiles = (rows + tcm::TM - 1) / tcm::TM;
+  const int grid = (int)std::min<long long>(ntiles, (long long)num_sms());
+  int rc;
+  if ((rc = prepare(env_step_tc_kernel, smem)) != FLYB_OK) return rc;
+  env_step_tc_kernel<<<grid, STEP_THREADS, smem, st>>>(*net, a, y, *cfg);
+  FLYB_LAUNCH_CHECK("env_step_tc_kernel");
   return FLYB_OK;
 }
 

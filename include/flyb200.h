@@ -97,12 +97,14 @@ typedef struct FlybPpoCfg {
 
 /* End-of-step housekeeping of PPO.run that rides on the last launch of a step (flyb_env_post_physics) instead of
  * costing one of its own: action_var <- max(floor, action_var - decay) (reference ppo.py:236-237) and the Philox
- * draw counter += 1.  Same effect as flyb_anneal_var. */
+ * draw counter += 1.  Same effect as flyb_anneal_var.  A rollout made of flyb_env_step_fused launches (which apply the
+ * annealing of their step number on the fly) passes steps = T with its closing flyb_env_post_physics. */
 typedef struct FlybStepTail {
   float* action_var;        /* (num_act) device; NULL = nothing to do */
   int32_t num_act;
   float decay, floor;
   uint64_t* step_counter;   /* device, nullable */
+  int32_t steps;            /* how many steps' worth to apply (iterated; counter += steps); 0 counts as 1 */
 } FlybStepTail;
 
 int flyb_abi_version(void);
@@ -176,6 +178,54 @@ int flyb_policy_act(const FlybNetLayout* net, const float* params, const void* w
                     float* logp, float* mu_out, float* obs_store, const FlybEnvCfg* cfg, float* actions_scaled,
                     float* dof_targets, int64_t* reset, int64_t* progress, float* potentials,
                     float* prev_potentials, float* root, float* dof_state, void* stream);
+
+/* ---- fused env step of a rollout: ONE launch = [flyb_env_post_physics of env step i-1] followed by
+ *      [flyb_policy_act fused with flyb_env_pre_physics of env step i] for the same envs, i.e. reference
+ *      fly.py:676-681 + ppo.py:213-220 + fly.py:626-660, 446-480 back to back.  The CTA that owns 128 envs builds their
+ *      observation rows from the physics state (after simulate()) straight into the tile its tcgen05 MLP reads; the rows
+ *      leave once, for the rollout ring.  Same results as the two calls, bit for bit (reward_sum up to the order of its
+ *      atomics).  A T-step rollout is  flyb_policy_act (step 0), T-1 x flyb_env_step_fused, flyb_env_post_physics
+ *      (closing, with FlybStepTail.steps = T): T + 1 launches instead of 2T.
+ *      Needs the tensor-core path (wpack) and num_act <= 20; flyb_env_step_fused_supported() tells.
+ *      Variance annealing (ppo.py:236-237): launch number i of the rollout passes anneal_steps = i — the kernel uses
+ *      action_var as it will be after i annealing steps (iterated, same bits) and the Philox draw `offset + *offset_dev`
+ *      with offset = i; action_var and the counter themselves are advanced by the closing post-physics tail. */
+typedef struct FlybStepIO {
+  /* physics state after simulate() (fly.py:378-395); root / dof_state rows of the envs this step resets are rewritten */
+  float* root;               /* (N,13) */
+  float* dof_state;          /* (N,D,2) */
+  const float* force;        /* (N*B,3) */
+  /* env buffers, in/out */
+  float* actions_scaled;     /* in: `self.actions` of step i-1 (fly.py:636); out: of step i */
+  float* potentials;
+  float* prev_potentials;
+  int64_t* progress;
+  int64_t* reset;            /* out: the mask after this step's Fly.reset bookkeeping (0 for the envs it reset) */
+  /* out, post-physics half */
+  float* obs;                /* (N,O) nullable: env.obs_buf */
+  float* obs_ring;           /* (N,O) nullable: rollout row all_obs[i] == all_next_obs[i-1] (ppo.py:226, 228) */
+  float* reward;             /* (N) */
+  float* reward_ring;        /* (N) nullable: all_reward[i-1] (ppo.py:229) */
+  float* reward_sum;         /* (1) nullable */
+  float* up_vec;             /* (N,3) */
+  float* heading_vec;        /* (N,3) */
+  int32_t* reset_ids;        /* (N): ascending ids of the envs whose mask step i-1 set (what step i resets) */
+  int32_t* reset_count;      /* (1) */
+  void* scratch;             /* flyb_env_scratch_bytes(N), zeroed once */
+  /* act half */
+  const float* action_var;   /* (A) */
+  const float* noise;        /* (N,A) nullable: explicit eps; NULL -> Philox */
+  uint64_t seed, offset;
+  const uint64_t* offset_dev;
+  float* action;             /* (N,A) clipped: all_acts[i] */
+  float* logp;               /* (N): all_log_prob[i] */
+  float* dof_targets;        /* (N*D) */
+  int32_t anneal_steps;
+  float anneal_decay, anneal_floor;
+} FlybStepIO;
+int flyb_env_step_fused_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg);
+int flyb_env_step_fused(const FlybNetLayout* net, const float* params, const void* wpack, const FlybEnvCfg* cfg,
+                        const FlybStepIO* io, void* stream);
 
 /* Net.pi / Net.v forward over `rows` observation rows (ppo.py:88-102). mu_out (rows,A) / value_out (rows) nullable. */
 int flyb_net_forward(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs, int64_t rows,

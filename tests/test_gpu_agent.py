@@ -523,3 +523,50 @@ def test_env_counts_that_misalign_the_rollout_rows(n):
         agent.run()                                                        # the 16th step triggers the update
     torch.cuda.synchronize()
     assert agent.optim_step == 75 and bool(torch.isfinite(agent.net.flat).all())
+
+
+@pytest.mark.parametrize("n,horizon,pool,explicit_noise", [(16384, 32, 16, False), (40000, 8, 4, True), (100, 4, 2, False),
+                                                           (4096 + 77, 16, 4, True)])
+def test_fused_rollout_is_bit_identical_to_the_two_kernel_rollout(n, horizon, pool, explicit_noise):
+    """flyb_env_step_fused (one launch per env step: obs + reward + reset of step i-1, act + pre-physics of step i) against
+    the two-launch schedule on the same seeds: every rollout buffer, env buffer, the synthetic state (reset rows), the
+    compacted ids, the annealed variance and the Philox counter must agree bit for bit.  Sizes cover one tile per CTA,
+    the persistent multi-tile loop with a ragged last tile, and a single ragged tile."""
+    if not TC:
+        pytest.skip("the fused step exists on the tensor-core path only")
+    agents = []
+    noise = None
+    if explicit_noise:
+        noise = torch.randn(horizon, n, 18, generator=torch.Generator().manual_seed(n)).to(DEV)
+    for fused in (True, False):
+        torch.manual_seed(3)
+        args = fb.make_args(num_envs=n, sim_device=DEV, horizon=horizon, verbose=False, state_pool=pool, seed=11,
+                            fused_steps=fused)
+        ag = fb.PPO(args)
+        assert ag._fused_steps == fused
+        for _ in range(2):                       # the second rollout starts from the first one's closing state
+            ag.collect_rollout(use_graph=False, noise=noise)
+        agents.append(ag)
+    torch.cuda.synchronize()
+    a, b = agents
+    for name in ("_obs_ring", "all_acts", "all_log_prob", "all_reward", "action_var", "_rng_counter"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
+    for name in ("obs_buf", "reward_buf", "reset_buf", "progress_buf", "potentials", "prev_potentials", "up_vec",
+                 "heading_vec", "_actions_scaled", "dof_targets", "reset_count"):
+        assert torch.equal(getattr(a.env, name), getattr(b.env, name)), name
+    cnt = int(a.env.reset_count.item())
+    assert torch.equal(a.env.reset_ids[:cnt], b.env.reset_ids[:cnt])
+    assert torch.equal(a.env.reset_ids[:cnt], a.env.reset_buf.nonzero().squeeze(-1).to(torch.int32))
+    for ea, eb in zip(a.env.state.pool, b.env.state.pool):
+        assert torch.equal(ea["root"], eb["root"]) and torch.equal(ea["dof_state"], eb["dof_state"])
+    torch.testing.assert_close(a.env.reward_sum, b.env.reward_sum, rtol=1e-5, atol=1e-2)
+    assert int(a._rng_counter.item()) == 2 * horizon
+    # and through a captured graph (what bench.py replays): same as eager, fused against fused
+    torch.manual_seed(3)
+    c = fb.PPO(fb.make_args(num_envs=n, sim_device=DEV, horizon=horizon, verbose=False, state_pool=pool, seed=11))
+    if horizon % pool == 0 and not explicit_noise:
+        c.collect_rollout(use_graph=True)        # warm-up rollout + capture
+        c.collect_rollout(use_graph=True)        # replay
+        torch.cuda.synchronize()
+        for name in ("_obs_ring", "all_acts", "all_log_prob", "all_reward", "action_var"):
+            assert torch.equal(getattr(a, name), getattr(c, name)), name
