@@ -78,10 +78,19 @@ class SyntheticStateSource:
         self.device = torch.device(device)
         npool = max(1, pool)
         states = [synth_state(cfg, seed + 7919 * i, self.device) for i in range(npool)]
-        # root / dof_state of all entries live in ONE slab each (entries are views), so that the restore is two copies
-        self._root_all = torch.stack([s["root"] for s in states]).contiguous()
-        self._dof_all = torch.stack([s["dof_state"] for s in states]).contiguous()
-        self.pool: List[dict] = [{"root": self._root_all[i], "dof_state": self._dof_all[i], "force": states[i]["force"]}
+        # root / dof_state of all entries live in ONE slab each (entries are views), so that the restore is two copies;
+        # every entry starts on a 256-byte boundary whatever N is (the kernels take 16-byte aligned state tensors)
+        def slab(key):
+            numel = states[0][key].numel()
+            pitch = (numel + 63) // 64 * 64
+            flat = torch.zeros(npool * pitch, dtype=torch.float32, device=self.device)
+            views = [flat[i * pitch:i * pitch + numel].view(states[0][key].shape) for i in range(npool)]
+            for v, s in zip(views, states):
+                v.copy_(s[key])
+            return flat, views
+        self._root_all, roots = slab("root")
+        self._dof_all, dofs = slab("dof_state")
+        self.pool: List[dict] = [{"root": roots[i], "dof_state": dofs[i], "force": states[i]["force"]}
                                  for i in range(npool)]
         self.restore = bool(restore)
         self._root_pristine = self._root_all.clone() if self.restore else None
