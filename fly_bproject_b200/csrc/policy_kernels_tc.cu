@@ -437,8 +437,13 @@ struct StepFinal : ActFinal {
   bool tables_built;
   unsigned parity;
 
+  int tb_;   // next env-phase trace slot (172..189), thread 0 of CTA 0
+  FLYB_D void emark() {
+    if (trace != nullptr && threadIdx.x == 0 && blockIdx.x == 0 && tb_ < 190) trace[tb_++] = clock64();
+  }
   FLYB_D void build_obs(const tcm::Smem& s, long long row0, int nrows) {
     constexpr int TM = tcm::TM;
+    emark();   // [0] env phase entered
     const FlybEnvCfg& c = *cfg;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int B = c.num_bodies;
@@ -513,6 +518,7 @@ struct StepFinal : ActFinal {
         }
       }
     }
+    emark();   // [1] every load issued
     // ---- stage: obs[12 : 12+3A] (fly.py:795, 801, 802), root rows, gathered contact rows
     {
       float* oe = obs_s + en * O + 12;
@@ -538,6 +544,7 @@ struct StepFinal : ActFinal {
       if (e_ok && rc < FORCE_VALS) force_s[en * FORCE_VALS + rc] = fv[it];
     }
     tcm::epi_bar_sync();
+    emark();   // [2] loads consumed, tile staged
 
     // ---- per-env math: four roles (warp pairs), each over the tile's two 64-env halves.  role 0: potential, heading /
     //      up projections, later reward + termination; 1: local velocities; 2: Euler angles; 3: contact flags, sums
@@ -597,6 +604,7 @@ struct StepFinal : ActFinal {
       }
     }
     tcm::epi_bar_sync();
+    emark();   // [3] per-env math done
     if (role == 0) {
       float my_reward = 0.0f;
 #pragma unroll
@@ -650,6 +658,7 @@ struct StepFinal : ActFinal {
     tcm::epi_bar_sync();
     asm volatile("bar.arrive 3, %0;" ::"n"(STEP_AUX_BAR_THREADS) : "memory");   // masks are in shared memory: wake the spare warp
     parity ^= 1u;
+    emark();   // [4] reward + masks done, rows visible to the bulk stores
   }
 
   FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {
@@ -761,8 +770,10 @@ env_step_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_const
   fin.potentials = x.potentials; fin.prev_potentials = x.prev_potentials; fin.root = x.root; fin.dof_state = x.dof_state;
   fin.t = &tab; fin.tw = &tab; fin.action_var = x.action_var; fin.rst_raw = 0; fin.trace = a.trace; fin.ti = 128;
   fin.anneal_steps = y.anneal_steps; fin.anneal_decay = y.anneal_decay; fin.anneal_floor = y.anneal_floor;
-  fin.e = y.env; fin.st = &stab; fin.tables_built = false; fin.parity = 0u;
+  fin.e = y.env; fin.st = &stab; fin.tables_built = false; fin.parity = 0u; fin.tb_ = 172;
+  if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[190] = clock64();   // kernel entry
   tcm::forward_persistent<true, false>(net, a, fin);
+  if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[191] = clock64();       // kernel exit
 }
 
 // ------------------------------------------------------------------------------------------------ host side

@@ -12,7 +12,9 @@
 //   [data-parallel runs all-reduce `grad` here]
 //   ppo_norm_kernel / ppo_adam_kernel   clip_grad_norm_ (ppo.py:198) + torch.optim.Adam.step (ppo.py:199).
 #include <algorithm>
+#include <cstdlib>
 
+#include "adam.cuh"
 #include "peer.cuh"
 #include "tc_common.cuh"
 #include "mlp_simt.cuh"
@@ -30,6 +32,11 @@ struct StepFuse {
   long long* step;
   const float* sq_part;
   int sq_parts;
+  // when `tail` is set the weight-gradient kernel itself finishes the step (reduction + clip + Adam behind grid barriers)
+  int tail;
+  float *params, *exp_avg, *exp_avg_sq, *grad_norm_out;
+  double lr, beta1, beta2, eps, max_norm;
+  int done;   // out: 1 = the step was completed by the tail (no Adam launch needed)
 };
 int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                 const float* obs, const float* action, const float* old_logp, const float* target,
@@ -406,64 +413,27 @@ ppo_norm_kernel(float* __restrict__ grad, int total, float scale, float* __restr
   }
 }
 
-struct AdamArgs {
-  double lr, beta1, beta2, eps, max_norm;
-  float scale;
-};
-
 __global__ void __launch_bounds__(256)
 ppo_adam_kernel(float* __restrict__ params, float* __restrict__ grad, float* __restrict__ exp_avg,
                 float* __restrict__ exp_avg_sq, int total, const float* __restrict__ norm_part,
                 const long long* __restrict__ step, const __grid_constant__ AdamArgs a,
                 float* __restrict__ grad_norm_out, uint32_t* __restrict__ peer_epoch, int norm_parts,
                 float* __restrict__ wpack, const int4* __restrict__ wpack_index) {
-  __shared__ float s_coef, s_step_size, s_bc2_sqrt;
+  __shared__ AdamCoef s_c;
   if (threadIdx.x < 32) {
     float t = 0.0f;   // fixed order: lane l adds partials l, l + 32, ...; then the butterfly
     for (int i = threadIdx.x; i < norm_parts; i += 32) t += norm_part[i];
     t = warp_sum(t);
     if (threadIdx.x == 0) {
-      const float total_norm = sqrtf(t);
-      // torch.nn.utils.clip_grad_norm_: clip_coef = max_norm / (total_norm + 1e-6), clamped to 1.0
-      s_coef = fminf((float)a.max_norm / (total_norm + 1e-6f), 1.0f);
-      const double tstep = (double)*step;
-      const double bc1 = 1.0 - pow(a.beta1, tstep);
-      const double bc2 = 1.0 - pow(a.beta2, tstep);
-      s_step_size = (float)(a.lr / bc1);
-      s_bc2_sqrt = (float)sqrt(bc2);
-      if (blockIdx.x == 0 && grad_norm_out) *grad_norm_out = total_norm;
+      s_c = adam_coefficients(a, t, *step);
+      if (blockIdx.x == 0 && grad_norm_out) *grad_norm_out = s_c.total_norm;
       if (blockIdx.x == 0 && peer_epoch) *peer_epoch += 1;   // this exchange is over (every norm CTA has read the old value)
     }
   }
   __syncthreads();
-  const float coef = s_coef, step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
-  const float w1 = (float)(1.0 - a.beta1), b2 = (float)a.beta2, w2 = (float)(1.0 - a.beta2), eps = (float)a.eps;
-  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
-    const float g = grad[i] * a.scale * coef;
-    grad[i] = g;                                      // p.grad after clip_grad_norm_
-    float m = exp_avg[i], v = exp_avg_sq[i];
-    m = m + w1 * (g - m);                             // exp_avg.lerp_(grad, 1 - beta1)
-    v = v * b2;                                       // exp_avg_sq.mul_(beta2)
-    v = v + (w2 * g) * g;                             //   .addcmul_(grad, grad, value = 1 - beta2)
-    const float denom = sqrtf(v) / bc2_sqrt + eps;    // (exp_avg_sq.sqrt() / bias_correction2_sqrt).add_(eps)
-    const float p_new = params[i] + (-step_size) * (m / denom);   // param.addcdiv_(exp_avg, denom, value = -step_size)
-    params[i] = p_new;
-    exp_avg[i] = m;
-    exp_avg_sq[i] = v;
-    if (wpack_index) {   // keep the tensor-core weight stream in step: hi/lo TF32 copies of this parameter, in place
-      const int4 d = wpack_index[i];
-      if (d.x >= 0) {
-        const float hi = __uint_as_float(tc::tf32_rna_bits(p_new));
-        const float lo = __uint_as_float(tc::tf32_rna_bits(p_new - hi));
-        wpack[d.x] = hi;
-        wpack[d.x + d.y] = lo;
-        if (d.z >= 0) {
-          wpack[d.z] = hi;
-          wpack[d.z + d.w] = lo;
-        }
-      }
-    }
-  }
+  const AdamCoef c = s_c;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256)
+    adam_entry(i, a, c, params, grad, exp_avg, exp_avg_sq, wpack, wpack_index);
 }
 
 template <typename K>
@@ -616,10 +586,16 @@ extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, fl
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_step: workspace must be 256-byte aligned");
   FLYB_REQUIRE(tc_supported(net), "flyb_ppo_step: wpack given but the tensor-core path does not cover this shape");
   cudaStream_t st = (cudaStream_t)stream;
-  StepFuse fuse{(long long*)step, nullptr, 0};
+  StepFuse fuse{};
+  fuse.step = (long long*)step;
+  static const bool use_tail = [] { const char* e = getenv("FLYB_PPO_TAIL"); return !(e && e[0] == '0'); }();
+  fuse.tail = use_tail ? 1 : 0;
+  fuse.params = params; fuse.exp_avg = exp_avg; fuse.exp_avg_sq = exp_avg_sq; fuse.grad_norm_out = grad_norm_out;
+  fuse.lr = cfg->lr; fuse.beta1 = cfg->beta1; fuse.beta2 = cfg->beta2; fuse.eps = cfg->eps; fuse.max_norm = cfg->max_grad_norm;
   rc = tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
                    workspace, nullptr, st, &fuse);
   if (rc != FLYB_OK) return rc;
+  if (fuse.done) return FLYB_OK;   // 2 launches: chain, weight gradients + reduction + clip + Adam
   return launch_adam(net, cfg, params, grad, exp_avg, exp_avg_sq, (const long long*)step, 1.0f, grad_norm_out,
                      fuse.sq_part, fuse.sq_parts, wpack, nullptr, st);
 }

@@ -28,6 +28,7 @@
 #include <algorithm>
 #include <cstdlib>
 
+#include "adam.cuh"
 #include "mlp_tc.cuh"
 #include "peer.cuh"
 
@@ -37,11 +38,16 @@ int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
 bool tc_supported(const FlybNetLayout* net);
 unsigned long long* tc_get_trace();
+const int* tc_wpack_index(const FlybNetLayout* net, const void* wpack);
 
 struct StepFuse {   // see ppo_kernels.cu
   long long* step;
   const float* sq_part;
   int sq_parts;
+  int tail;
+  float *params, *exp_avg, *exp_avg_sq, *grad_norm_out;
+  double lr, beta1, beta2, eps, max_norm;
+  int done;
 };
 
 namespace tcb {
@@ -557,6 +563,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
 
 // ================================================================================================ weight gradients
 // One "pair" = one layer's dW = dZ^T X:  A = dZ image (MA features -> D lanes), B = X image (NB features -> columns).
+constexpr int RED_GROUPS_C = 4;                // interleaved partial groups of the gradient reduction (ppo_reduce_tc_kernel)
 constexpr int DW_KG = 2;                       // k-steps (of 8 rows) per pipeline stage
 constexpr int DW_RAW_SLOTS = 4, DW_OP_SLOTS = 2;
 constexpr int DW_TRANS_WARPS = 16, DW_THREADS = (2 + DW_TRANS_WARPS) * 32;
@@ -578,7 +585,29 @@ struct DwPair {
 struct DwRole {
   DwPair pair[2];
 };
+// flyb_ppo_step: the rest of the optimiser step rides in the tail of this kernel (cooperative launch, every CTA
+// resident): grid barrier, fixed-order sum of the per-CTA partials (the same association as ppo_reduce_tc_kernel, so
+// the gradient is bit-identical), per-CTA squared norms, grid barrier, clip coefficient, Adam + in-place refresh of the
+// tensor-core weight stream.  Two launches per optimiser step instead of four.
+struct DwTail {
+  int enabled;
+  int off[12], size[12];
+  int total, nparts, nloss;
+  float inv_rows;
+  const float* loss_part;
+  float* loss;
+  float* grad;
+  float* sq_part;           // [gridDim.x]
+  long long* step;
+  float *params, *exp_avg, *exp_avg_sq, *grad_norm_out;
+  AdamArgs adam;
+  float* wpack;
+  const int4* wpack_index;
+};
+__device__ unsigned g_dw_grid_sync[2];   // grid barrier state of the cooperative launch (count, generation)
+
 struct DwArgs {
+  DwTail tail;
   DwRole role[2];
   long long ntiles;
   int ctas_per_role;
@@ -893,6 +922,77 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 1) tc::tmem_dealloc(tb, 512);
+
+  if (a.tail.enabled) {
+    // ======================================================================= reduction + clip + Adam (flyb_ppo_step)
+    const DwTail& t = a.tail;
+    __shared__ float s_red[DW_THREADS / 32];
+    __shared__ AdamCoef s_c;
+    constexpr int TB = 512;                     // entries per block of work
+    const int tid = threadIdx.x;
+    __threadfence();                            // this CTA's partial is written
+    grid_barrier(g_dw_grid_sync, gridDim.x);
+    float sq = 0.0f;
+    for (int base = blockIdx.x * TB; base < t.total; base += gridDim.x * TB) {
+      const int i = base + tid;
+      if (tid < TB && i < t.total) {
+        bool valid = false;
+#pragma unroll
+        for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= t.off[sg] && i < t.off[sg] + t.size[sg]);
+        float acc[RED_GROUPS_C] = {0.f, 0.f, 0.f, 0.f};   // group g sums partials g, g + 4, ... in order
+        if (valid) {
+          const float* src = a.dw_part + i;
+          int p = 0;
+          for (; p + 4 <= t.nparts; p += 4) {
+            const float v0 = __ldcg(src + (size_t)p * t.total), v1 = __ldcg(src + (size_t)(p + 1) * t.total);
+            const float v2 = __ldcg(src + (size_t)(p + 2) * t.total), v3 = __ldcg(src + (size_t)(p + 3) * t.total);
+            acc[0] += v0; acc[1] += v1; acc[2] += v2; acc[3] += v3;
+          }
+          for (; p < t.nparts; ++p) acc[p & 3] += __ldcg(src + (size_t)p * t.total);
+        }
+        const float g = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+        t.grad[i] = g;
+        sq = fmaf(g, g, sq);
+      }
+    }
+    sq = warp_sum(sq);
+    if (lane == 0) s_red[warp] = sq;
+    __syncthreads();
+    if (tid == 0) {
+      float tot = 0.0f;
+      for (int w = 0; w < DW_THREADS / 32; ++w) tot += s_red[w];
+      t.sq_part[blockIdx.x] = tot;
+      if (blockIdx.x == 0) *t.step += 1;        // Adam's step counter
+    }
+    if (blockIdx.x == 0 && warp == 1) {         // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
+      float x = 0.0f, y = 0.0f;
+      for (int k = lane; k < t.nloss; k += 32) {
+        x += t.loss_part[k * 2 + 0];
+        y += t.loss_part[k * 2 + 1];
+      }
+      x = warp_sum(x);
+      y = warp_sum(y);
+      if (lane == 0) *t.loss = -x * t.inv_rows + y * t.inv_rows;
+    }
+    __threadfence();
+    grid_barrier(g_dw_grid_sync, gridDim.x);
+    if (warp == 0) {
+      float tot = 0.0f;   // fixed order: lane l adds partials l, l + 32, ...; then the butterfly
+      for (int k = lane; k < (int)gridDim.x; k += 32) tot += __ldcg(t.sq_part + k);
+      tot = warp_sum(tot);
+      if (lane == 0) {
+        s_c = adam_coefficients(t.adam, tot, *(volatile long long*)t.step);
+        if (blockIdx.x == 0 && t.grad_norm_out) *t.grad_norm_out = s_c.total_norm;
+      }
+    }
+    __syncthreads();
+    const AdamCoef c = s_c;
+    for (int base = blockIdx.x * TB; base < t.total; base += gridDim.x * TB) {
+      const int i = base + tid;
+      if (tid < TB && i < t.total)
+        adam_entry(i, t.adam, c, t.params, t.grad, t.exp_avg, t.exp_avg_sq, t.wpack, t.wpack_index);
+    }
+  }
 }
 
 // grad = sum of the per-CTA partials (fixed order); entries outside the 12 parameter tensors (alignment padding) = 0
@@ -1048,12 +1148,31 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   { const char* e = getenv("FLYB_DW_DBG"); d.dbg = e ? atoi(e) : 0; }
   const size_t smem2 = 1024 + (size_t)DW_RAW_SLOTS * DW_RAW_SLOT + (size_t)DW_OP_SLOTS * DW_OP_SLOT + 512 + 2048 + 256;
   if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel), smem2)) != FLYB_OK) return rc;
+  const int A = net->num_act;
+  const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
+  if (fuse && fuse->tail && !peers && 2 * w.ctas_per_role <= num_sms()) {
+    // flyb_ppo_step: reduction + clip + Adam in this kernel's tail, behind grid barriers -> cooperative launch
+    DwTail& t = d.tail;
+    t.enabled = 1;
+    for (int i = 0; i < 12; ++i) { t.off[i] = net->off[i]; t.size[i] = sizes[i]; }
+    t.total = net->total; t.nparts = w.ctas_per_role; t.nloss = w.grid1; t.inv_rows = ga.inv_rows;
+    t.loss_part = w.loss_part; t.loss = loss; t.grad = grad; t.sq_part = w.sq_part; t.step = fuse->step;
+    t.params = fuse->params; t.exp_avg = fuse->exp_avg; t.exp_avg_sq = fuse->exp_avg_sq; t.grad_norm_out = fuse->grad_norm_out;
+    t.adam = AdamArgs{fuse->lr, fuse->beta1, fuse->beta2, fuse->eps, fuse->max_norm, 1.0f};
+    t.wpack = (float*)const_cast<void*>(wpack);
+    t.wpack_index = (const int4*)tc_wpack_index(net, wpack);
+    void* kargs[] = {(void*)&d};
+    rc = check_cuda(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(ppo_dw_tc_kernel), dim3(2 * w.ctas_per_role),
+                                                dim3(DW_THREADS), kargs, smem2, st),
+                    "cudaLaunchCooperativeKernel(ppo_dw_tc_kernel)");
+    if (rc != FLYB_OK) return rc;
+    fuse->done = 1;
+    return FLYB_OK;
+  }
   ppo_dw_tc_kernel<<<2 * w.ctas_per_role, DW_THREADS, smem2, st>>>(d);
   FLYB_LAUNCH_CHECK("ppo_dw_tc_kernel");
 
   ReduceArgs r{};
-  const int A = net->num_act;
-  const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
   for (int i = 0; i < 12; ++i) { r.off[i] = net->off[i]; r.size[i] = sizes[i]; }
   r.total = net->total; r.nparts = w.ctas_per_role; r.nloss = w.grid1; r.inv_rows = ga.inv_rows;
   const int red_grid = w.red_grid;

@@ -1,11 +1,11 @@
 # One GPU call that produces everything profiles/ keeps for a round: tests, bench (own + reference arm), per-kernel
-# times, the ncu launch list of the bench command and full-set captures of the hot kernels.  TAG=r01g bash tools/gpu_round.sh
+# times, the ncu launch list of the bench command and full-set captures of the hot kernels.  TAG=r02g bash tools/gpu_round.sh
 set -x
-TAG=${TAG:-r01}
+TAG=${TAG:-r02}
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_tests.log 2>&1; echo "tests exit $?" >> gpurun_out/${TAG}_tests.log
-timeout 600 python bench.py --steps 20 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench exit $?"
-timeout 300 python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 > gpurun_out/${TAG}_ncu.log 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"policy_act|post_physics|ppo_fwd_bwd_tc|ppo_dw_tc|net_forward_tc|gae_scan" -c 8 -o gpurun_out/${TAG}_hot python tools/prof_kernels.py all --iters 1 > gpurun_out/${TAG}_ncu_full.log 2>&1
+timeout 1500 python -m pytest tests -m gpu -q --timeout 900 > gpurun_out/${TAG}_tests.log 2>&1; echo "tests exit $?" >> gpurun_out/${TAG}_tests.log
+timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench exit $?"
+timeout 400 python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/${TAG}_ncu.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"env_step_tc|policy_act|post_physics|ppo_fwd_bwd_tc|ppo_dw_tc|net_forward_tc|gae_scan" -c 9 -o gpurun_out/${TAG}_hot python tools/prof_kernels.py all --iters 1 > gpurun_out/${TAG}_ncu_full.log 2>&1
 tail -3 gpurun_out/${TAG}_tests.log

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Small driver for ncu captures: launches each hot-path kernel a few times at the bench workload (configs[1]).
 
-    python tools/prof_kernels.py [act|post|vfwd|gae|grad|all] [--iters N] [--fp32]
+    python tools/prof_kernels.py [act|post|step|vfwd|gae|grad|all] [--iters N] [--fp32]
 """
 import argparse
 import ctypes as C
@@ -72,7 +72,12 @@ def main():
     def k_grad(i):
         agent._minibatch(0, agent.mini_chunk_size)
 
+    def k_step(i):
+        agent._fused_step(1 + i % (a.horizon - 1))
+
     table = {"act": k_act, "post": k_post, "vfwd": k_vfwd, "gae": k_gae, "grad": k_grad}
+    if agent._fused_steps:
+        table["step"] = k_step
     for name, fn in table.items():
         if a.which in ("all", name):
             timed(name, fn)

@@ -1,0 +1,33 @@
+#!/usr/bin/env python
+"""clock64 timeline of CTA 0 of the fused env-step kernel (debug aid; flyb_debug_set_trace): env phase marks, MMA warp,
+epilogue warp 0 and the act finaliser, all relative to the kernel's entry.  python tools/step_trace.py [num_envs]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+import fly_bproject_b200 as fb  # noqa: E402
+from fly_bproject_b200 import _lib  # noqa: E402
+
+dev = "cuda:0"
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
+args = fb.make_args(num_envs=n, sim_device=dev, horizon=8, verbose=False, state_pool=8, seed=1)
+agent = fb.PPO(args)
+assert agent._fused_steps
+for _ in range(2):
+    agent.collect_rollout(use_graph=False)
+torch.cuda.synchronize()
+for rep in range(3):
+    trace = torch.zeros(192, dtype=torch.int64, device=dev)
+    _lib.check(agent.lib.flyb_debug_set_trace(trace.data_ptr()))
+    agent._fused_step(1 + rep)
+    torch.cuda.synchronize()
+    agent.lib.flyb_debug_set_trace(None)
+    t = trace.cpu().tolist()
+    t0 = t[190]
+    print(f"--- launch {rep}: kernel entry -> exit {t[191] - t0} cycles (thread 0 of CTA 0)")
+    print("env phase [entered, loads issued, tile staged, math done, reward+masks done]:", [x - t0 for x in t[172:190] if x > 0])
+    print("MMA warp   :", [x - t0 for x in t[:64] if x > 0])
+    print("epilogue w0:", [x - t0 for x in t[64:128] if x > 0])
+    print("finaliser  :", [x - t0 for x in t[128:160] if x > 0])
