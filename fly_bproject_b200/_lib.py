@@ -100,6 +100,8 @@ SIGNATURES = {
     "flyb_ppo_apply": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 5
                        + [C.c_float, _P, _P, _P, C.POINTER(PeerGroup), _P]),
     "flyb_ppo_step": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 8 + [C.c_int64] + [_P] * 8),
+    "flyb_ppo_step_dp": (C.c_int, [C.POINTER(NetLayout), C.POINTER(PpoCfg)] + [_P] * 8 + [C.c_int64] + [_P] * 5
+                         + [C.c_float, _P, _P, C.POINTER(PeerGroup), _P]),
     "flyb_peer_total_pad": (C.c_int32, [C.c_int32]),
     "flyb_peer_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "flyb_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), _P]),

@@ -14,6 +14,7 @@ data-parallel gradient sum itself is the library's own kernels over NVLink peer 
 from __future__ import annotations
 
 import ctypes as C
+import os
 from collections import OrderedDict
 from typing import Optional
 
@@ -230,6 +231,7 @@ class PPO:
         # data-parallel: one process per GPU, the only collective is the gradient all-reduce
         self.rank, self.world_size = dp.world()
         self._peers = None                  # dp.PeerExchange: gradient sum by the library's own kernels over NVLink
+        self._dp_tail = os.environ.get("FLYB_DP_TAIL", "0") == "1"      # exchange inside the weight-gradient kernel's tail
         if self.world_size > 1:
             dp.broadcast_params_(self.net.flat, src=0)
             self.net.repack()
@@ -418,6 +420,16 @@ class PPO:
                 p(self.adam_step), p(self.grad_norm), self._ws_ptr, stream), "flyb_ppo_step")
             return
         peers = self._peers.byref() if self._peers is not None else None
+        if peers is not None and self.net.wpack is not None and self._dp_tail:
+            # chain kernel + ONE cooperative launch: weight gradients, reduction, push / flags / rank-ordered sum over
+            # NVLink peer memory, norm, clip + Adam
+            _lib.check(self.lib.flyb_ppo_step_dp(
+                lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.net.wpack), p(self._obs_ring[k:j]),
+                p(self.all_acts[k:j]), p(self.all_log_prob[k:j]), p(self._target[k:j]), p(self.all_advantage[k:j]),
+                p(self.action_var), rows, p(self.grad), p(self.loss), p(self.exp_avg), p(self.exp_avg_sq),
+                p(self.adam_step), 1.0 / self.world_size, p(self.grad_norm), self._ws_ptr, peers, stream),
+                "flyb_ppo_step_dp")
+            return
         _lib.check(self.lib.flyb_ppo_grad(
             lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.net.wpack), p(self._obs_ring[k:j]), p(self.all_acts[k:j]),
             p(self.all_log_prob[k:j]), p(self._target[k:j]), p(self.all_advantage[k:j]), p(self.action_var), rows,

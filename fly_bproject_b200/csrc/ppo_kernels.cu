@@ -37,6 +37,7 @@ struct StepFuse {
   float *params, *exp_avg, *exp_avg_sq, *grad_norm_out;
   double lr, beta1, beta2, eps, max_norm;
   int done;   // out: 1 = the step was completed by the tail (no Adam launch needed)
+  float grad_scale;   // 1 / world when the tail also does the data-parallel exchange (peers != NULL), else 1
 };
 int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
                 const float* obs, const float* action, const float* old_logp, const float* target,
@@ -563,6 +564,36 @@ extern "C" int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, f
   FLYB_LAUNCH_CHECK("ppo_norm_kernel");
   return launch_adam(net, cfg, params, grad, exp_avg, exp_avg_sq, (const long long*)step, grad_scale, grad_norm_out,
                      norm_part, NORM_BLOCKS, wpack, peers, st);
+}
+
+extern "C" int flyb_ppo_step_dp(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack,
+                                const float* obs, const float* action, const float* old_logp, const float* target,
+                                const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
+                                float* exp_avg, float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out,
+                                void* workspace, const FlybPeerGroup* peers, void* stream) {
+  int rc = validate_net(net, params);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(cfg && wpack && peers && obs && action && old_logp && target && advantage && action_var && grad && loss &&
+                   exp_avg && exp_avg_sq && step && workspace,
+               "flyb_ppo_step_dp: NULL argument (it needs the tensor-core path and a peer group)");
+  FLYB_REQUIRE(rows > 0, "flyb_ppo_step_dp: rows must be > 0");
+  FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_step_dp: workspace must be 256-byte aligned");
+  FLYB_REQUIRE(tc_supported(net), "flyb_ppo_step_dp: the tensor-core path does not cover this shape");
+  if ((rc = peer_validate(peers, net->total)) != FLYB_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  StepFuse fuse{};
+  fuse.step = (long long*)step;
+  fuse.tail = 1;
+  fuse.params = params; fuse.exp_avg = exp_avg; fuse.exp_avg_sq = exp_avg_sq; fuse.grad_norm_out = grad_norm_out;
+  fuse.lr = cfg->lr; fuse.beta1 = cfg->beta1; fuse.beta2 = cfg->beta2; fuse.eps = cfg->eps; fuse.max_norm = cfg->max_grad_norm;
+  fuse.grad_scale = grad_scale;
+  rc = tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
+                   workspace, peers, st, &fuse);
+  if (rc != FLYB_OK) return rc;
+  if (fuse.done) return FLYB_OK;
+  // the weight-gradient grid does not fit one wave on this device: the split path (the reduce kernel has pushed)
+  return flyb_ppo_apply(net, cfg, params, grad, exp_avg, exp_avg_sq, step, grad_scale, grad_norm_out, workspace, wpack,
+                        peers, stream);
 }
 
 extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack,

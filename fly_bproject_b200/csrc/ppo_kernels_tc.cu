@@ -48,6 +48,7 @@ struct StepFuse {   // see ppo_kernels.cu
   float *params, *exp_avg, *exp_avg_sq, *grad_norm_out;
   double lr, beta1, beta2, eps, max_norm;
   int done;
+  float grad_scale;   // 1 / world when the tail also does the data-parallel exchange (peers != NULL), else 1
 };
 
 namespace tcb {
@@ -603,6 +604,8 @@ struct DwTail {
   AdamArgs adam;
   float* wpack;
   const int4* wpack_index;
+  int has_peers;            // data-parallel: the gradient exchange over NVLink peer memory happens in the tail too
+  PeerView pv;
 };
 __device__ unsigned g_dw_grid_sync[2];   // grid barrier state of the cooperative launch (count, generation)
 
@@ -930,6 +933,11 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
     __shared__ AdamCoef s_c;
     constexpr int TB = 512;                     // entries per block of work
     const int tid = threadIdx.x;
+    uint32_t epoch = 0;
+    if (t.has_peers) {
+      epoch = *(volatile const uint32_t*)t.pv.epoch;   // exchanges completed before this one (bumped at the very end)
+      if (blockIdx.x == 0 && tid == 0) t.pv.stamp[0] = global_ns();
+    }
     __threadfence();                            // this CTA's partial is written
     grid_barrier(g_dw_grid_sync, gridDim.x);
     float sq = 0.0f;
@@ -952,7 +960,28 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         }
         const float g = (acc[0] + acc[1]) + (acc[2] + acc[3]);
         t.grad[i] = g;
-        sq = fmaf(g, g, sq);
+        if (t.has_peers) peer_push(t.pv, epoch & 1u, i, g);   // posted NVLink stores + system fence of the writer
+        else sq = fmaf(g, g, sq);
+      }
+    }
+    if (t.has_peers) {
+      // every push of this rank is fenced -> raise this rank's flag everywhere, wait for everybody's, add the slots in
+      // rank order (bit-identical on every rank)
+      grid_barrier(g_dw_grid_sync, gridDim.x);
+      if (blockIdx.x == 0) {
+        if (tid == 0) t.pv.stamp[3] = global_ns();
+        peer_raise_flags(t.pv, epoch + 1u);
+      }
+      peer_wait_all(t.pv, epoch + 1u);
+      if (blockIdx.x == 0 && tid == 0) t.pv.stamp[4] = global_ns();
+      for (int base = blockIdx.x * TB; base < t.total; base += gridDim.x * TB) {
+        const int i = base + tid;
+        if (tid < TB && i < t.total) {
+          const float g = peer_sum(t.pv, epoch & 1u, i);
+          t.grad[i] = g;
+          const float gs = g * t.adam.scale;
+          sq = fmaf(gs, gs, sq);
+        }
       }
     }
     sq = warp_sum(sq);
@@ -983,6 +1012,10 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
       if (lane == 0) {
         s_c = adam_coefficients(t.adam, tot, *(volatile long long*)t.step);
         if (blockIdx.x == 0 && t.grad_norm_out) *t.grad_norm_out = s_c.total_norm;
+        if (blockIdx.x == 0 && t.has_peers) {
+          *t.pv.epoch = epoch + 1u;   // this exchange is over (every CTA read the old value before the first barrier)
+          t.pv.stamp[5] = global_ns();
+        }
       }
     }
     __syncthreads();
@@ -1150,7 +1183,7 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel), smem2)) != FLYB_OK) return rc;
   const int A = net->num_act;
   const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
-  if (fuse && fuse->tail && !peers && 2 * w.ctas_per_role <= num_sms()) {
+  if (fuse && fuse->tail && 2 * w.ctas_per_role <= num_sms()) {
     // flyb_ppo_step: reduction + clip + Adam in this kernel's tail, behind grid barriers -> cooperative launch
     DwTail& t = d.tail;
     t.enabled = 1;
@@ -1158,7 +1191,11 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
     t.total = net->total; t.nparts = w.ctas_per_role; t.nloss = w.grid1; t.inv_rows = ga.inv_rows;
     t.loss_part = w.loss_part; t.loss = loss; t.grad = grad; t.sq_part = w.sq_part; t.step = fuse->step;
     t.params = fuse->params; t.exp_avg = fuse->exp_avg; t.exp_avg_sq = fuse->exp_avg_sq; t.grad_norm_out = fuse->grad_norm_out;
-    t.adam = AdamArgs{fuse->lr, fuse->beta1, fuse->beta2, fuse->eps, fuse->max_norm, 1.0f};
+    t.adam = AdamArgs{fuse->lr, fuse->beta1, fuse->beta2, fuse->eps, fuse->max_norm, peers ? fuse->grad_scale : 1.0f};
+    if (peers) {
+      t.has_peers = 1;
+      t.pv = make_peer_view(*peers);
+    }
     t.wpack = (float*)const_cast<void*>(wpack);
     t.wpack_index = (const int4*)tc_wpack_index(net, wpack);
     void* kargs[] = {(void*)&d};

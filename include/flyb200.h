@@ -305,13 +305,26 @@ int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* param
                    void* wpack, const FlybPeerGroup* peers, void* stream);
 /* Single-GPU optimiser step in one call: flyb_ppo_grad followed by flyb_ppo_apply(grad_scale = 1) with nothing in
  * between, which lets the library drop two launches: the gradient reduction also takes the squared norm and counts
- * the step, and the Adam kernel refreshes `wpack` in place through the index flyb_pack_weights built (4 launches:
- * forward/backward chain, weight gradients, reduce, clip + Adam).  Same results as the two calls up to the
- * association of the norm's partial sums.  `grad` ends as p.grad after clipping, as with flyb_ppo_apply. */
+ * the step, and Adam refreshes `wpack` in place through the index flyb_pack_weights built.  On the tensor-core path
+ * the whole step is TWO launches: the forward/backward chain, and the weight-gradient kernel whose tail — behind grid
+ * barriers, the kernel is launched cooperatively — sums the per-CTA partials in the fixed order of the stand-alone
+ * reduction (bit-identical gradient), takes the norm and runs clip + Adam (FLYB_PPO_TAIL=0: the four-launch form).
+ * Same results as the two calls up to the association of the norm's partial sums.  `grad` ends as p.grad after
+ * clipping, as with flyb_ppo_apply. */
 int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack, const float* obs,
                   const float* action, const float* old_logp, const float* target, const float* advantage,
                   const float* action_var, int64_t rows, float* grad, float* loss, float* exp_avg, float* exp_avg_sq,
                   int64_t* step, float* grad_norm_out, void* workspace, void* stream);
+
+/* The same single call for a data-parallel run: flyb_ppo_grad + gradient sum over the peer group + flyb_ppo_apply in
+ * TWO launches — the weight-gradient kernel (launched cooperatively) reduces its partials behind a grid barrier, pushes
+ * the result to every rank, raises / waits for the flags, adds the slots in rank order, takes the norm and runs Adam.
+ * Same protocol and results as the two calls (FlybPeerGroup); needs the tensor-core path (wpack) and a peer group. */
+int flyb_ppo_step_dp(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack, const float* obs,
+                     const float* action, const float* old_logp, const float* target, const float* advantage,
+                     const float* action_var, int64_t rows, float* grad, float* loss, float* exp_avg, float* exp_avg_sq,
+                     int64_t* step, float grad_scale, float* grad_norm_out, void* workspace,
+                     const FlybPeerGroup* peers, void* stream);
 
 /* action_var <- max(floor, action_var - decay) (ppo.py:236-237), on the device so a captured graph can replay it;
  * step_counter (1, nullable) u64 += 1 (the Philox draw number of flyb_policy_act). */

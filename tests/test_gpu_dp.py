@@ -26,7 +26,8 @@ def _worker(rank, world, port, out, mode):
     import torch.distributed as dist
     import fly_bproject_b200 as fb
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
-    os.environ["FLYB_DP"] = mode
+    os.environ["FLYB_DP"] = "nccl" if mode == "nccl" else "peer"
+    os.environ["FLYB_DP_TAIL"] = "1" if mode == "peer_tail" else "0"
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{rank}"))
     try:
@@ -34,11 +35,12 @@ def _worker(rank, world, port, out, mode):
         args = fb.make_args(num_envs=2048, sim_device=f"cuda:{rank}", horizon=16, verbose=False, state_pool=4,
                             seed=1234)           # IDENTICAL args on every rank: the library decorrelates the shards
         agent = fb.PPO(args)
-        assert agent.world_size == world and (agent._peers is not None) == (mode == "peer")
+        assert agent.world_size == world and (agent._peers is not None) == (mode != "nccl")
+        assert agent._dp_tail == (mode == "peer_tail")
         agent.collect_rollout(use_graph=False)
         acts_sum, obs_sum = float(agent.all_acts.double().sum()), float(agent._obs_ring.double().sum())
-        for _ in range(2):      # peer mode: eager warm-up + capture, then a replay; NCCL mode: eager twice
-            agent.update(use_graph=(mode == "peer"))
+        for _ in range(2):      # peer modes: eager warm-up + capture, then a replay; NCCL mode: eager twice
+            agent.update(use_graph=(mode != "nccl"))
         torch.cuda.synchronize()
         torch.save({"flat": agent.net.flat.cpu(), "m": agent.exp_avg.cpu(), "v": agent.exp_avg_sq.cpu(),
                     "steps": agent.optim_step, "loss": float(agent.loss), "acts_sum": acts_sum, "obs_sum": obs_sum,
@@ -55,7 +57,7 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
         pytest.skip(f"needs {world} CUDA devices")
     out = str(tmp_path / "dp")
     res = {}
-    for mode in ("peer", "nccl"):
+    for mode in ("peer", "nccl", "peer_tail"):   # peer_tail: the exchange inside the weight-gradient kernel's tail
         mp.spawn(_worker, args=(world, _free_port(), out, mode), nprocs=world, join=True)
         rs = [torch.load(f"{out}.{mode}.{r}") for r in range(world)]
         for r in rs[1:]:
@@ -74,6 +76,8 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
     # more ranks: NCCL's tree / ring order differs from the rank order, and 150 Adam steps (each ~lr in size whatever
     # the gradient's magnitude) amplify the reassociation noise: only the bulk has to agree
     assert float((res["peer"]["flat"] - res["nccl"]["flat"]).abs().mean()) < 1e-3
+    # same sums in the same order; only the association of the norm's partial sums differs (an ulp in the clip coefficient)
+    assert float((res["peer_tail"]["flat"] - res["peer"]["flat"]).abs().mean()) < 1e-3
 
 
 def _soak_worker(rank, world, port, out, exchanges):
