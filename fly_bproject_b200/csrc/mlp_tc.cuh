@@ -241,7 +241,16 @@ struct FwdArgs {
   int O, A;
   size_t out_bytes;
   unsigned long long* trace;   // debug: clock64 timeline of CTA 0 (nullable; flyb_debug_set_trace)
+  // Final::kBuildsObs kernels only: a per-row block of `pre_row_bytes` bytes (the env's whole contact-force block) is
+  // bulk-copied for the CTA's first tile into the region that starts at the X planes (X | obs | out: all free until
+  // the observation rows are built), signalled on obs_full.  NULL / 0: nothing.
+  const float* pre_src = nullptr;
+  unsigned int pre_row_bytes = 0;
 };
+// bytes of the contiguous shared-memory region [X hi | X lo | obs stage | out staging]
+__host__ __device__ inline size_t build_region_bytes(int O, size_t out_bytes) {
+  return 2 * X_PLANE_BYTES + obs_stage_bytes(O) + ((out_bytes + 127) / 128 * 128);
+}
 
 // trace slots: [0,64) MMA warp, [64,128) epilogue warp 0 lane 0
 FLYB_D void trace_mark(unsigned long long* trace, int& idx, int limit) {
@@ -275,6 +284,14 @@ FLYB_D void producer_kickoff(const Smem& s, const FwdArgs& a, bool load_obs = tr
       if (load_obs && (bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
         tc::mbar_arrive_expect_tx(s.obs_full, bytes);
         tc::tma_load_1d(s.obs, src, bytes, s.obs_full);
+      }
+      if (!load_obs && a.pre_src != nullptr) {   // the first tile's contact-force blocks (see FwdArgs::pre_src)
+        const uint32_t pbytes = (uint32_t)nrows * a.pre_row_bytes;
+        if ((pbytes & 15u) == 0) {
+          tc::mbar_arrive_expect_tx(s.obs_full, pbytes);
+          tc::tma_load_1d(s.xhi, reinterpret_cast<const char*>(a.pre_src) + (size_t)row0 * a.pre_row_bytes, pbytes,
+                          s.obs_full);
+        }
       }
       for (int i = 0; i < NST; ++i) {
         tc::mbar_arrive_expect_tx(&s.full[i], STAGE);

@@ -6,6 +6,7 @@
 // Also here: flyb_pack_weights, which rewrites the flat fp32 parameters as the packed hi/lo weight stream the
 // TMA producer reads (consumption order, 4 KB stages — layout in mlp_tc.cuh).
 #include <algorithm>
+#include <cstdlib>
 
 #include "env_math.cuh"
 #include "env_scan.cuh"
@@ -421,6 +422,7 @@ constexpr int STEP_AUX_WARP = tcm::THREADS / 32;
 constexpr int STEP_AUX_BAR_THREADS = tcm::EPI_THREADS + 32;
 constexpr size_t STEP_ENV_STAGE_BYTES = (size_t)tcm::TM * (13 + FORCE_VALS + 2) * 4;   // root, force rows, two scalars
 
+FLYB_D void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 FLYB_D float4 ld_global4(const float4* p) {   // coherent 128-bit load (the same kernel later rewrites reset rows)
   float4 v;
   asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
@@ -436,6 +438,13 @@ struct StepFinal : ActFinal {
   StepTables* st;
   bool tables_built;
   unsigned parity;
+  // contact forces by bulk copy: the tile's 128 contiguous force blocks (128 x B x 12 bytes) land in the X | obs | out
+  // region, free until the rows are built, and the 33 values an env needs are picked out of shared memory.  The gather
+  // of 11-of-93 rows through the LSU touches ~940 of an env's 1116 bytes in DRAM anyway (64-byte access granularity)
+  // and is bound by the SM's outstanding-miss limit; one sequential copy streams at the HBM rate.
+  int force_bulk;          // 0: gather through the LSU
+  unsigned force_phase;    // phase of s.obs_full
+  bool first_tile;
 
   int tb_;   // next env-phase trace slot (172..189), thread 0 of CTA 0
   FLYB_D void emark() {
@@ -472,6 +481,14 @@ struct StepFinal : ActFinal {
     const int en = tid >> 1, qd = tid & 1;             // two threads per env for the gathers
     const bool e_ok = en < nrows;
     const long long env = row0 + en;
+    const unsigned fbytes = (unsigned)nrows * (unsigned)B * 12u;
+    const bool bulk = force_bulk != 0 && (fbytes & 15u) == 0u;
+    if (bulk && !first_tile && tid == 0) {             // (the first tile's copy was issued at kernel entry)
+      tc::fence_proxy_async();
+      tc::mbar_arrive_expect_tx(s.obs_full, fbytes);
+      tc::tma_load_1d(s.xhi, reinterpret_cast<const char*>(e.force) + (size_t)row0 * B * 12, fbytes, s.obs_full);
+    }
+    first_tile = false;
     const int nroot = nrows * 13;
     const float4* root4 = reinterpret_cast<const float4*>(root + (size_t)row0 * 13);   // row0 % 128 == 0: 16-byte aligned
     float4 r4[2];
@@ -493,7 +510,7 @@ struct StepFinal : ActFinal {
     }
     constexpr int FITER = (FORCE_VALS + 1) / 2;   // 17
     float fv[FITER];
-    {
+    if (!bulk) {
       const float* fe = e.force + (size_t)env * B * 3;
 #pragma unroll
       for (int it = 0; it < FITER; ++it) {
@@ -519,6 +536,17 @@ struct StepFinal : ActFinal {
       }
     }
     emark();   // [1] every load issued
+    if (bulk) {   // the force blocks have landed: pick this env's 33 values, then hand the region back
+      tc::mbar_wait(s.obs_full, force_phase);
+      force_phase ^= 1u;
+      const float* fe = s.xhi + (size_t)en * B * 3;     // block stride 279 words: odd, so conflict-free across envs
+#pragma unroll
+      for (int it = 0; it < FITER; ++it) {
+        const int rc = qd + 2 * it;
+        fv[it] = (e_ok && rc < FORCE_VALS) ? fe[st->foff[rc]] : 0.0f;
+      }
+      tcm::epi_bar_sync();
+    }
     // ---- stage: obs[12 : 12+3A] (fly.py:795, 801, 802), root rows, gathered contact rows
     {
       float* oe = obs_s + en * O + 12;
@@ -658,6 +686,32 @@ struct StepFinal : ActFinal {
     tcm::epi_bar_sync();
     asm volatile("bar.arrive 3, %0;" ::"n"(STEP_AUX_BAR_THREADS) : "memory");   // masks are in shared memory: wake the spare warp
     parity ^= 1u;
+    // ---- the CTA's NEXT tile (persistent loop, N > 128 x CTAs): pull its state lines into L2 now, so that the DRAM
+    //      latency of its gathers is paid under this tile's MMAs.  Same addresses, same thread mapping as above.
+    {
+      const long long next0 = row0 + (long long)gridDim.x * TM;
+      const long long nenv = c.num_envs;
+      if (next0 + en < nenv) {
+        const long long nx = next0 + en;
+        const float* fe = e.force + (size_t)nx * B * 3;
+#pragma unroll
+        for (int it = 0; it < FITER; ++it) {
+          const int rc = qd + 2 * it;
+          if (rc < FORCE_VALS && (rc % 3) == 0) prefetch_l2(fe + st->foff[rc]);   // one touch per gathered row
+        }
+        if (qd == 0) {
+          const char* dp = reinterpret_cast<const char*>(reinterpret_cast<const float2*>(dof_state) + (size_t)nx * D);
+          for (int b = 0; b < D * 8; b += 128) prefetch_l2(dp + b);
+          prefetch_l2(root + (size_t)nx * 13);
+        } else {
+          const char* ap = reinterpret_cast<const char*>(actions_scaled + (size_t)nx * A);
+          for (int b = 0; b < A * 4; b += 128) prefetch_l2(ap + b);
+          prefetch_l2(potentials + nx);
+          prefetch_l2(progress + nx);
+          prefetch_l2(reset + nx);
+        }
+      }
+    }
     emark();   // [4] reward + masks done, rows visible to the bulk stores
   }
 
@@ -771,6 +825,7 @@ env_step_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_const
   fin.t = &tab; fin.tw = &tab; fin.action_var = x.action_var; fin.rst_raw = 0; fin.trace = a.trace; fin.ti = 128;
   fin.anneal_steps = y.anneal_steps; fin.anneal_decay = y.anneal_decay; fin.anneal_floor = y.anneal_floor;
   fin.e = y.env; fin.st = &stab; fin.tables_built = false; fin.parity = 0u; fin.tb_ = 172;
+  fin.force_bulk = a.pre_src != nullptr ? 1 : 0; fin.force_phase = 0u; fin.first_tile = true;
   if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[190] = clock64();   // kernel entry
   tcm::forward_persistent<true, false>(net, a, fin);
   if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[191] = clock64();       // kernel exit
@@ -881,6 +936,12 @@ int tc_launch_step(const FlybNetLayout* net, const float* params, const void* wp
   const size_t out = std::max((size_t)tcm::TM * 3 * net->num_act * 4, STEP_ENV_STAGE_BYTES);
   const long long rows = cfg->num_envs;
   tcm::FwdArgs a{nullptr, (const unsigned char*)wpack, params, rows, net->num_obs, net->num_act, out, g_trace};
+  static const bool no_bulk = [] { const char* ev = getenv("FLYB_STEP_FORCE_BULK"); return ev && ev[0] == '0'; }();
+  const size_t block = (size_t)cfg->num_bodies * 12;
+  if (!no_bulk && (size_t)tcm::TM * block <= tcm::build_region_bytes(net->num_obs, out) && aligned16(io->force)) {
+    a.pre_src = io->force;
+    a.pre_row_bytes = (unsigned)block;
+  }
   StepTcArgs y{};
   ActTcArgs& x = y.act;
   x.action_var = io->action_var; x.noise = io->noise; x.seed = io->seed; x.offset = io->offset;
