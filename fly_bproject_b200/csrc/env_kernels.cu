@@ -14,8 +14,11 @@
 //   * reset ids are compacted in ascending order (== torch.nonzero) inside the same launch: warp ballot ->
 //     one 64-bit mask per CTA -> the last CTA to finish scans the bitmap and writes the id list; the count
 //     stays on the device — the reference's host sync at fly.py:447-450 is gone.
+#include <cstdlib>
+
 #include "env_math.cuh"
 #include "env_scan.cuh"
+#include "tc_common.cuh"
 
 namespace flyb {
 unsigned long long* tc_get_trace();
@@ -39,7 +42,8 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
                     float* __restrict__ up_vec, float* __restrict__ heading_vec, int* __restrict__ reset_ids,
                     int* __restrict__ reset_count, ScanScratch* __restrict__ scratch, float* __restrict__ obs_copy,
                     float* __restrict__ reward_copy, float* __restrict__ reward_sum,
-                    const __grid_constant__ FlybStepTail tail, unsigned long long* __restrict__ trace) {
+                    const __grid_constant__ FlybStepTail tail, unsigned long long* __restrict__ trace,
+                    const int force_bulk) {
   // debug (flyb_debug_set_trace): thread 0 of CTA 0 marks [160..]: entry, loads issued, loads consumed, per-env math
   // done, reward + masks done, mask published, obs slab out (clock64 is per SM: marks of other CTAs would not compare)
   int tmark = 160;
@@ -53,6 +57,12 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   float* obs_s = smem;                        // [ENVS][O]      (O is odd -> conflict-free row access)
   float* root_s = obs_s + ENVS * O;           // [ENVS][13]
   float* force_s = root_s + ENVS * 13;        // [ENVS][33]
+  // force_bulk: the CTA's 64 contiguous contact-force blocks (64 x B x 12 bytes) arrive as ONE bulk copy and the 33
+  // values an env needs are picked out of shared memory.  Gathering 11 of 93 rows through the LSU touches ~940 of an
+  // env's 1116 bytes in DRAM anyway (64-byte access granularity) and runs at the SM's outstanding-miss limit
+  // (~1.5 TB/s machine-wide, measured); the sequential copy streams at the HBM rate.
+  float* force_blk = force_s + ENVS * FORCE_VALS + (ENVS * (O + 13 + FORCE_VALS) & 3 ? 4 - (ENVS * (O + 13 + FORCE_VALS) & 3) : 0);
+  __shared__ __align__(8) uint64_t s_fbar;
   __shared__ unsigned s_mask[ENVS / 32];
   __shared__ int s_cnt[ENVS];                 // role 3 -> role 0: legs | at_limit << 8 | abdomen_hit << 16
   __shared__ float s_sq[ENVS];
@@ -71,6 +81,14 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   static_assert(PP_THREADS == 4 * ENVS, "four threads per env");
   const int e = tid >> 2, qd = tid & 3;
   const bool e_ok = e < nenv;
+  const unsigned fbytes = (unsigned)nenv * (unsigned)B * 12u;
+  const bool bulk = force_bulk != 0 && (fbytes & 15u) == 0u;   // 64 x 1116 bytes per full CTA: a multiple of 16
+  if (bulk && tid == 0) {
+    tc::mbar_init(&s_fbar, 1);
+    tc::fence_mbar_init();
+    tc::mbar_arrive_expect_tx(&s_fbar, fbytes);
+    tc::tma_load_1d(force_blk, reinterpret_cast<const char*>(force) + (size_t)env0 * B * 12, fbytes, &s_fbar);
+  }
 
   // ---- loads, wave 1: root slab (contiguous nenv*13 floats; 16B aligned since ENVS*52 % 16 == 0), per-env scalars
   constexpr int ROOT4 = ENVS * 13 / 4;        // 208 <= PP_THREADS
@@ -100,7 +118,7 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
   // ---- wave 2: the 11 gathered contact-force rows of this thread's env, values rc = qd, qd + 4, ...
   constexpr int FITER = (FORCE_VALS + 3) / 4;   // 9
   float fv[FITER];
-  {
+  if (!bulk) {
     const float* fe = force + (size_t)(env0 + e) * B * 3;
 #pragma unroll
     for (int it = 0; it < FITER; ++it) {
@@ -140,6 +158,15 @@ post_physics_kernel(const __grid_constant__ FlybEnvCfg cfg, const float* __restr
     }
   }
   mark();   // every load of this thread has been issued; the first dependent use follows
+  if (bulk) {
+    tc::mbar_wait(&s_fbar, 0u);
+    const float* fe = force_blk + (size_t)e * B * 3;   // block stride B * 3 = 279 words: odd, conflict-free across envs
+#pragma unroll
+    for (int it = 0; it < FITER; ++it) {
+      const int rc = qd + 4 * it;
+      fv[it] = (e_ok && rc < FORCE_VALS) ? fe[s_foff[rc]] : 0.0f;
+    }
+  }
   if (tid * 4 + 3 < nroot) reinterpret_cast<float4*>(root_s)[tid] = r4;
   for (int i = (nroot & ~3) + tid; i < nroot; i += PP_THREADS) root_s[i] = __ldg(root + (size_t)env0 * 13 + i);
 #pragma unroll
@@ -435,7 +462,12 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
   FLYB_REQUIRE(aligned16(root) && aligned16(obs) && aligned16(dof_state),
                "flyb_env_post_physics: root/dof_state/obs must be 16-byte aligned");
   const int O = 19 + 3 * cfg->num_act;
-  const size_t smem = (size_t)ENVS * (O + 13 + FORCE_VALS) * sizeof(float);
+  size_t smem = ((size_t)ENVS * (O + 13 + FORCE_VALS) * sizeof(float) + 15) / 16 * 16;
+  // bulk-copied force blocks: worth it while at least two CTAs still fit an SM
+  static const bool no_bulk = [] { const char* ev = getenv("FLYB_ENV_FORCE_BULK"); return ev && ev[0] == '0'; }();
+  const size_t fblk = (size_t)ENVS * cfg->num_bodies * 12;
+  const int force_bulk = (!no_bulk && aligned16(force) && fblk % 16 == 0 && smem + fblk <= 110 * 1024) ? 1 : 0;
+  if (force_bulk) smem += fblk;
   rc = ensure_smem(reinterpret_cast<const void*>(post_physics_kernel), smem);
   if (rc != FLYB_OK) return rc;
   const int grid = (cfg->num_envs + ENVS - 1) / ENVS;
@@ -447,7 +479,7 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
   post_physics_kernel<<<grid, PP_THREADS, smem, (cudaStream_t)stream>>>(
       *cfg, root, dof_state, force, actions_scaled, potentials, prev_potentials, (long long*)progress,
       (long long*)reset, obs, reward, up_vec, heading_vec, reset_ids, reset_count, (ScanScratch*)scratch, obs_copy,
-      reward_copy, reward_sum, t, tc_get_trace());
+      reward_copy, reward_sum, t, tc_get_trace(), force_bulk);
   FLYB_LAUNCH_CHECK("post_physics_kernel");
   return FLYB_OK;
 }

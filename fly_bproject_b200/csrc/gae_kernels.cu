@@ -110,8 +110,10 @@ extern "C" int flyb_gae(const float* reward, const float* values, const int64_t*
   FLYB_REQUIRE(horizon > 0 && num_envs > 0, "flyb_gae: horizon and num_envs must be > 0");
   // gamma * lmbda is formed in double then rounded, as Python does for `self.gamma * self.lmbda` (ppo.py:167)
   const float gl = (float)((double)gamma * (double)lmbda);
-  const bool vec = (num_envs % 4 == 0) && aligned16(reward) && aligned16(values) && aligned16(target) &&
-                   aligned16(advantage) && aligned16(reset_last);
+  // measured at configs[1] (16384 envs x 32): 4.3 us scalar vs 8.2 us vectorised — with a quarter of the threads the
+  // scan is latency-bound; the vector kernel takes over once N / 4 threads still fill the 148 SMs
+  const bool vec = (num_envs % 4 == 0) && num_envs >= 4 * 148 * 256 && aligned16(reward) && aligned16(values) &&
+                   aligned16(target) && aligned16(advantage) && aligned16(reset_last);
   if (vec) {
     gae_scan4_kernel<<<(num_envs / 4 + 63) / 64, 64, 0, (cudaStream_t)stream>>>(
         reward, values, (const long long*)reset_last, horizon, num_envs, gamma, gl, target, advantage);

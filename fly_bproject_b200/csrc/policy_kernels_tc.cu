@@ -578,9 +578,10 @@ struct StepFinal : ActFinal {
     //      up projections, later reward + termination; 1: local velocities; 2: Euler angles; 3: contact flags, sums
     const int role = warp >> 1;
     const int me0 = ((warp & 1) << 5) | lane;
+    // (the two passes stay rolled: this code runs once per launch, every instruction-cache line it spans is a miss)
     float k_hproj[2], k_pot[2], k_h[2], k_qz[2], k_qw[2];
     Vec3 k_up[2], k_head[2];
-#pragma unroll
+#pragma unroll 1
     for (int p = 0; p < 2; ++p) {
       const int me = p * 64 + me0;
       const bool me_ok = me < nrows;
@@ -594,8 +595,13 @@ struct StepFinal : ActFinal {
       if (role == 0) {
         env_head_heading(r, c, tq, h);
         if (me_ok) { o[10] = h.up_proj; o[11] = h.heading_proj; }
-        k_hproj[p] = h.heading_proj; k_pot[p] = h.potential; k_h[p] = r[2]; k_qz[p] = r[5]; k_qw[p] = r[6];
-        k_up[p] = h.up_vec; k_head[p] = h.heading_vec;
+        if (p == 0) {
+          k_hproj[0] = h.heading_proj; k_pot[0] = h.potential; k_h[0] = r[2]; k_qz[0] = r[5]; k_qw[0] = r[6];
+          k_up[0] = h.up_vec; k_head[0] = h.heading_vec;
+        } else {
+          k_hproj[1] = h.heading_proj; k_pot[1] = h.potential; k_h[1] = r[2]; k_qz[1] = r[5]; k_qw[1] = r[6];
+          k_up[1] = h.up_vec; k_head[1] = h.heading_vec;
+        }
       } else if (role == 1) {
         env_head_vel(r, tq, h);
         if (me_ok) {
@@ -635,11 +641,16 @@ struct StepFinal : ActFinal {
     emark();   // [3] per-env math done
     if (role == 0) {
       float my_reward = 0.0f;
-#pragma unroll
+#pragma unroll 1
       for (int p = 0; p < 2; ++p) {
         const int me = p * 64 + me0;
         const bool me_ok = me < nrows;
         bool flag = false;
+        // (static register indexing: select after reading both)
+        const float s_h = p ? k_h[1] : k_h[0], s_hproj = p ? k_hproj[1] : k_hproj[0], s_qz = p ? k_qz[1] : k_qz[0];
+        const float s_qw = p ? k_qw[1] : k_qw[0], s_pot = p ? k_pot[1] : k_pot[0], s_potin = p ? pot_in[1] : pot_in[0];
+        const long long s_prog = p ? prog_in[1] : prog_in[0], s_rst = p ? reset_in[1] : reset_in[0];
+        const Vec3 s_up = p ? k_up[1] : k_up[0], s_head = p ? k_head[1] : k_head[0];
         if (me_ok) {
           const long long gi = row0 + me;
           const int packed = cnt_s[me];
@@ -647,31 +658,31 @@ struct StepFinal : ActFinal {
           in.actions_sq_sum = sq_s[me];
           in.electricity = 0.0f;
           in.at_limit = (packed >> 8) & 0xff;
-          in.height = k_h[p];
-          in.heading_proj = k_hproj[p];
-          in.qz = k_qz[p];
-          in.qw = k_qw[p];
-          in.prev_potential = pot_in[p];    // fly.py:780
-          in.potential = k_pot[p];
+          in.height = s_h;
+          in.heading_proj = s_hproj;
+          in.qz = s_qz;
+          in.qw = s_qw;
+          in.prev_potential = s_potin;      // fly.py:780
+          in.potential = s_pot;
           in.legs_touching = packed & 0xff;
           in.abdomen_hit = (packed >> 16) != 0;
-          long long prog = prog_in[p] + 1;  // fly.py:678
+          long long prog = s_prog + 1;      // fly.py:678
           if (prog == 0) prog = 1;          // fly.py:415-416
           in.progress = prog;
-          in.reset_prev = reset_in[p];
+          in.reset_prev = s_rst;
           float rew;
           long long rst;
           env_reward_reset(in, c, &rew, &rst);
-          potentials[gi] = k_pot[p];
-          prev_potentials[gi] = pot_in[p];
+          potentials[gi] = s_pot;
+          prev_potentials[gi] = s_potin;
           progress[gi] = prog;
           reset[gi] = rst;                  // read back by this tile's act half (begin_tile), behind the barrier below
           e.reward[gi] = rew;
           if (e.reward_ring) e.reward_ring[gi] = rew;
           my_reward += rew;
-          e.up_vec[gi * 3 + 0] = k_up[p].x; e.up_vec[gi * 3 + 1] = k_up[p].y; e.up_vec[gi * 3 + 2] = k_up[p].z;
-          e.heading_vec[gi * 3 + 0] = k_head[p].x; e.heading_vec[gi * 3 + 1] = k_head[p].y;
-          e.heading_vec[gi * 3 + 2] = k_head[p].z;
+          e.up_vec[gi * 3 + 0] = s_up.x; e.up_vec[gi * 3 + 1] = s_up.y; e.up_vec[gi * 3 + 2] = s_up.z;
+          e.heading_vec[gi * 3 + 0] = s_head.x; e.heading_vec[gi * 3 + 1] = s_head.y;
+          e.heading_vec[gi * 3 + 2] = s_head.z;
           flag = rst != 0;
         }
         const unsigned ballot = __ballot_sync(0xffffffffu, flag);

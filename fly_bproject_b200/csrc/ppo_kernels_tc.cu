@@ -951,12 +951,21 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         if (valid) {
           const float* src = a.dw_part + i;
           int p = 0;
+          for (; p + 16 <= t.nparts; p += 16) {   // 16 loads in flight; each group still adds its partials in order
+            float v[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v[u] = __ldcg(src + (size_t)(p + u) * t.total);
+#pragma unroll
+            for (int u = 0; u < 16; ++u) acc[u & 3] += v[u];
+          }
           for (; p + 4 <= t.nparts; p += 4) {
             const float v0 = __ldcg(src + (size_t)p * t.total), v1 = __ldcg(src + (size_t)(p + 1) * t.total);
             const float v2 = __ldcg(src + (size_t)(p + 2) * t.total), v3 = __ldcg(src + (size_t)(p + 3) * t.total);
             acc[0] += v0; acc[1] += v1; acc[2] += v2; acc[3] += v3;
           }
-          for (; p < t.nparts; ++p) acc[p & 3] += __ldcg(src + (size_t)p * t.total);
+          if (p < t.nparts) acc[0] += __ldcg(src + (size_t)p * t.total);
+          if (p + 1 < t.nparts) acc[1] += __ldcg(src + (size_t)(p + 1) * t.total);
+          if (p + 2 < t.nparts) acc[2] += __ldcg(src + (size_t)(p + 2) * t.total);
         }
         const float g = (acc[0] + acc[1]) + (acc[2] + acc[3]);
         t.grad[i] = g;

@@ -15,6 +15,10 @@ This is a CLOSED loop: the observation's commanded-action slots and the DOF targ
 (held to 1e-5 relative / 2e-6 absolute in [-1, 1]) scaled to the joint range, whose half-width reaches 5.4 rad
 (joint_LHTibia, assets/nmf_no_limits_limited_Dofs.urdf:227) — those entries therefore carry an absolute floor of
 2e-6 x 5.4 ~ 1.1e-5, taken as 2e-5 here; every other entry keeps the open-loop bar of test_gpu_env.py.
+The reward's joints-at-limit term is a STEP function of those commanded actions (cmd > 0.9 * upper, fly.py:736-737):
+an action within its 2e-6 tolerance of a threshold may count one limit more or less, i.e. the reward moves by exactly
+joints_at_limit_cost_scale = 0.1.  Such flips are allowed for at most 1e-5 of the rewards of a rollout (observed: 1-2
+in 0.6-2 million) and must be whole multiples of 0.1; everything else is held to 1e-5.
 """
 import pytest
 import torch
@@ -82,12 +86,19 @@ def test_whole_config_rollout_gae_and_one_minibatch_step(asset, full, walking, n
             torch.testing.assert_close(agent.all_log_prob[i].cpu(), logp, rtol=1e-5, atol=1e-4)
             assert_obs_close(env.obs_buf.cpu(), s.obs_buf, a_dim, atol=SCALED_ACTION_ATOL)
             torch.testing.assert_close(env.dof_targets.cpu(), targets, rtol=1e-5, atol=SCALED_ACTION_ATOL)
-            torch.testing.assert_close(env.reward_buf.cpu(), s.reward_buf, rtol=RTOL_ENV,
-                                       atol=0.016 if walking else ATOL_ENV)
+            rerr = (env.reward_buf.cpu() - s.reward_buf).abs()
+            roff = rerr > (0.016 if walking else ATOL_ENV) + RTOL_ENV * s.reward_buf.abs()
+            assert int(roff.sum()) <= max(1, n // 100000), f"{int(roff.sum())} rewards off at step {i}"
     ring[horizon] = s.obs_buf
     torch.cuda.synchronize()
     torch.testing.assert_close(agent.action_var.cpu(), var, rtol=1e-6, atol=0)
-    torch.testing.assert_close(agent.all_reward.cpu(), rews, rtol=RTOL_ENV, atol=0.016 if walking else ATOL_ENV)
+    got_rew = agent.all_reward.cpu()
+    err = (got_rew - rews).abs()
+    off = err > (0.016 if walking else ATOL_ENV) + RTOL_ENV * rews.abs()
+    assert float(off.float().mean()) <= 1e-5, f"{int(off.sum())} rewards off"
+    if off.any():      # threshold flips of the joints-at-limit count: whole multiples of 0.1
+        steps = err[off] / 0.1
+        assert float((steps - steps.round()).abs().max()) < (0.2 if walking else 1e-3) and float(steps.round().min()) >= 1.0
 
     # ---- GAE over the whole rollout (ppo.py:157-171), on the ORACLE's buffers so that the comparison is of the scan
     #      and the value forward, not of accumulated rollout differences
