@@ -220,10 +220,17 @@ class PPO:
         self._decay, self._floor = (0.0, 0.0) if testing else (0.00001, 0.01)             # ppo.py:236-237
         self._tail = _lib.StepTail(self.action_var.data_ptr(), a, self._decay, self._floor, self._rng_counter.data_ptr(), 1)
         # one launch per env step inside collect_rollout (flyb_env_step_fused): tensor-core path, standard step order
-        self._fused_steps = bool(
+        # Default: where every 128-env tile has an SM of its own (N <= 128 x SMs).  Beyond that the fused CTAs run their
+        # tiles' env and MLP phases back to back while the two-kernel schedule spreads the env phase over the whole
+        # machine (measured, profiles/r02d_sweep_*: 34.9 vs 35.5 us per env step at 16384 envs, 82.9 vs 62.5 at 32768).
+        fused_ok = bool(
             self._fused_env and self.net.wpack is not None and not self.env.reset_after_simulate
-            and _get(args, "fused_steps", True)
             and self.lib.flyb_env_step_fused_supported(C.byref(self.net.layout), C.byref(self.env.cfg)))
+        want = _get(args, "fused_steps", None)
+        if want is None:
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            want = (n + 127) // 128 <= sms
+        self._fused_steps = bool(fused_ok and want)
         self._graphs = {}
         if resume_state is not None:
             self._restore(resume_state)

@@ -463,10 +463,12 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
                "flyb_env_post_physics: root/dof_state/obs must be 16-byte aligned");
   const int O = 19 + 3 * cfg->num_act;
   size_t smem = ((size_t)ENVS * (O + 13 + FORCE_VALS) * sizeof(float) + 15) / 16 * 16;
-  // bulk-copied force blocks: worth it while at least two CTAs still fit an SM
-  static const bool no_bulk = [] { const char* ev = getenv("FLYB_ENV_FORCE_BULK"); return ev && ev[0] == '0'; }();
+  // bulk-copied force blocks: measured SLOWER here than the gather (26.1 vs 21.9 us at 16384 envs, profiles/r02e): the
+  // kernel's 256 small CTAs hide the gather's latency by occupancy, and 101 KB of shared memory per CTA takes that away.
+  // In the fused step (one big CTA per SM, nothing to overlap with) the same copy wins.  Opt-in: FLYB_ENV_FORCE_BULK=1.
+  static const bool want_bulk = [] { const char* ev = getenv("FLYB_ENV_FORCE_BULK"); return ev && ev[0] == '1'; }();
   const size_t fblk = (size_t)ENVS * cfg->num_bodies * 12;
-  const int force_bulk = (!no_bulk && aligned16(force) && fblk % 16 == 0 && smem + fblk <= 110 * 1024) ? 1 : 0;
+  const int force_bulk = (want_bulk && aligned16(force) && fblk % 16 == 0 && smem + fblk <= 110 * 1024) ? 1 : 0;
   if (force_bulk) smem += fblk;
   rc = ensure_smem(reinterpret_cast<const void*>(post_physics_kernel), smem);
   if (rc != FLYB_OK) return rc;

@@ -518,21 +518,30 @@ struct StepFinal : ActFinal {
         fv[it] = (e_ok && rc < FORCE_VALS) ? __ldg(fe + st->foff[rc]) : 0.0f;
       }
     }
-    constexpr int DU = 10;                        // A <= 20 on this path (O = 19 + 3A <= 80)
+    // DOF pairs / commanded actions: the tile's pairs as ONE flat array, element f = (env f / A, action f % A) — a warp
+    // reads 32 consecutive (or, with a partial actuation, nearly consecutive) pairs: coalesced, a handful of lines per
+    // instruction instead of one line per lane
+    constexpr int DU = 10;                        // ceil(128 x 20 / 256): A <= 20 on this path (O = 19 + 3A <= 80)
     float2 pv[DU];
     float cmd[DU];
+    const int npairs = nrows * A;
+    const int el_step = tcm::EPI_THREADS / A, k_step = tcm::EPI_THREADS % A;
     {
-      const float2* de = reinterpret_cast<const float2*>(dof_state) + (size_t)env * D;
-      const float* ae = actions_scaled + (size_t)env * A;
+      const float2* de = reinterpret_cast<const float2*>(dof_state) + (size_t)row0 * D;
+      const float* ae = actions_scaled + (size_t)row0 * A;
+      int el = tid / A, k = tid - el * A;
 #pragma unroll
       for (int u = 0; u < DU; ++u) {
-        const int k = qd + 2 * u;
+        const int f = tid + tcm::EPI_THREADS * u;
         pv[u] = make_float2(0.f, 0.f);
         cmd[u] = 0.0f;
-        if (e_ok && k < A) {
-          pv[u] = de[st->aidx[k]];
-          cmd[u] = ae[k];
+        if (f < npairs) {
+          pv[u] = de[el * D + st->aidx[k]];
+          cmd[u] = ae[f];
         }
+        el += el_step;
+        k += k_step;
+        if (k >= A) { k -= A; ++el; }
       }
     }
     emark();   // [1] every load issued
@@ -549,15 +558,19 @@ struct StepFinal : ActFinal {
     }
     // ---- stage: obs[12 : 12+3A] (fly.py:795, 801, 802), root rows, gathered contact rows
     {
-      float* oe = obs_s + en * O + 12;
+      int el = tid / A, k = tid - el * A;
 #pragma unroll
       for (int u = 0; u < DU; ++u) {
-        const int k = qd + 2 * u;
-        if (e_ok && k < A) {
+        const int f = tid + tcm::EPI_THREADS * u;
+        if (f < npairs) {
+          float* oe = obs_s + el * O + 12;
           oe[k] = unscale(pv[u].x, st->lo[k], st->hi[k]);
           oe[A + k] = pv[u].y * c.dof_vel_scale;
           oe[2 * A + k] = cmd[u];
         }
+        el += el_step;
+        k += k_step;
+        if (k >= A) { k -= A; ++el; }
       }
     }
 #pragma unroll

@@ -619,7 +619,11 @@ extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, fl
   cudaStream_t st = (cudaStream_t)stream;
   StepFuse fuse{};
   fuse.step = (long long*)step;
-  static const bool use_tail = [] { const char* e = getenv("FLYB_PPO_TAIL"); return !(e && e[0] == '0'); }();
+  // measured (profiles/r02e): the cooperative two-launch form is 3 us SLOWER per optimiser step than the four plain
+  // launches (139.5 vs 136.2 us at 32768 samples) — two grid barriers over 148 heavy CTAs and a launch that cannot
+  // overlap its predecessor's drain cost more than the two launch gaps they replace.  Opt-in: FLYB_PPO_TAIL=1.
+  const char* tail_env = getenv("FLYB_PPO_TAIL");   // read per call: a test flips it
+  const bool use_tail = tail_env && tail_env[0] == '1';
   fuse.tail = use_tail ? 1 : 0;
   fuse.params = params; fuse.exp_avg = exp_avg; fuse.exp_avg_sq = exp_avg_sq; fuse.grad_norm_out = grad_norm_out;
   fuse.lr = cfg->lr; fuse.beta1 = cfg->beta1; fuse.beta2 = cfg->beta2; fuse.eps = cfg->eps; fuse.max_norm = cfg->max_grad_norm;

@@ -623,6 +623,7 @@ struct DwArgs {
                                // [64,128) transposer warp 0: stage in hand / handed on, [128,190) MMA warp: operands seen
 };
 
+template <bool TAIL>
 __global__ void __launch_bounds__(DW_THREADS, 1)
 ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
   extern __shared__ unsigned char smem_raw[];
@@ -926,7 +927,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
   __syncthreads();
   if (warp == 1) tc::tmem_dealloc(tb, 512);
 
-  if (a.tail.enabled) {
+  if constexpr (TAIL) {
     // ======================================================================= reduction + clip + Adam (flyb_ppo_step)
     const DwTail& t = a.tail;
     __shared__ float s_red[DW_THREADS / 32];
@@ -1189,7 +1190,8 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   d.trace = trace_dw ? tc_get_trace() : nullptr;
   { const char* e = getenv("FLYB_DW_DBG"); d.dbg = e ? atoi(e) : 0; }
   const size_t smem2 = 1024 + (size_t)DW_RAW_SLOTS * DW_RAW_SLOT + (size_t)DW_OP_SLOTS * DW_OP_SLOT + 512 + 2048 + 256;
-  if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel), smem2)) != FLYB_OK) return rc;
+  if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel<false>), smem2)) != FLYB_OK) return rc;
+  if ((rc = ensure_smem(reinterpret_cast<const void*>(ppo_dw_tc_kernel<true>), smem2)) != FLYB_OK) return rc;
   const int A = net->num_act;
   const int sizes[12] = {256 * net->k0_pad, 256, 128 * 256, 128, 64 * 128, 64, A * 64, A, 64 * 128, 64, 64, 1};
   if (fuse && fuse->tail && 2 * w.ctas_per_role <= num_sms()) {
@@ -1208,14 +1210,14 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
     t.wpack = (float*)const_cast<void*>(wpack);
     t.wpack_index = (const int4*)tc_wpack_index(net, wpack);
     void* kargs[] = {(void*)&d};
-    rc = check_cuda(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(ppo_dw_tc_kernel), dim3(2 * w.ctas_per_role),
+    rc = check_cuda(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(ppo_dw_tc_kernel<true>), dim3(2 * w.ctas_per_role),
                                                 dim3(DW_THREADS), kargs, smem2, st),
                     "cudaLaunchCooperativeKernel(ppo_dw_tc_kernel)");
     if (rc != FLYB_OK) return rc;
     fuse->done = 1;
     return FLYB_OK;
   }
-  ppo_dw_tc_kernel<<<2 * w.ctas_per_role, DW_THREADS, smem2, st>>>(d);
+  ppo_dw_tc_kernel<false><<<2 * w.ctas_per_role, DW_THREADS, smem2, st>>>(d);
   FLYB_LAUNCH_CHECK("ppo_dw_tc_kernel");
 
   ReduceArgs r{};

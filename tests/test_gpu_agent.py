@@ -451,7 +451,11 @@ def test_ppo_step_is_grad_plus_apply_and_keeps_the_weight_stream_in_step():
     dv = [x.contiguous().to(DEV) for x in (g["roll_obs"][0:mc], g["roll_acts"][0:mc], g["roll_logp"][0:mc],
                                            g["roll_target"][0:mc], g["roll_adv"][0:mc], g["roll_var"])]
     out = {}
-    for mode in ("split", "fused"):
+    import os
+    for mode in ("split", "fused", "fused_tail"):
+        # "fused_tail": FLYB_PPO_TAIL=1, the two-launch form (reduction + clip + Adam behind grid barriers in the tail of
+        # the cooperatively launched weight-gradient kernel) — opt-in, measured slower than the four launches
+        os.environ["FLYB_PPO_TAIL"] = "1" if mode == "fused_tail" else "0"
         net = golden_net(g)
         ws = torch.zeros(lib.flyb_ppo_workspace_bytes(C.byref(net.layout), rows) + 256, dtype=torch.uint8, device=DEV)
         wsp = (ws.data_ptr() + 255) // 256 * 256
@@ -480,14 +484,17 @@ def test_ppo_step_is_grad_plus_apply_and_keeps_the_weight_stream_in_step():
             if it == 0:
                 out[mode] = [net.flat.clone(), m.clone(), v.clone(), loss.clone()]
         out[mode] += [float(loss), norms]
-    a, b = out["split"], out["fused"]
-    # step 1: same gradient bit for bit; the two differ only in how the norm's partial sums are grouped, i.e. the
-    # clip coefficient moves by an ulp or two.  Later steps start from those ulp-apart parameters.
-    assert torch.equal(a[3], b[3])
-    for x, y, name in zip(a[:3], b[:3], ("params", "exp_avg", "exp_avg_sq")):
-        torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-7, msg=name)
-    assert a[4] == pytest.approx(b[4], rel=1e-4)
-    assert a[5] == pytest.approx(b[5], rel=1e-4)
+    os.environ.pop("FLYB_PPO_TAIL", None)
+    a = out["split"]
+    for other in ("fused", "fused_tail"):
+        b = out[other]
+        # step 1: same gradient bit for bit; the forms differ only in how the norm's partial sums are grouped, i.e. the
+        # clip coefficient moves by an ulp or two.  Later steps start from those ulp-apart parameters.
+        assert torch.equal(a[3], b[3]), other
+        for x, y, name in zip(a[:3], b[:3], ("params", "exp_avg", "exp_avg_sq")):
+            torch.testing.assert_close(x, y, rtol=1e-5, atol=1e-7, msg=f"{other} {name}")
+        assert a[4] == pytest.approx(b[4], rel=1e-4)
+        assert a[5] == pytest.approx(b[5], rel=1e-4)
 
 
 @pytest.mark.parametrize("n", [1001, 301])
