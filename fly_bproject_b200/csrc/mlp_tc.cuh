@@ -25,40 +25,70 @@
 // operand stored as [hi slab | lo slab], slab = N x 32 bytes in the no-swizzle K-major core-matrix layout
 // (tc_common.cuh).  Trunk = W1[0], W1[1], W2[0], W1[2], W2[1], W1[3], W2[2], W2[3]  (W1 chunk: 5 stages,
 // W2 K-chunk: 8 stages), then W3pi (8), W3v (8), W4 (2).
+//
+// TWO SHAPES, one source: the file is compiled once per shape, each into its own namespace (flyb::tcn / flyb::tcw):
+//   narrow (default)      K0 =  80, APAD = 32   num_obs <= 80,  num_act <= 32   (the 18-joint actuation: O = 73, A = 18)
+//   wide (FLYB_TC_WIDE)   K0 = 160, APAD = 48   num_obs <= 160, num_act <= 48   (the 42-joint set: O = 145, A = 42)
+// The wide X planes alone are 161 KB, so the wide shape has no raw observation stage: the epilogue warps pull the tile
+// with 4-byte cp.async straight into the hi plane (chunk pitch padded by 16 bytes so that consecutive columns do not
+// land on one bank) and split it in place; the finaliser's staging aliases the X planes, which are dead once the last
+// layer-1 MMA has completed (mu-independent staging work moves from `early` to that point); the weight ring has 6 stages.
 #pragma once
 #include "tc_common.cuh"
 
+#ifndef FLYB_TC_WIDE
+#define FLYB_TC_WIDE 0
+#endif
+#if FLYB_TC_WIDE
+#define FLYB_TC_VNS tcw
+#else
+#define FLYB_TC_VNS tcn
+#endif
+
 namespace flyb {
+namespace FLYB_TC_VNS {
 namespace tcm {
 
+constexpr bool WIDE = FLYB_TC_WIDE != 0;
 constexpr int TM = 128;
-constexpr int K0 = 80;
-constexpr int H1 = 256, H2 = 128, H3 = 64, APAD = 32;
+constexpr int K0 = WIDE ? 160 : 80;
+constexpr int H1 = 256, H2 = 128, H3 = 64, APAD = WIDE ? 48 : 32;
 constexpr int CH = 64, NCH = H1 / CH;
 constexpr int STAGE = 8192;
-constexpr int NST = 8, LOG_NST = 3;            // ring stages (64 KB)
+constexpr int NST = WIDE ? 6 : 8;              // ring stages (64 KB / 48 KB)
+FLYB_HD uint32_t ring_slot(uint32_t stage) { return stage % (uint32_t)NST; }
+FLYB_HD uint32_t ring_phase(uint32_t stage) { return (stage / (uint32_t)NST) & 1u; }
 constexpr int EPI_WARPS = 8, EPI_THREADS = EPI_WARPS * 32;
 constexpr int PRODUCER_WARP = 8, MMA_WARP = 9;
 constexpr int THREADS = 320;
 
-constexpr int W1C_STAGES = (K0 / 8) * 2 * (CH * 32) / STAGE;   // 5
-constexpr int W2C_STAGES = (CH / 8) * 2 * (H2 * 32) / STAGE;   // 8
-constexpr int TRUNK_STAGES = NCH * (W1C_STAGES + W2C_STAGES);  // 52
-constexpr int W3_STAGES = (H2 / 8) * 2 * (H3 * 32) / STAGE;    // 8
-constexpr int W4_STAGES = (H3 / 8) * 2 * (APAD * 32) / STAGE;  // 2
+// an operand with N rows: one k-step (8 k) = [hi slab | lo slab] of N x 32 bytes each; a stage holds KPS whole k-steps
+// (N = 48 leaves a quarter of its stages unused)
+constexpr int kps_for(int n) { return STAGE / (2 * n * 32); }
+constexpr int stages_for(int n, int ksteps) { return ksteps / kps_for(n); }
+constexpr int W1C_STAGES = stages_for(CH, K0 / 8);             // 5 / 10
+constexpr int W2C_STAGES = stages_for(H2, CH / 8);             // 8
+constexpr int TRUNK_STAGES = NCH * (W1C_STAGES + W2C_STAGES);  // 52 / 72
+constexpr int W3_STAGES = stages_for(H3, H2 / 8);              // 8
+constexpr int W4_STAGES = stages_for(APAD, H3 / 8);            // 2 / 4
 constexpr int OFF_W3PI = TRUNK_STAGES, OFF_W3V = OFF_W3PI + W3_STAGES, OFF_W4 = OFF_W3V + W3_STAGES;
-constexpr int FWD_STAGES = OFF_W4 + W4_STAGES;                 // 70 stages = 560 KB
+constexpr int FWD_STAGES = OFF_W4 + W4_STAGES;                 // 70 stages = 560 KB / 92 stages
 
 // TMEM column map
 constexpr uint32_t C_D1 = 0, C_A2 = 128, C_D2 = 384;
 constexpr uint32_t C_A3H = 0, C_A3L = H2, C_D3 = 256, C_A4H = 384, C_A4L = 448, C_D4 = 0;
 
 // bias block in shared memory (floats)
-constexpr int B_B1 = 0, B_B2 = 256, B_B3PI = 384, B_B3V = 448, B_B4 = 512, B_W4V = 544, B_B4V = 608, B_TOTAL = 640;
+constexpr int B_B1 = 0, B_B2 = 256, B_B3PI = 384, B_B3V = 448, B_B4 = 512, B_W4V = B_B4 + APAD, B_B4V = B_W4V + 64,
+              B_TOTAL = B_B4V + 32;
 
-__host__ __device__ inline size_t obs_stage_bytes(int O) { return ((size_t)TM * O * 4 + 127) / 128 * 128; }
-constexpr size_t X_PLANE_BYTES = (size_t)TM * K0 * 4;     // 40960: one of the hi / lo planes of the A operand
-constexpr uint32_t X_LBO = TM * 16, X_SBO = 128;          // K-major no-swizzle: [k/4][row][4 floats]
+__host__ __device__ inline size_t obs_stage_bytes(int O) { return WIDE ? 0 : ((size_t)TM * O * 4 + 127) / 128 * 128; }
+// K-major no-swizzle A operand: [k/4][row][4 floats]; the wide shape pads the chunk pitch (see the header comment)
+constexpr uint32_t X_LBO = TM * 16 + (WIDE ? 16 : 0), X_SBO = 128;
+constexpr size_t X_PLANE_BYTES = (size_t)(K0 / 4) * X_LBO;   // 40960 / 82560: one of the hi / lo planes
+FLYB_D uint4* x_chunk(float* plane, int kc, int r) {
+  return reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(plane) + (size_t)kc * X_LBO) + r;
+}
 
 struct Smem {
   unsigned char* ring;
@@ -73,8 +103,9 @@ struct Smem {
 };
 
 __host__ __device__ inline size_t smem_bytes(int O, size_t out_bytes) {
-  return 1024 + (size_t)NST * STAGE + 2 * X_PLANE_BYTES + obs_stage_bytes(O) + ((out_bytes + 127) / 128 * 128) +
-         B_TOTAL * 4 + TM * 4 + (2 * NST + 6) * 8 + 16;
+  // wide: the finaliser's staging aliases the X planes (out_bytes <= 2 * X_PLANE_BYTES, checked by the launchers)
+  return 1024 + (size_t)NST * STAGE + 2 * X_PLANE_BYTES + obs_stage_bytes(O) +
+         (WIDE ? 0 : ((out_bytes + 127) / 128 * 128)) + B_TOTAL * 4 + TM * 4 + (2 * NST + 6) * 8 + 16;
 }
 
 // `raw` must be the kernel's `extern __shared__` array itself: every pointer below is derived from it by plain
@@ -89,10 +120,10 @@ FLYB_D Smem carve(unsigned char* raw, int O, size_t out_bytes) {
   p += X_PLANE_BYTES;
   s.xlo = reinterpret_cast<float*>(p);
   p += X_PLANE_BYTES;
-  s.obs = reinterpret_cast<float*>(p);
+  s.obs = WIDE ? nullptr : reinterpret_cast<float*>(p);
   p += obs_stage_bytes(O);
-  s.out = reinterpret_cast<float*>(p);
-  p += (out_bytes + 127) / 128 * 128;
+  s.out = WIDE ? s.xhi : reinterpret_cast<float*>(p);
+  p += WIDE ? 0 : (out_bytes + 127) / 128 * 128;
   s.bias = reinterpret_cast<float*>(p);
   p += B_TOTAL * 4;
   s.vpart = reinterpret_cast<float*>(p);
@@ -165,14 +196,14 @@ FLYB_D void mma_segment(MmaState& m, uint32_t a_hi, uint32_t a_lo, uint32_t d, b
     }
   };
   static_assert(2 * SLAB <= STAGE, "a k-step (hi + lo slab) must fit one stage");
-  constexpr int KPS = STAGE / (2 * SLAB);   // k-steps per stage
+  constexpr int KPS = kps_for(N);   // whole k-steps per stage
   static_assert(KSTEPS % KPS == 0, "segment must end on a stage boundary");
   // rolled over stages (the whole kernel runs once per tile: straight-line code would only miss in the
   // instruction cache), unrolled over the KPS k-steps of a stage
 #pragma unroll 1
   for (int ks0 = 0; ks0 < KSTEPS; ks0 += KPS) {
-    const uint32_t slot = m.stage & (NST - 1);
-    tc::mbar_wait(&m.full[slot], (m.stage >> LOG_NST) & 1u);
+    const uint32_t slot = ring_slot(m.stage);
+    tc::mbar_wait(&m.full[slot], ring_phase(m.stage));
     tc::tc_fence_after();
     const uint32_t base = m.ring + slot * STAGE;
 #pragma unroll
@@ -363,7 +394,9 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
 
   // ---- one-time setup
   constexpr bool BUILD = Final::kBuildsObs;
-  if (!KICKED && warp == PRODUCER_WARP) producer_kickoff(s, a, !BUILD);
+  constexpr bool NO_TMA_OBS = BUILD || WIDE;   // the producer warp does not load observation tiles
+  static_assert(!(BUILD && WIDE), "the fused env step exists for the narrow shape only");
+  if (!KICKED && warp == PRODUCER_WARP) producer_kickoff(s, a, !NO_TMA_OBS);
   if (warp == MMA_WARP) tc::tmem_alloc(s.tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
@@ -387,7 +420,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       const float* src = a.obs + (size_t)row0 * O;
       // The first tile's rows were requested by producer_kickoff(): no wait for it (the epilogue warps may already
       // have released that buffer by now — waiting for "the phase before" would then wait for the NEXT release).
-      if (kicked == 0 && !BUILD) {
+      if (kicked == 0 && !NO_TMA_OBS) {
         tc::mbar_wait_relaxed(s.obs_empty, obs_phase);   // the epilogue warps are done with the previous tile's rows
         obs_phase ^= 1u;
         if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
@@ -399,8 +432,8 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
         const unsigned char* g = a.wpack + (size_t)first * STAGE;
         for (int i = 0; i < count; ++i, ++gs, g += STAGE) {
           if (kicked > 0) { --kicked; continue; }
-          const uint32_t slot = gs & (NST - 1);
-          tc::mbar_wait_relaxed(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
+          const uint32_t slot = ring_slot(gs);
+          tc::mbar_wait_relaxed(&s.empty[slot], ring_phase(gs) ^ 1u);
           const uint32_t bar = tc::smem_u32(&s.full[slot]);
           asm volatile(
               "{\n\t.reg .pred q;\n\t.reg .b64 st;\n\tsetp.ne.b32 q, %4, 0;\n\t"
@@ -488,7 +521,28 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
       const float* src = a.obs + (size_t)row0 * O;
       const bool by_tma = (bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0;
-      if constexpr (BUILD) {
+      if constexpr (WIDE) {
+        // the previous tile's finaliser is done with the staging that aliases the X planes (its bulk store included)
+        if (threadIdx.x == 0) tc::tma_store_wait_read<0>();
+        epi_bar_sync();
+        // the tile's nrows x O floats are contiguous: lane-consecutive 4-byte cp.async into the hi plane's K-major slots
+        {
+          const int n = nrows * O;
+          const int r_step = EPI_THREADS / O, c_step = EPI_THREADS % O;
+          int rr = threadIdx.x / O, c = threadIdx.x - rr * O;
+          unsigned char* plane = reinterpret_cast<unsigned char*>(s.xhi);
+          for (int e = threadIdx.x; e < n; e += EPI_THREADS) {
+            const uint32_t dst = tc::smem_u32(plane + (size_t)(c >> 2) * X_LBO + (size_t)rr * 16 + (c & 3) * 4);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + e) : "memory");
+            rr += r_step;
+            c += c_step;
+            if (c >= O) { c -= O; ++rr; }
+          }
+          cp_async_commit();
+          cp_async_wait<0>();
+          epi_bar_sync();
+        }
+      } else if constexpr (BUILD) {
         fin.build_obs(s, row0, nrows);
       } else if (by_tma) {
         tc::mbar_wait(s.obs_full, obs_phase);
@@ -502,27 +556,36 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
       fin.begin_tile(s, row0, r, nrows);
 
       // ---- X = split(obs row) in the UMMA K-major layout, zero padded to K0 columns and TM rows
+      //      (wide: the raw values already sit in their hi-plane slots and are split in place)
       {
-        const float* xr = s.obs + r * O;
+        const float* xr = WIDE ? nullptr : s.obs + r * O;
         const bool live = r < nrows;
 #pragma unroll 2
         for (int g = 0; g < K0 / 8; ++g) {
           const int kc = h * (K0 / 8) + g;   // 16-byte K chunk
           uint32_t hi[4], lo[4];
+          float raw[4];
+          if constexpr (WIDE) {
+            const uint4 v = *x_chunk(s.xhi, kc, r);
+            raw[0] = __uint_as_float(v.x); raw[1] = __uint_as_float(v.y);
+            raw[2] = __uint_as_float(v.z); raw[3] = __uint_as_float(v.w);
+          }
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int c = kc * 4 + j;
-            split_fast((live && c < O) ? xr[c] : 0.0f, hi[j], lo[j]);
+            float x = 0.0f;
+            if (live && c < O) x = WIDE ? raw[j] : xr[c];
+            split_fast(x, hi[j], lo[j]);
           }
-          reinterpret_cast<uint4*>(s.xhi)[kc * TM + r] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-          reinterpret_cast<uint4*>(s.xlo)[kc * TM + r] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          *x_chunk(s.xhi, kc, r) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          *x_chunk(s.xlo, kc, r) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
         tc::fence_proxy_async();   // generic-proxy writes -> visible to the tensor core's shared-memory reads
       }
       trace_mark(etrace, ti, 128);
       fin.obs_consumed(s);
       arrive_a(0);
-      fin.early(s, row0, nrows);   // mu-independent work, overlapped with the first MMAs of the tile
+      if constexpr (!WIDE) fin.early(s, row0, nrows);   // mu-independent work, overlapped with the first MMAs of the tile
       if (!setup_seen) {           // bias block + tables are complete from here on
         setup_wait();
         setup_seen = true;
@@ -539,6 +602,8 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
         arrive_a(b);
         trace_mark(etrace, ti, 128);
       }
+      // wide: every layer-1 MMA has completed (chunk 3's accumulator was seen), the X planes are dead -> staging
+      if constexpr (WIDE) fin.early(s, row0, nrows);
       // ---- A3 = ELU(D2 + b2): 64 columns per thread
       wait_d(0);
       trace_mark(etrace, ti, 128);
@@ -576,7 +641,7 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
         trace_mark(etrace, ti, 128);
         float mu[APAD];
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
+        for (int g = 0; g < APAD / 16; ++g) {
           uint32_t v[16];
           tc::tmem_ld16(tc::tmem_addr(tb, lane_base, C_D4 + g * 16), v);
           tc::tmem_wait_ld();
@@ -602,4 +667,5 @@ FLYB_D void forward_persistent(const FlybNetLayout& net, const FwdArgs& a, Final
 }
 
 }  // namespace tcm
+}  // namespace FLYB_TC_VNS
 }  // namespace flyb

@@ -10,6 +10,7 @@
 #include "env_math.cuh"
 #include "mlp_simt.cuh"
 #include "philox.cuh"
+#include "tc_dispatch.cuh"
 
 namespace flyb {
 
@@ -196,21 +197,6 @@ int validate_net(const FlybNetLayout* net, const float* params) {
 }
 
 // tensor-core path (policy_kernels_tc.cu)
-bool tc_supported(const FlybNetLayout* net);
-bool tc_act_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg);
-bool tc_step_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg);
-int tc_launch_step(const FlybNetLayout* net, const float* params, const void* wpack, const FlybEnvCfg* cfg,
-                   const FlybStepIO* io, cudaStream_t st);
-size_t tc_wpack_bytes(const FlybNetLayout* net);
-int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st);
-int tc_launch_forward(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs,
-                      long long rows, float* mu_out, float* value_out, cudaStream_t st);
-int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs, long long rows,
-                  const float* action_var, const float* noise, uint64_t seed, uint64_t offset,
-                  const uint64_t* offset_dev, float* action, float* logp, float* mu_out, float* obs_store,
-                  const FlybEnvCfg* cfg, float* actions_scaled, float* dof_targets, int64_t* reset, int64_t* progress,
-                  float* potentials, float* prev_potentials, float* root, float* dof_state, cudaStream_t st);
-
 }  // namespace flyb
 
 using namespace flyb;
@@ -229,7 +215,7 @@ extern "C" int flyb_pack_weights(const FlybNetLayout* net, const float* params, 
   int rc = validate_net(net, params);
   if (rc != FLYB_OK) return rc;
   FLYB_REQUIRE(wpack != nullptr && aligned16(wpack), "flyb_pack_weights: wpack must be a 16-byte aligned buffer");
-  FLYB_REQUIRE(tc_supported(net), "flyb_pack_weights: the tensor-core path needs num_obs <= 80 and num_act <= 32");
+  FLYB_REQUIRE(tc_supported(net), "flyb_pack_weights: the tensor-core path needs num_obs <= 160 and num_act <= 48");
   return tc_pack_weights(net, params, wpack, (cudaStream_t)stream);
 }
 
@@ -296,7 +282,7 @@ extern "C" int flyb_policy_act(const FlybNetLayout* net, const float* params, co
   }
   if (wpack) {   // tensor-core path (3xTF32 on tcgen05, policy_kernels_tc.cu)
     FLYB_REQUIRE(tc_act_supported(net, cfg), "flyb_policy_act: wpack given but the tensor-core path does not cover "
-                 "this shape (needs num_obs <= 80, num_act <= 32)");
+                 "this shape (needs num_obs <= 160, num_act <= 48)");
     FLYB_REQUIRE(aligned16(wpack), "wpack must be 16-byte aligned");
     return tc_launch_act(net, params, wpack, obs, rows, action_var, noise, seed, offset, offset_dev, action, logp,
                          mu_out, obs_store, cfg, actions_scaled, dof_targets, reset, progress, potentials,

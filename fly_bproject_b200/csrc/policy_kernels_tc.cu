@@ -17,6 +17,9 @@ namespace flyb {
 
 int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
+unsigned long long* tc_get_trace();
+
+namespace FLYB_TC_VNS {   // tcn (narrow shape) or tcw (wide shape, FLYB_TC_WIDE): see mlp_tc.cuh
 
 // ------------------------------------------------------------------------------------------------ weight packing
 struct PackSeg {
@@ -41,7 +44,7 @@ static PackPlan forward_plan(const FlybNetLayout& net) {
   auto add = [&](int N, int ksteps, int w_off, int ldw, int n0, int k0, int n_rows, int k_cols) {
     PackSeg& s = p.seg[p.nseg++];
     s.first_stage = stage;
-    s.nstages = ksteps * 2 * N * 32 / STAGE;
+    s.nstages = stages_for(N, ksteps);
     s.N = N; s.ksteps = ksteps; s.w_off = w_off; s.ldw = ldw; s.n0 = n0; s.k0 = k0; s.n_rows = n_rows; s.k_cols = k_cols;
     s.transposed = 0;
     stage += s.nstages;
@@ -59,15 +62,18 @@ static PackPlan forward_plan(const FlybNetLayout& net) {
   add(H3, H2 / 8, net.off[8], H2, 0, 0, H3, H2);                   // W3v   (to_value.0)
   add(APAD, H3 / 8, net.off[6], H3, 0, 0, net.num_act, H3);        // W4    (to_mean.2), rows >= A are zero
   // ---- backward operands (ppo_kernels_tc.cu): B[n][k] = W[k][n], consumed after the forward stages
-  auto addt = [&](int N, int ksteps, int w_off, int ldw, int n0, int n_rows, int k_cols) {
-    add(N, ksteps, w_off, ldw, n0, 0, n_rows, k_cols);
-    p.seg[p.nseg - 1].transposed = 1;
-  };
-  addt(H3, APAD / 8, net.off[6], H3, 0, H3, net.num_act);          // W4^T : dM1 = dZmu * W4       (k = action)
-  addt(H2, H3 / 8, net.off[4], H2, 0, H2, H3);                     // W3pi^T: dH2 += dZm1 * W3pi    (k = m1 feature)
-  addt(H2, H3 / 8, net.off[8], H2, 0, H2, H3);                     // W3v^T : dH2 += dZv1 * W3v
-  addt(128, H2 / 8, net.off[2], H1, 0, 128, H2);                   // W2^T, h1 features [0,128)   (k = h2 feature)
-  addt(128, H2 / 8, net.off[2], H1, 128, 128, H2);                 // W2^T, h1 features [128,256)
+  //      (narrow shape only: the wide shape's optimiser step runs on the CUDA-core kernels)
+  if (!WIDE) {
+    auto addt = [&](int N, int ksteps, int w_off, int ldw, int n0, int n_rows, int k_cols) {
+      add(N, ksteps, w_off, ldw, n0, 0, n_rows, k_cols);
+      p.seg[p.nseg - 1].transposed = 1;
+    };
+    addt(H3, APAD / 8, net.off[6], H3, 0, H3, net.num_act);          // W4^T : dM1 = dZmu * W4       (k = action)
+    addt(H2, H3 / 8, net.off[4], H2, 0, H2, H3);                     // W3pi^T: dH2 += dZm1 * W3pi    (k = m1 feature)
+    addt(H2, H3 / 8, net.off[8], H2, 0, H2, H3);                     // W3v^T : dH2 += dZv1 * W3v
+    addt(128, H2 / 8, net.off[2], H1, 0, 128, H2);                   // W2^T, h1 features [0,128)   (k = h2 feature)
+    addt(128, H2 / 8, net.off[2], H1, 128, 128, H2);                 // W2^T, h1 features [128,256)
+  }
   p.total_stages = stage;
   return p;
 }
@@ -84,13 +90,16 @@ pack_weights_kernel(const __grid_constant__ PackPlan plan, const float* __restri
     const PackSeg& s = plan.seg[si];
     const int li = idx - s.first_stage * (tcm::STAGE / 4);
     const int slab_floats = s.N * 8;
-    const int slab = li / slab_floats, e = li - slab * slab_floats;
-    const int ks = slab >> 1, is_lo = slab & 1;
+    // a stage holds kps whole k-steps ([hi slab | lo slab] each); what is left of it (N = 48) stays zero
+    const int kps = tcm::STAGE / (2 * s.N * 32);
+    const int st_local = li / (tcm::STAGE / 4), within = li - st_local * (tcm::STAGE / 4);
+    const int slab = within / slab_floats, e = within - slab * slab_floats;
+    const int ks = st_local * kps + (slab >> 1), is_lo = slab & 1;
     const int kc = e / (s.N * 4), rem = e - kc * (s.N * 4);
     const int n = rem >> 2, kk = rem & 3;
     const int k = s.k0 + ks * 8 + kc * 4 + kk;
     float w = 0.0f;
-    if (n < s.n_rows && k < s.k_cols)
+    if ((slab >> 1) < kps && n < s.n_rows && k < s.k_cols)
       w = s.transposed ? params[s.w_off + (size_t)k * s.ldw + s.n0 + n] : params[s.w_off + (size_t)(s.n0 + n) * s.ldw + k];
     const float hi = __uint_as_float(tc::tf32_rna_bits(w));
     wpack[idx] = is_lo ? __uint_as_float(tc::tf32_rna_bits(w - hi)) : hi;
@@ -112,9 +121,11 @@ pack_index_kernel(const __grid_constant__ PackPlan plan, int* __restrict__ inv) 
     const PackSeg& s = plan.seg[si];
     const int li = idx - s.first_stage * (tcm::STAGE / 4);
     const int slab_floats = s.N * 8;
-    const int slab = li / slab_floats, e = li - slab * slab_floats;
-    if (slab & 1) continue;   // lo slab: reached through delta
-    const int ks = slab >> 1;
+    const int kps = tcm::STAGE / (2 * s.N * 32);
+    const int st_local = li / (tcm::STAGE / 4), within = li - st_local * (tcm::STAGE / 4);
+    const int slab = within / slab_floats, e = within - slab * slab_floats;
+    if ((slab & 1) || (slab >> 1) >= kps) continue;   // lo slab: reached through delta; tail of the stage: unused
+    const int ks = st_local * kps + (slab >> 1);
     const int kc = e / (s.N * 4), rem = e - kc * (s.N * 4);
     const int n = rem >> 2, kk = rem & 3;
     const int k = s.k0 + ks * 8 + kc * 4 + kk;
@@ -261,15 +272,22 @@ struct ActFinal {
     }
     __syncwarp();
   }
+  const float* obs_src;    // wide shape: the observation rows in global memory (there is no raw stage to copy from)
   FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {
     rst_raw = (has_env && reset != nullptr && r < nrows) ? reset[row0 + r] : 0;
     if (obs_store) {   // rollout row all_obs[i] = obs (ppo.py:226)
-      store_tile(obs_store + (size_t)row0 * O, s.obs, nrows * O);
-      if (threadIdx.x == 0) tc::tma_store_commit();
+      if constexpr (tcm::WIDE) {
+        const float* src = obs_src + (size_t)row0 * O;
+        float* dst = obs_store + (size_t)row0 * O;
+        for (int i = threadIdx.x; i < nrows * O; i += tcm::EPI_THREADS) dst[i] = __ldg(src + i);
+      } else {
+        store_tile(obs_store + (size_t)row0 * O, s.obs, nrows * O);
+        if (threadIdx.x == 0) tc::tma_store_commit();
+      }
     }
   }
   FLYB_D void obs_consumed(const tcm::Smem& s) {
-    if (obs_store && threadIdx.x == 0) tc::tma_store_wait_read<0>();   // the bulk store has read the staging buffer
+    if (!tcm::WIDE && obs_store && threadIdx.x == 0) tc::tma_store_wait_read<0>();   // the bulk store has read the staging buffer
     __syncwarp();
     if ((threadIdx.x & 31) == 0) tc::mbar_arrive(s.obs_empty);
   }
@@ -390,6 +408,7 @@ struct ActFinal {
 };
 
 
+#if !FLYB_TC_WIDE
 // ------------------------------------------------------------------------------------------------ fused env step
 // ONE launch per env step of a rollout: [get_obs + progress += 1 + get_reward of step i-1 (fly.py:676-681)] followed by
 // [act + action scaling + DOF targets + Fly.reset bookkeeping of step i (ppo.py:213-220, fly.py:626-660, 446-480)] for
@@ -774,6 +793,7 @@ struct StepFinal : ActFinal {
     }
   }
 };
+#endif   // !FLYB_TC_WIDE
 
 // ------------------------------------------------------------------------------------------------ kernels
 template <bool WANT_PI, bool WANT_V>
@@ -813,7 +833,7 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
   ActFinal fin;
   fin.noise = x.noise; fin.seed = x.seed;
   fin.draw = x.offset + (x.offset_dev ? __ldg(x.offset_dev) : 0ull);
-  fin.action = x.action; fin.logp = x.logp; fin.mu_out = x.mu_out; fin.obs_store = x.obs_store;
+  fin.action = x.action; fin.logp = x.logp; fin.mu_out = x.mu_out; fin.obs_store = x.obs_store; fin.obs_src = a.obs;
   fin.A = A; fin.O = net.num_obs; fin.D = x.has_env ? cfg.num_dof : 0;
   fin.cfg = &cfg; fin.has_env = x.has_env;
   fin.actions_scaled = x.actions_scaled; fin.dof_targets = x.dof_targets; fin.reset = x.reset; fin.progress = x.progress;
@@ -825,6 +845,7 @@ policy_act_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_con
 }
 
 
+#if !FLYB_TC_WIDE
 struct StepTcArgs {
   ActTcArgs act;
   StepEnvArgs env;
@@ -854,12 +875,14 @@ env_step_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_const
   tcm::forward_persistent<true, false>(net, a, fin);
   if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[191] = clock64();       // kernel exit
 }
+#endif   // !FLYB_TC_WIDE
 
 // ------------------------------------------------------------------------------------------------ host side
-static unsigned long long* g_trace = nullptr;   // debug timeline buffer (flyb_debug_set_trace), normally NULL
-void tc_set_trace(void* p) { g_trace = (unsigned long long*)p; }
-unsigned long long* tc_get_trace() { return g_trace; }
-bool tc_supported(const FlybNetLayout* net) { return net->k0_pad == tcm::K0 && net->num_act <= tcm::APAD; }
+#define g_trace (::flyb::tc_get_trace())
+// narrow: exactly the K0 = 80 layout (the PPO kernels' layer-1 accumulators assume it); wide: anything up to K0 = 160
+bool tc_supported(const FlybNetLayout* net) {
+  return (tcm::WIDE ? net->k0_pad <= tcm::K0 : net->k0_pad == tcm::K0) && net->num_act <= tcm::APAD;
+}
 
 // wpack = [weight stream: total_stages x 8 KB][inverse index: net->total x 4 int32]
 size_t tc_wpack_bytes(const FlybNetLayout* net) {
@@ -915,7 +938,8 @@ int tc_launch_forward(const FlybNetLayout* net, const float* params, const void*
 bool tc_act_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg) {
   if (!tc_supported(net)) return false;
   const size_t out = (size_t)tcm::TM * 3 * net->num_act * 4;
-  return tcm::smem_bytes(net->num_obs, out) <= 227u * 1024u;
+  if (tcm::WIDE && out > 2 * tcm::X_PLANE_BYTES) return false;   // the staging aliases the X planes
+  return tcm::smem_bytes(net->num_obs, out) + 3072 <= 227u * 1024u;
 }
 
 int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpack, const float* obs, long long rows,
@@ -948,6 +972,7 @@ int tc_launch_act(const FlybNetLayout* net, const float* params, const void* wpa
 }
 
 
+#if !FLYB_TC_WIDE
 // fused env step (flyb_env_step_fused): shapes the tensor-core act path covers, with the env staging next to the ring
 bool tc_step_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg) {
   if (!tc_supported(net) || cfg == nullptr || net->num_act > 20) return false;
@@ -988,5 +1013,15 @@ int tc_launch_step(const FlybNetLayout* net, const float* params, const void* wp
   FLYB_LAUNCH_CHECK("env_step_tc_kernel");
   return FLYB_OK;
 }
+
+#endif   // !FLYB_TC_WIDE
+
+}  // namespace FLYB_TC_VNS
+
+#if !FLYB_TC_WIDE
+static unsigned long long* g_trace_buf = nullptr;   // debug timeline buffer (flyb_debug_set_trace), normally NULL
+void tc_set_trace(void* p) { g_trace_buf = (unsigned long long*)p; }
+unsigned long long* tc_get_trace() { return g_trace_buf; }
+#endif
 
 }  // namespace flyb

@@ -17,14 +17,13 @@
 #include "adam.cuh"
 #include "peer.cuh"
 #include "tc_common.cuh"
+#include "tc_dispatch.cuh"
 #include "mlp_simt.cuh"
 
 namespace flyb {
 
 int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
-bool tc_supported(const FlybNetLayout* net);
-int tc_pack_weights(const FlybNetLayout* net, const float* params, void* wpack, cudaStream_t st);
 size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows);
 // flyb_ppo_step: the gradient reduction also takes the squared norm and bumps Adam's step counter, so that Adam can
 // follow without a norm kernel.  in: step;  out: sq_part [sq_parts]
@@ -43,7 +42,6 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
                 const float* obs, const float* action, const float* old_logp, const float* target,
                 const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
                 void* workspace, const FlybPeerGroup* peers, cudaStream_t st, StepFuse* fuse = nullptr);
-const int* tc_wpack_index(const FlybNetLayout* net, const void* wpack);
 
 constexpr int DW_SPLITS_MAX = 64;
 constexpr int NORM_BLOCKS = 256;
@@ -463,8 +461,8 @@ extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, co
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_grad: workspace must be 256-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   if (peers && (rc = peer_validate(peers, net->total)) != FLYB_OK) return rc;
-  if (wpack) {   // tensor-core path (ppo_kernels_tc.cu)
-    FLYB_REQUIRE(tc_supported(net), "flyb_ppo_grad: wpack given but the tensor-core path does not cover this shape");
+  FLYB_REQUIRE(!wpack || tc_supported(net), "flyb_ppo_grad: wpack given but the tensor-core path does not cover this shape");
+  if (wpack && tc_ppo_supported(net)) {   // tensor-core path (ppo_kernels_tc.cu); the wide shape's step runs below
     return tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
                        workspace, peers, st);
   }
@@ -578,7 +576,7 @@ extern "C" int flyb_ppo_step_dp(const FlybNetLayout* net, const FlybPpoCfg* cfg,
                "flyb_ppo_step_dp: NULL argument (it needs the tensor-core path and a peer group)");
   FLYB_REQUIRE(rows > 0, "flyb_ppo_step_dp: rows must be > 0");
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_step_dp: workspace must be 256-byte aligned");
-  FLYB_REQUIRE(tc_supported(net), "flyb_ppo_step_dp: the tensor-core path does not cover this shape");
+  FLYB_REQUIRE(tc_ppo_supported(net), "flyb_ppo_step_dp: the tensor-core PPO step does not cover this shape");
   if ((rc = peer_validate(peers, net->total)) != FLYB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   StepFuse fuse{};
@@ -601,11 +599,12 @@ extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, fl
                              const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
                              float* exp_avg, float* exp_avg_sq, int64_t* step, float* grad_norm_out, void* workspace,
                              void* stream) {
-  if (!wpack) {   // CUDA-core path: the two halves as they are
+  if (!wpack || !tc_ppo_supported(net)) {   // CUDA-core gradient: the two halves as they are (Adam still keeps a
+    // forward-only weight stream — the wide shape's — in step)
     int rc = flyb_ppo_grad(net, cfg, params, nullptr, obs, action, old_logp, target, advantage, action_var, rows, grad,
                            loss, workspace, nullptr, stream);
     if (rc != FLYB_OK) return rc;
-    return flyb_ppo_apply(net, cfg, params, grad, exp_avg, exp_avg_sq, step, 1.0f, grad_norm_out, workspace, nullptr,
+    return flyb_ppo_apply(net, cfg, params, grad, exp_avg, exp_avg_sq, step, 1.0f, grad_norm_out, workspace, wpack,
                           nullptr, stream);
   }
   int rc = validate_net(net, params);
@@ -615,7 +614,7 @@ extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, fl
                "flyb_ppo_step: NULL argument");
   FLYB_REQUIRE(rows > 0, "flyb_ppo_step: rows must be > 0");
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_step: workspace must be 256-byte aligned");
-  FLYB_REQUIRE(tc_supported(net), "flyb_ppo_step: wpack given but the tensor-core path does not cover this shape");
+  FLYB_REQUIRE(tc_ppo_supported(net), "flyb_ppo_step: wpack given but the tensor-core path does not cover this shape");
   cudaStream_t st = (cudaStream_t)stream;
   StepFuse fuse{};
   fuse.step = (long long*)step;

@@ -36,10 +36,10 @@ namespace flyb {
 
 int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
-bool tc_supported(const FlybNetLayout* net);
 unsigned long long* tc_get_trace();
-const int* tc_wpack_index(const FlybNetLayout* net, const void* wpack);
 
+#ifndef FLYB_STEP_FUSE_DEFINED
+#define FLYB_STEP_FUSE_DEFINED
 struct StepFuse {   // see ppo_kernels.cu
   long long* step;
   const float* sq_part;
@@ -50,14 +50,19 @@ struct StepFuse {   // see ppo_kernels.cu
   int done;
   float grad_scale;   // 1 / world when the tail also does the data-parallel exchange (peers != NULL), else 1
 };
+#endif
+
+namespace FLYB_TC_VNS {   // tcn (narrow shape) or tcw (wide shape, FLYB_TC_WIDE): see mlp_tc.cuh
+bool tc_supported(const FlybNetLayout* net);
+const int* tc_wpack_index(const FlybNetLayout* net, const void* wpack);
 
 namespace tcb {
 using namespace tcm;
 
-constexpr int W4T_STAGES = (APAD / 8) * 2 * (H3 * 32) / STAGE;        // 2
-constexpr int W3T_STAGES = (2 * H3 / 8) * 2 * (H2 * 32) / STAGE;      // 16
-constexpr int W2T_STAGES = 2 * (H2 / 8) * 2 * (128 * 32) / STAGE;     // 32
-constexpr int ALL_STAGES = FWD_STAGES + W4T_STAGES + W3T_STAGES + W2T_STAGES;   // 120
+constexpr int W4T_STAGES = stages_for(H3, APAD / 8);                  // 2 / 3
+constexpr int W3T_STAGES = stages_for(H2, 2 * H3 / 8);                // 16
+constexpr int W2T_STAGES = 2 * stages_for(128, H2 / 8);               // 32
+constexpr int ALL_STAGES = FWD_STAGES + W4T_STAGES + W3T_STAGES + W2T_STAGES;   // 120 / 143
 
 // image feature counts
 constexpr int F_X = K0, F_H1 = H1, F_H2 = H2, F_MV = 2 * H3, F_DZMUV = 64, F_DZMV = 2 * H3, F_DZH2 = H2, F_DZH1 = H1;
@@ -127,7 +132,10 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
   extern __shared__ unsigned char smem_raw[];
   const Smem s = carve(smem_raw, a.O, 0);
   __shared__ float s_std[APAD], s_inv_std[APAD], s_inv_var[APAD];
-  __shared__ __align__(16) float s_act[TM * APAD];   // the tile's actions, row-major with the real stride A
+  // the tile's actions, row-major with the real stride A.  Wide shape: no room for 24 KB next to the 161 KB X planes —
+  // the tile lives IN the hi plane, which is dead once the last layer-1 MMA has completed (staged after the trunk)
+  __shared__ __align__(16) float s_act_static[WIDE ? 4 : TM * APAD];
+  float* const s_act = WIDE ? s.xhi : s_act_static;
   __shared__ float s_half_log_det;
   __shared__ float s_vp[2 * TM];
   __shared__ float s_red[EPI_WARPS][2];
@@ -136,7 +144,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
   const long long ntiles = (a.rows + TM - 1) / TM;
 
   // ---- one-time setup (barriers + the first loads go out first, see producer_kickoff)
-  if (warp == PRODUCER_WARP) producer_kickoff(s, a);
+  if (warp == PRODUCER_WARP) producer_kickoff(s, a, !WIDE);
   if (warp == MMA_WARP) tc::tmem_alloc(s.tmem_slot, 512);
   {
     const float* p = a.params;
@@ -168,8 +176,9 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
     s_half_log_det = hl;
   }
   const uint32_t tb = *s.tmem_slot;
-  constexpr uint32_t C_D4B = 256, C_A5H = 0, C_A5L = 32, C_D5 = 320, C_A6H = 0, C_A6L = 128, C_D6 = 384, C_A7H = 0,
-                     C_A7L = 128, C_D7 = 256;
+  // (wide: dZmu's lo plane cannot sit at [48,96) — [64,128) already holds dZv1's hi columns of A6 — it takes [128,176))
+  constexpr uint32_t C_D4B = 256, C_A5H = 0, C_A5L = WIDE ? 128 : 32, C_D5 = 320, C_A6H = 0, C_A6L = 128, C_D6 = 384,
+                     C_A7H = 0, C_A7L = 128, C_D7 = 256;
 
   if (warp == PRODUCER_WARP) {
     // =========================================================================== TMA producer (warp-uniform)
@@ -184,7 +193,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       const float* src = a.obs + (size_t)row0 * O;
       // The first tile's rows were requested by producer_kickoff(): no wait for it (the epilogue warps may already
       // have released that buffer by now — waiting for "the phase before" would then wait for the NEXT release).
-      if (kicked == 0) {
+      if (kicked == 0 && !WIDE) {
         tc::mbar_wait_relaxed(s.obs_empty, obs_phase);   // the epilogue warps are done with the previous tile's rows
         obs_phase ^= 1u;
         if ((bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0 && leader) {
@@ -195,8 +204,8 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       const unsigned char* g = a.wpack;
       for (int i = 0; i < ALL_STAGES; ++i, ++gs, g += STAGE) {
         if (kicked > 0) { --kicked; continue; }
-        const uint32_t slot = gs & (NST - 1);
-        tc::mbar_wait_relaxed(&s.empty[slot], ((gs >> LOG_NST) & 1u) ^ 1u);
+        const uint32_t slot = ring_slot(gs);
+        tc::mbar_wait_relaxed(&s.empty[slot], ring_phase(gs) ^ 1u);
         const uint32_t bar = tc::smem_u32(&s.full[slot]);
         asm volatile(
             "{\n\t.reg .pred q;\n\t.reg .b64 st;\n\tsetp.ne.b32 q, %4, 0;\n\t"
@@ -310,7 +319,24 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       const uint32_t bytes = (uint32_t)nrows * (uint32_t)O * 4u;
       const float* src = a.obs + (size_t)row0 * O;
       const bool by_tma = (bytes & 15u) == 0 && (reinterpret_cast<uintptr_t>(src) & 15u) == 0;
-      if (by_tma) {
+      if constexpr (WIDE) {
+        // (the previous tile's policy head is done with the action tile that lives in the hi plane)
+        epi_bar_sync();
+        const int n = nrows * O;
+        const int r_step = EPI_THREADS / O, c_step = EPI_THREADS % O;
+        int rr = threadIdx.x / O, c = threadIdx.x - rr * O;
+        unsigned char* plane = reinterpret_cast<unsigned char*>(s.xhi);
+        for (int e = threadIdx.x; e < n; e += EPI_THREADS) {
+          const uint32_t dst = tc::smem_u32(plane + (size_t)(c >> 2) * X_LBO + (size_t)rr * 16 + (c & 3) * 4);
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + e) : "memory");
+          rr += r_step;
+          c += c_step;
+          if (c >= O) { c -= O; ++rr; }
+        }
+        cp_async_commit();
+        cp_async_wait<0>();
+        epi_bar_sync();
+      } else if (by_tma) {
         tc::mbar_wait(s.obs_full, obs_phase);
         obs_phase ^= 1u;
       } else {
@@ -320,20 +346,26 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       }
       // ---- X = split(obs row) in the UMMA K-major layout (layer-1 A operand) + row image (dW1's B operand)
       {
-        const float* xr = s.obs + r * O;
+        const float* xr = WIDE ? nullptr : s.obs + r * O;
 #pragma unroll 2
         for (int g = 0; g < K0 / 8; ++g) {
           const int kc = h * (K0 / 8) + g;
           uint32_t hi[4], lo[4];
-          float xv[4];
+          float xv[4], raw[4];
+          if constexpr (WIDE) {
+            const uint4 v = *x_chunk(s.xhi, kc, r);
+            raw[0] = __uint_as_float(v.x); raw[1] = __uint_as_float(v.y);
+            raw[2] = __uint_as_float(v.z); raw[3] = __uint_as_float(v.w);
+          }
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int c = kc * 4 + j;
-            xv[j] = (live && c < O) ? xr[c] : 0.0f;
+            xv[j] = 0.0f;
+            if (live && c < O) xv[j] = WIDE ? raw[j] : xr[c];
             split_fast(xv[j], hi[j], lo[j]);
           }
-          reinterpret_cast<uint4*>(s.xhi)[kc * TM + r] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-          reinterpret_cast<uint4*>(s.xlo)[kc * TM + r] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          *x_chunk(s.xhi, kc, r) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          *x_chunk(s.xlo, kc, r) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
           *reinterpret_cast<float4*>(img_ptr(x_t, F_X, r, kc * 4)) = make_float4(xv[0], xv[1], xv[2], xv[3]);
         }
         tc::fence_proxy_async();
@@ -342,7 +374,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
       if (lane == 0) tc::mbar_arrive(s.obs_empty);
       arrive_a(0);
       // the tile's actions -> shared memory, asynchronously (consumed by the policy head, behind a barrier)
-      {
+      auto stage_actions = [&]() {
         const float* asrc = ga.action + (size_t)row0 * A;
         const int nfl = nrows * A;
         if ((nfl & 3) == 0 && (reinterpret_cast<uintptr_t>(asrc) & 15u) == 0) {
@@ -351,7 +383,8 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
           for (int i = threadIdx.x; i < nfl; i += EPI_THREADS) s_act[i] = __ldg(asrc + i);
         }
         cp_async_commit();
-      }
+      };
+      if constexpr (!WIDE) stage_actions();
 
       // per-row scalars of the heads, fetched now so that their latency is long gone when the heads need them
       const float tgt = live ? __ldg(ga.target + row) : 0.0f;
@@ -367,6 +400,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
                      s.bias + B_B1 + c * CH + 32 * h, img_ptr(h1_t, F_H1, r, c * CH + 32 * h), 32);
         arrive_a(b);
       }
+      if constexpr (WIDE) stage_actions();   // chunk 3's accumulator was seen: every layer-1 MMA has completed
       wait_d(0);   // D2
       epi_elu_save(t0 + C_D2 + 64 * h, t0 + C_A3H + 64 * h, t0 + C_A3L + 64 * h, s.bias + B_B2 + 64 * h,
                    img_ptr(h2_t, F_H2, r, 64 * h), 64);

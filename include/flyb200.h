@@ -120,8 +120,11 @@ int flyb_debug_set_trace(void* dev_buffer);
 /* ---- tensor-core weight stream.  The GEMMs of Net.pi / Net.v (reference ppo.py:88-102) run on tcgen05 tensor
  *      cores as 3xTF32 products (fp32 accumulate; within ~1e-6 of an fp32 evaluation) when the caller passes
  *      `wpack`: the parameters re-laid as hi/lo TF32 operand slabs in the order the kernel's TMA producer
- *      consumes them.  flyb_wpack_bytes: size of that buffer, 0 when the shape is outside the tensor-core path
- *      (it covers num_obs <= 80 and num_act <= 32; the 42-DOF joint set uses the CUDA-core fp32 path).
+ *      consumes them.  flyb_wpack_bytes: size of that buffer, 0 when the shape is outside the tensor-core path.
+ *      Two shapes are compiled: num_obs in (64, 80] with num_act <= 32 (the 18-joint actuation, O = 73: forward, act,
+ *      fused env step AND the PPO step on tensor cores) and anything else up to num_obs <= 160, num_act <= 48 (the
+ *      42-joint set, O = 145 / A = 42: forward and act on tensor cores; flyb_ppo_grad / flyb_ppo_step then run the
+ *      exact-fp32 CUDA-core kernels and only Adam's in-place refresh touches the weight stream).
  *      The buffer also holds, behind the slabs, the parameter -> slab index flyb_pack_weights builds.
  *      flyb_pack_weights must be re-run whenever `params` changes by other hands (flyb_ppo_apply / flyb_ppo_step
  *      keep a given wpack in step themselves).

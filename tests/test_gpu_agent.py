@@ -54,10 +54,12 @@ def test_net_forward_matches_reference_golden():
         assert torch.equal(sd[k].cpu(), g["w0/" + k])
 
 
-@pytest.mark.parametrize("o,a,rows", [(73, 18, 1), (73, 18, 16384 + 17), (145, 42, 3001)])
+@pytest.mark.parametrize("o,a,rows", [(73, 18, 1), (73, 18, 16384 + 17), (145, 42, 3001), (145, 42, 1), (145, 42, 40000),
+                                      (100, 27, 515)])
 def test_net_forward_matches_oracle_random_weights(o, a, rows):
     p = fo.init_params(o, a, seed=o)
     net = fb.Net(o, a, DEV, init=False, tensor_cores=TC)
+    assert (net.wpack is not None) == TC      # both shapes (O <= 80 / A <= 32 and O <= 160 / A <= 48) have a tcgen05 forward
     net.load_state_dict(p)
     x = torch.randn(rows, o, generator=torch.Generator().manual_seed(rows)) * 1.5
     mu, val = net._forward(x.to(DEV), True, True)
