@@ -295,9 +295,9 @@ def run_own(args, cfg):
     upd_value = n_minibatches * rows_mb * world / (upd_ms * 1e-3)
     step_us = roll_ms * 1e3 / horizon                              # one env step INSIDE the rollout graph
     launches_rollout = (horizon + 1) if fused else 2 * horizon
-    # per optimiser step: chain + [weight gradients + reduction + clip + Adam] on one GPU (tensor-core path); chain,
+    # per optimiser step: chain, weight gradients, reduce (+ norm), clip + Adam on one GPU (tensor-core path); chain,
     # weight gradients, reduce (+ push), norm (+ sum), Adam otherwise
-    launches_update = 2 + n_minibatches * (2 if (world == 1 and tc_path) else 5)
+    launches_update = 2 + n_minibatches * (4 if (world == 1 and tc_path) else 5)
     launches = K * REPEATS * (launches_rollout + launches_update)
 
     # ---------------- per-kernel device times, each kernel alone in a graph (pool rotation keeps L2 cold)

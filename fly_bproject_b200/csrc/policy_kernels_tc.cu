@@ -62,8 +62,7 @@ static PackPlan forward_plan(const FlybNetLayout& net) {
   add(H3, H2 / 8, net.off[8], H2, 0, 0, H3, H2);                   // W3v   (to_value.0)
   add(APAD, H3 / 8, net.off[6], H3, 0, 0, net.num_act, H3);        // W4    (to_mean.2), rows >= A are zero
   // ---- backward operands (ppo_kernels_tc.cu): B[n][k] = W[k][n], consumed after the forward stages
-  //      (narrow shape only: the wide shape's optimiser step runs on the CUDA-core kernels)
-  if (!WIDE) {
+  {
     auto addt = [&](int N, int ksteps, int w_off, int ldw, int n0, int n_rows, int k_cols) {
       add(N, ksteps, w_off, ldw, n0, 0, n_rows, k_cols);
       p.seg[p.nseg - 1].transposed = 1;

@@ -24,9 +24,9 @@ namespace flyb {
 
 int num_sms();
 int validate_net(const FlybNetLayout* net, const float* params);
-size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows);
 // flyb_ppo_step: the gradient reduction also takes the squared norm and bumps Adam's step counter, so that Adam can
 // follow without a norm kernel.  in: step;  out: sq_part [sq_parts]
+#define FLYB_STEP_FUSE_DEFINED
 struct StepFuse {
   long long* step;
   const float* sq_part;
@@ -38,11 +38,6 @@ struct StepFuse {
   int done;   // out: 1 = the step was completed by the tail (no Adam launch needed)
   float grad_scale;   // 1 / world when the tail also does the data-parallel exchange (peers != NULL), else 1
 };
-int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,
-                const float* obs, const float* action, const float* old_logp, const float* target,
-                const float* advantage, const float* action_var, long long rows, float* grad, float* loss,
-                void* workspace, const FlybPeerGroup* peers, cudaStream_t st, StepFuse* fuse = nullptr);
-
 constexpr int DW_SPLITS_MAX = 64;
 constexpr int NORM_BLOCKS = 256;
 
@@ -464,7 +459,7 @@ extern "C" int flyb_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, co
   FLYB_REQUIRE(!wpack || tc_supported(net), "flyb_ppo_grad: wpack given but the tensor-core path does not cover this shape");
   if (wpack && tc_ppo_supported(net)) {   // tensor-core path (ppo_kernels_tc.cu); the wide shape's step runs below
     return tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
-                       workspace, peers, st);
+                       workspace, peers, st, (StepFuse*)nullptr);
   }
   const PpoWs w = carve_ws(*net, rows, workspace);
 

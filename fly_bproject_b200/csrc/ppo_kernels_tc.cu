@@ -458,7 +458,7 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
         wait_d(0);   // D4
         float mu[APAD];
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
+        for (int g = 0; g < APAD / 16; ++g) {
           uint32_t v[16];
           tc::tmem_ld16(t0 + C_D4B + g * 16, v);
           tc::tmem_wait_ld();
@@ -493,14 +493,33 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
           const float dmu = dlogp * ((a_k - mu_k) * s_inv_var[k]);
           dz[j] = (k < A) ? dmu * elu_grad_from_out(mu_k) : 0.0f;   // trailing ELU on mu (ppo.py:30)
         }
-        tmem_put16(t0 + C_A5H + 16 * h, t0 + C_A5L + 16 * h, dz);   // [0,64): A3 columns, dead since D3
-        // image [dZmu (32) | dZval | 0 ...]: each half writes its 16 dZmu columns and one 16-block of the tail
+        tmem_put16(t0 + C_A5H + 16 * h, t0 + C_A5L + 16 * h, dz);   // A3 columns, dead since D3
+        // image [dZmu (APAD) | dZval | 0 ...] in 16-feature blocks; half h writes blocks h and h + 2.  Blocks below
+        // APAD / 16 are dZmu (and go to the A5 operand as well), block APAD / 16 opens with dZval, the rest is zero.
         img_store16(img_ptr(dzmuv_t, F_DZMUV, r, 16 * h), dz);
         float tail[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) tail[j] = 0.0f;
-        if (h == 0) tail[0] = dval;   // feature 32
-        img_store16(img_ptr(dzmuv_t, F_DZMUV, r, 32 + 16 * h), tail);
+        if constexpr (APAD / 16 == 2) {
+          if (h == 0) tail[0] = dval;   // feature 32
+          img_store16(img_ptr(dzmuv_t, F_DZMUV, r, 32 + 16 * h), tail);
+        } else {
+          if (h == 0) {                 // block 2: dZmu columns 32 .. 47
+            float dz2[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int k = 32 + j;
+              const float mu_k = mu[APAD - 16 + j];
+              const float dmu = dlogp * ((act[APAD - 16 + j] - mu_k) * s_inv_var[k]);
+              dz2[j] = (k < A) ? dmu * elu_grad_from_out(mu_k) : 0.0f;
+            }
+            tmem_put16(t0 + C_A5H + 32, t0 + C_A5L + 32, dz2);
+            img_store16(img_ptr(dzmuv_t, F_DZMUV, r, 32), dz2);
+          } else {                      // block 3: [dZval | 0 ...], feature 48
+            tail[0] = dval;
+            img_store16(img_ptr(dzmuv_t, F_DZMUV, r, 48), tail);
+          }
+        }
         arrive_a(0);   // -> D5
       }
       // ---- dZm1 = (dZmu * W4) .* ELU'(m1): 32 columns per thread
@@ -598,16 +617,18 @@ ppo_fwd_bwd_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_co
 
 // ================================================================================================ weight gradients
 // One "pair" = one layer's dW = dZ^T X:  A = dZ image (MA features -> D lanes), B = X image (NB features -> columns).
+static_assert(APAD / 16 == 2 || APAD / 16 == 3, "the policy head handles two or three 16-column blocks of dZmu");
 constexpr int RED_GROUPS_C = 4;                // interleaved partial groups of the gradient reduction (ppo_reduce_tc_kernel)
 constexpr int DW_KG = 2;                       // k-steps (of 8 rows) per pipeline stage
 constexpr int DW_RAW_SLOTS = 4, DW_OP_SLOTS = 2;
 constexpr int DW_TRANS_WARPS = 16, DW_THREADS = (2 + DW_TRANS_WARPS) * 32;
 FLYB_D void dw_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(DW_TRANS_WARPS * 32) : "memory"); }
-constexpr int DW_MAX_FEATS = 384;              // MA + NB of the widest pair (dZh2 128 + h1 256)
+constexpr int DW_MAX_FEATS = WIDE ? 416 : 384; // MA + NB of the widest pair (dZh2 128 + h1 256; wide: dZh1 256 + X 160)
 constexpr uint32_t DW_RAW_SLOT = DW_KG * DW_MAX_FEATS * 32;               // 24576 B
 // operand stage: per k-step and operand [hi plane | lo plane], plane = 2 K-chunks x (F * 16 + 16) bytes
 __host__ __device__ constexpr uint32_t dw_plane_bytes(int F) { return 2u * ((uint32_t)F * 16u + 16u); }
-constexpr uint32_t DW_OP_SLOT = DW_KG * 2 * (dw_plane_bytes(128) + dw_plane_bytes(256)) + 4096;   // + over-read slack
+constexpr uint32_t DW_OP_SLOT =   // the pair with the largest planes, + over-read slack
+    DW_KG * 2 * (WIDE ? dw_plane_bytes(256) + dw_plane_bytes(160) : dw_plane_bytes(128) + dw_plane_bytes(256)) + 4096;
 
 struct DwPair {
   const float* a_img;   // dZ row images
@@ -782,29 +803,33 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
     for (int i = tid; i < 2 * 256; i += DW_TRANS_WARPS * 32) bias_s[i] = 0.0f;
     dw_bar_sync();
     // Per-thread chunk plan, fixed for the whole kernel: one float4 chunk = (k-step j, feature group g, row r8) of the
-    // raw stage [A: DW_KG x (MA/4) x 8 x 4 | B: DW_KG x (NB/4) x 8 x 4].  A thread owns chunk `tid` of an operand and,
-    // for the 256-feature operand only, chunk `tid + 512` (= the same slot of the second k-step).
+    // raw stage [A: DW_KG x (MA/4) x 8 x 4 | B: DW_KG x (NB/4) x 8 x 4].  An operand with F features has 4 F chunks per
+    // stage; a thread owns chunk `tid` and, where 4 F > 512 (F = 256: all threads, F = 160: the first 128), `tid + 512`.
     static_assert(DW_KG == 2, "the k-step of a chunk is found by one compare");
     int t_src[2][2], t_n[2][2];
-    uint32_t t_dst[2][2], t_plane[2][2], t_step[2];
+    uint32_t t_dst[2][2][2], t_plane[2][2];
 #pragma unroll
     for (int pi = 0; pi < 2; ++pi) {
       const DwPair& p = role.pair[pi];
       const uint32_t pa_b = dw_plane_bytes(p.MA), pb_b = dw_plane_bytes(p.NB);
-      t_step[pi] = 2u * (pa_b + pb_b);   // bytes of one k-step block [A hi | A lo | B hi | B lo] in the operand stage
+      const uint32_t kstep_bytes = 2u * (pa_b + pb_b);   // one k-step block [A hi | A lo | B hi | B lo] in the operand stage
 #pragma unroll
       for (int op = 0; op < 2; ++op) {
         const int F = op ? p.NB : p.MA;
         const int per_k = 2 * F, total = DW_KG * per_k;
-        const int j = tid >= per_k ? 1 : 0;
-        const int rem = tid - j * per_k;
-        const int g = rem >> 3, r8 = rem & 7;
         t_src[pi][op] = (op ? DW_KG * 2 * p.MA : 0) + tid;
         t_n[pi][op] = (a.dbg & 1) ? 0 : (tid < total ? (tid + DW_TRANS_WARPS * 32 < total ? 2 : 1) : 0);
         t_plane[pi][op] = op ? pb_b : pa_b;
-        // K-major operand: plane[(chunk = r8 >> 2)][feature][r8 & 3], chunk stride F * 16 + 16 bytes
-        t_dst[pi][op] = (op ? 2u * pa_b : 0u) + (uint32_t)j * t_step[pi] + (uint32_t)(r8 >> 2) * ((uint32_t)F * 16u + 16u) +
-                        (uint32_t)g * 64u + (uint32_t)(r8 & 3) * 4u;
+#pragma unroll
+        for (int it = 0; it < 2; ++it) {
+          const int q = tid + it * DW_TRANS_WARPS * 32;
+          const int j = q >= per_k ? 1 : 0;
+          const int rem = q - j * per_k;
+          const int g = rem >> 3, r8 = rem & 7;
+          // K-major operand: plane[(chunk = r8 >> 2)][feature][r8 & 3], chunk stride F * 16 + 16 bytes
+          t_dst[pi][op][it] = (op ? 2u * pa_b : 0u) + (uint32_t)j * kstep_bytes +
+                              (uint32_t)(r8 >> 2) * ((uint32_t)F * 16u + 16u) + (uint32_t)g * 64u + (uint32_t)(r8 & 3) * 4u;
+        }
       }
     }
     // Lanes 16..31 store their four features in the order 2,3,0,1: with the 16-byte feature pitch of the core matrix
@@ -826,8 +851,6 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         const int src = pi ? t_src[1][op] : t_src[0][op];
         const int n = pi ? t_n[1][op] : t_n[0][op];
         const uint32_t plane = pi ? t_plane[1][op] : t_plane[0][op];
-        const uint32_t step = pi ? t_step[1] : t_step[0];
-        unsigned char* kbase = odst + (pi ? t_dst[1][op] : t_dst[0][op]);
 #pragma unroll
         for (int it = 0; it < 2; ++it) {
           if (it < n) {
@@ -836,7 +859,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
               float4& acc = pi == 0 ? bsum[0] : bsum[1];
               acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
             }
-            unsigned char* kb = kbase + it * step;
+            unsigned char* kb = odst + (pi ? t_dst[1][op][it] : t_dst[0][op][it]);
             uint32_t hi, lo;
             split_fast(rot ? v.z : v.x, hi, lo);
             *reinterpret_cast<uint32_t*>(kb + eo0) = hi;
@@ -921,25 +944,25 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
           const float b = bias_val(0, m);
           if (hsel == 0) out[a.off[3] + m] = b;
         }
-        {   // layer 4: lanes [0,A) = to_mean.2 rows over m1 columns [0,64); lane 32 = to_value.2 over v1 columns [64,128)
+        {   // layer 4: lanes [0,A) = to_mean.2 rows over m1 columns [0,64); lane APAD = to_value.2 over v1 columns [64,128)
           const DwPair& p = role.pair[1];
           float* dst = nullptr;
           int lo = 0, hi = 0;
           if (m < a.A) { dst = out + a.off[6] + (size_t)m * 64; lo = 0; hi = 64; }
-          else if (m == 32) { dst = out + a.off[10]; lo = 64; hi = 128; }
+          else if (m == APAD) { dst = out + a.off[10]; lo = 64; hi = 128; }
           dump(p.d_col[0], 128, dst, lo, hi);
           const float b = bias_val(1, m & 63);
           if (hsel == 0) {
             if (m < a.A) out[a.off[7] + m] = b;
-            else if (m == 32) out[a.off[11]] = b;
+            else if (m == APAD) out[a.off[11]] = b;
           }
         }
       } else {
-        {   // layer 1: dW1[128 mh + m][n] (256 x 80), db1
+        {   // layer 1: dW1[128 mh + m][n] (256 x K0), db1
           const DwPair& p = role.pair[0];
           for (int mh = 0; mh < 2; ++mh) {
-            // 80 columns = 5 blocks of 16: alternate blocks between the two warps of the quarter
-            dump(p.d_col[mh], 80, out + a.off[0] + (size_t)(128 * mh + m) * 80, 0, 80);
+            // K0 columns in blocks of 16, dealt round-robin to the four warps of the quarter
+            dump(p.d_col[mh], K0, out + a.off[0] + (size_t)(128 * mh + m) * K0, 0, K0);
             const float b = bias_val(0, 128 * mh + m);
             if (hsel == 0) out[a.off[1] + 128 * mh + m] = b;
           }
@@ -1182,8 +1205,11 @@ static Ws carve_ws(const FlybNetLayout& net, long long rows, void* basep) {
 
 }  // namespace tcb
 
+// the chain / weight-gradient kernels assume the first layer's row pitch IS the shape's K0 (80 or 160)
+bool tc_ppo_supported(const FlybNetLayout* net) { return net->k0_pad == tcm::K0 && net->num_act <= tcm::APAD; }
+
 size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows) {
-  if (!tc_supported(net)) return 0;
+  if (!tc_ppo_supported(net)) return 0;
   return tcb::carve_ws(*net, rows, nullptr).bytes;
 }
 
@@ -1213,8 +1239,13 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   // role 0: layer 2 (dZh2 x h1) and layer 4 ([dZmu|dZval] x [m1|v1]);  role 1: layer 1 (dZh1 x X), layer 3 ([dZm1|dZv1] x h2)
   d.role[0].pair[0] = DwPair{w.im.dzh2, w.im.h1, F_DZH2, F_H1, 1, {0u, 0u}, {256u, 256u}};
   d.role[0].pair[1] = DwPair{w.im.dzmuv, w.im.mv, F_DZMUV, F_MV, 1, {288u, 288u}, {416u, 416u}};
-  d.role[1].pair[0] = DwPair{w.im.dzh1, w.im.x, F_DZH1, F_X, 2, {0u, 96u}, {192u, 208u}};
-  d.role[1].pair[1] = DwPair{w.im.dzmv, w.im.h2, F_DZMV, F_H2, 1, {256u, 256u}, {384u, 384u}};
+  if (WIDE) {   // layer-1 accumulators are 160 columns per M half
+    d.role[1].pair[0] = DwPair{w.im.dzh1, w.im.x, F_DZH1, F_X, 2, {0u, 160u}, {448u, 464u}};
+    d.role[1].pair[1] = DwPair{w.im.dzmv, w.im.h2, F_DZMV, F_H2, 1, {320u, 320u}, {480u, 480u}};
+  } else {
+    d.role[1].pair[0] = DwPair{w.im.dzh1, w.im.x, F_DZH1, F_X, 2, {0u, 96u}, {192u, 208u}};
+    d.role[1].pair[1] = DwPair{w.im.dzmv, w.im.h2, F_DZMV, F_H2, 1, {256u, 256u}, {384u, 384u}};
+  }
   d.ntiles = ntiles;
   d.ctas_per_role = w.ctas_per_role;
   d.dw_part = w.dw_part;
@@ -1273,5 +1304,7 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   FLYB_LAUNCH_CHECK("ppo_reduce_tc_kernel");
   return FLYB_OK;
 }
+
+}  // namespace FLYB_TC_VNS
 
 }  // namespace flyb

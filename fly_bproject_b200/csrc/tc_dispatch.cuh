@@ -1,6 +1,6 @@
 // Host-side dispatch between the two compiled shapes of the tensor-core kernels (mlp_tc.cuh): flyb::tcn (narrow:
-// num_obs <= 80, num_act <= 32 — forward, act, fused env step and the PPO step) and flyb::tcw (wide: num_obs <= 160,
-// num_act <= 48 — forward and act; its PPO step runs on the CUDA-core kernels).
+// num_obs in (64, 80], num_act <= 32 — forward, act, fused env step and the PPO step) and flyb::tcw (wide: num_obs <= 160,
+// num_act <= 48 — forward, act; the PPO step where the padded first-layer pitch is exactly 160, i.e. num_obs in (144, 160]).
 #pragma once
 #include "flyb_common.cuh"
 
@@ -25,6 +25,20 @@ FLYB_TC_DECLARE(tcn)
 FLYB_TC_DECLARE(tcw)
 #undef FLYB_TC_DECLARE
 
+struct StepFuse;
+#define FLYB_TC_DECLARE_PPO(NS)                                                                                          \
+  namespace NS {                                                                                                         \
+  bool tc_ppo_supported(const FlybNetLayout* net);                                                                       \
+  size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows);                                               \
+  int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,              \
+                  const float* obs, const float* action, const float* old_logp, const float* target,                     \
+                  const float* advantage, const float* action_var, long long rows, float* grad, float* loss,             \
+                  void* workspace, const FlybPeerGroup* peers, cudaStream_t st, StepFuse* fuse);                         \
+  }
+FLYB_TC_DECLARE_PPO(tcn)
+FLYB_TC_DECLARE_PPO(tcw)
+#undef FLYB_TC_DECLARE_PPO
+
 namespace tcn {
 bool tc_step_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg);
 int tc_launch_step(const FlybNetLayout* net, const float* params, const void* wpack, const FlybEnvCfg* cfg,
@@ -35,7 +49,14 @@ inline bool tc_wide(const FlybNetLayout* net) { return !tcn::tc_supported(net) &
 // the forward / act kernels cover the shape (either compiled shape)
 inline bool tc_supported(const FlybNetLayout* net) { return tcn::tc_supported(net) || tcw::tc_supported(net); }
 // the tensor-core PPO step (chain + weight-gradient kernels) covers the shape
-inline bool tc_ppo_supported(const FlybNetLayout* net) { return tcn::tc_supported(net); }
+inline bool tc_ppo_supported(const FlybNetLayout* net) { return tcn::tc_ppo_supported(net) || tcw::tc_ppo_supported(net); }
+inline size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows) {
+  return tcn::tc_ppo_supported(net) ? tcn::tc_ppo_workspace_bytes(net, rows) : tcw::tc_ppo_workspace_bytes(net, rows);
+}
+template <class... Args>
+inline int tc_ppo_grad(const FlybNetLayout* net, Args... args) {
+  return tcn::tc_ppo_supported(net) ? tcn::tc_ppo_grad(net, args...) : tcw::tc_ppo_grad(net, args...);
+}
 inline bool tc_act_supported(const FlybNetLayout* net, const FlybEnvCfg* cfg) {
   return tc_wide(net) ? tcw::tc_act_supported(net, cfg) : tcn::tc_act_supported(net, cfg);
 }

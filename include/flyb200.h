@@ -122,9 +122,10 @@ int flyb_debug_set_trace(void* dev_buffer);
  *      `wpack`: the parameters re-laid as hi/lo TF32 operand slabs in the order the kernel's TMA producer
  *      consumes them.  flyb_wpack_bytes: size of that buffer, 0 when the shape is outside the tensor-core path.
  *      Two shapes are compiled: num_obs in (64, 80] with num_act <= 32 (the 18-joint actuation, O = 73: forward, act,
- *      fused env step AND the PPO step on tensor cores) and anything else up to num_obs <= 160, num_act <= 48 (the
- *      42-joint set, O = 145 / A = 42: forward and act on tensor cores; flyb_ppo_grad / flyb_ppo_step then run the
- *      exact-fp32 CUDA-core kernels and only Adam's in-place refresh touches the weight stream).
+ *      fused env step and the PPO step on tensor cores) and anything else up to num_obs <= 160, num_act <= 48 (forward
+ *      and act on tensor cores; the PPO step too where num_obs is in (144, 160] — the 42-joint set, O = 145 / A = 42;
+ *      for the shapes in between flyb_ppo_grad / flyb_ppo_step run the exact-fp32 CUDA-core kernels and only Adam's
+ *      in-place refresh touches the weight stream).
  *      The buffer also holds, behind the slabs, the parameter -> slab index flyb_pack_weights builds.
  *      flyb_pack_weights must be re-run whenever `params` changes by other hands (flyb_ppo_apply / flyb_ppo_step
  *      keep a given wpack in step themselves).

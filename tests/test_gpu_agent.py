@@ -354,7 +354,8 @@ def test_three_minibatch_steps_match_reference_golden():
     assert ill <= 0.01 * 69587, f"{ill} near-zero-gradient elements moved differently"
 
 
-@pytest.mark.parametrize("o,a,rows", [(145, 42, 1000), (73, 18, 32768), (73, 18, 100)])
+@pytest.mark.parametrize("o,a,rows", [(145, 42, 1000), (145, 42, 32768 + 5), (145, 42, 7), (73, 18, 32768), (73, 18, 100),
+                                      (100, 27, 300)])
 def test_ppo_grad_matches_oracle_autograd_other_shapes(o, a, rows):
     gen = torch.Generator().manual_seed(rows + o)
     p0 = fo.init_params(o, a, seed=3)
