@@ -871,8 +871,17 @@ env_step_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_const
   fin.e = y.env; fin.st = &stab; fin.tables_built = false; fin.parity = 0u; fin.tb_ = 172;
   fin.force_bulk = a.pre_src != nullptr ? 1 : 0; fin.force_phase = 0u; fin.first_tile = true;
   if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[190] = clock64();   // kernel entry
+  // debug: every CTA's entry / exit on the GLOBAL timer (ns), slots [192 + 2 b, 193 + 2 b]: launch skew, slow CTAs
+  unsigned long long t_in = 0;
+  if (a.trace != nullptr && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_in));
   tcm::forward_persistent<true, false>(net, a, fin);
   if (a.trace != nullptr && blockIdx.x == 0 && threadIdx.x == 0) a.trace[191] = clock64();       // kernel exit
+  if (a.trace != nullptr && threadIdx.x == 0 && blockIdx.x < 148) {
+    unsigned long long t_out;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_out));
+    a.trace[192 + 2 * blockIdx.x] = t_in;
+    a.trace[193 + 2 * blockIdx.x] = t_out;
+  }
 }
 #endif   // !FLYB_TC_WIDE
 

@@ -113,7 +113,7 @@ const char* flyb_last_error(void);
 int flyb_device_count(void);
 
 int flyb_net_layout(int32_t num_obs, int32_t num_act, FlybNetLayout* out);
-/* Debug aid: device buffer (>= 160 uint64) that CTA 0 of the tensor-core kernels fills with clock64() marks of its
+/* Debug aid: device buffer (>= 488 uint64) that CTA 0 of the tensor-core kernels fills with clock64() marks of its
  * MMA / epilogue hand-offs; NULL (default) switches tracing off. */
 int flyb_debug_set_trace(void* dev_buffer);
 

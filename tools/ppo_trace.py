@@ -24,7 +24,7 @@ agent.make_data()
 for _ in range(3):
     agent._minibatch(0, agent.mini_chunk_size)
 torch.cuda.synchronize()
-trace = torch.zeros(192, dtype=torch.int64, device=dev)
+trace = torch.zeros(192 + 2 * 148, dtype=torch.int64, device=dev)
 _lib.check(agent.lib.flyb_debug_set_trace(trace.data_ptr()))
 agent._minibatch(0, agent.mini_chunk_size)
 torch.cuda.synchronize()

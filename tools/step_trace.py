@@ -19,7 +19,7 @@ for _ in range(2):
     agent.collect_rollout(use_graph=False)
 torch.cuda.synchronize()
 for rep in range(3):
-    trace = torch.zeros(192, dtype=torch.int64, device=dev)
+    trace = torch.zeros(192 + 2 * 148, dtype=torch.int64, device=dev)
     _lib.check(agent.lib.flyb_debug_set_trace(trace.data_ptr()))
     agent._fused_step(1 + rep)
     torch.cuda.synchronize()
@@ -31,3 +31,15 @@ for rep in range(3):
     print("MMA warp   :", [x - t0 for x in t[:64] if x > 0])
     print("epilogue w0:", [x - t0 for x in t[64:128] if x > 0])
     print("finaliser  :", [x - t0 for x in t[128:160] if x > 0])
+    ins = [t[192 + 2 * b] for b in range(148) if t[192 + 2 * b] > 0]
+    outs = [t[193 + 2 * b] for b in range(148) if t[193 + 2 * b] > 0]
+    if ins:
+        g0 = min(ins)
+        srt = lambda v: sorted(x - g0 for x in v)
+        si, so = srt(ins), srt(outs)
+        q = lambda v, f: v[min(len(v) - 1, int(f * len(v)))]
+        print(f"per-CTA global timer, ns after the first CTA's entry ({len(ins)} CTAs): entry min/med/max "
+              f"{si[0]}/{q(si, .5)}/{si[-1]}   exit min/med/p90/max {so[0]}/{q(so, .5)}/{q(so, .9)}/{so[-1]}   "
+              f"CTA 0: entry {t[192] - g0} exit {t[193] - g0}")
+        durs = sorted(t[193 + 2 * b] - t[192 + 2 * b] for b in range(148) if t[192 + 2 * b] > 0)
+        print(f"per-CTA duration ns min/med/p90/max {durs[0]}/{q(durs, .5)}/{q(durs, .9)}/{durs[-1]}")

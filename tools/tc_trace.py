@@ -17,7 +17,7 @@ agent = fb.PPO(args)
 for i in range(8):
     agent._step_kernels(i)
 torch.cuda.synchronize()
-trace = torch.zeros(192, dtype=torch.int64, device=dev)
+trace = torch.zeros(192 + 2 * 148, dtype=torch.int64, device=dev)
 _lib.check(agent.lib.flyb_debug_set_trace(trace.data_ptr()))
 agent._step_kernels(0)
 torch.cuda.synchronize()
