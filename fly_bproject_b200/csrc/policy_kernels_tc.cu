@@ -480,6 +480,7 @@ struct StepFinal : ActFinal {
     int* cnt_s = reinterpret_cast<int*>(force_s + TM * FORCE_VALS);   // legs | at_limit << 8 | abdomen_hit << 16
     float* sq_s = reinterpret_cast<float*>(cnt_s + TM);
     tcm::epi_bar_sync();   // the previous tile's pi() is done with s.out; its ring store has drained s.obs (obs_consumed)
+    emark();   // [1] all eight warps are here
     if (!tables_built) {
       if (tid < FORCE_VALS) {
         const int r = tid / 3;
@@ -495,6 +496,7 @@ struct StepFinal : ActFinal {
       tables_built = true;
       tcm::epi_bar_sync();
     }
+    emark();   // [2] tables built
     // ---- every global load of the tile is issued before the first dependent shared-memory store
     const int en = tid >> 1, qd = tid & 1;             // two threads per env for the gathers
     const bool e_ok = en < nrows;
@@ -526,6 +528,7 @@ struct StepFinal : ActFinal {
           reset_in[p] = reset[row0 + p * 64 + tid];
         }
     }
+    emark();   // [3] root / scalar loads issued
     constexpr int FITER = (FORCE_VALS + 1) / 2;   // 17
     float fv[FITER];
     if (!bulk) {
@@ -562,7 +565,7 @@ struct StepFinal : ActFinal {
         if (k >= A) { k -= A; ++el; }
       }
     }
-    emark();   // [1] every load issued
+    emark();   // [4] every load issued
     if (bulk) {   // the force blocks have landed: pick this env's 33 values, then hand the region back
       tc::mbar_wait(s.obs_full, force_phase);
       force_phase ^= 1u;
@@ -603,7 +606,7 @@ struct StepFinal : ActFinal {
       if (e_ok && rc < FORCE_VALS) force_s[en * FORCE_VALS + rc] = fv[it];
     }
     tcm::epi_bar_sync();
-    emark();   // [2] loads consumed, tile staged
+    emark();   // [5] loads consumed, tile staged
 
     // ---- per-env math: four roles (warp pairs), each over the tile's two 64-env halves.  role 0: potential, heading /
     //      up projections, later reward + termination; 1: local velocities; 2: Euler angles; 3: contact flags, sums
@@ -669,7 +672,7 @@ struct StepFinal : ActFinal {
       }
     }
     tcm::epi_bar_sync();
-    emark();   // [3] per-env math done
+    emark();   // [6] per-env math done
     if (role == 0) {
       float my_reward = 0.0f;
 #pragma unroll 1
@@ -754,7 +757,7 @@ struct StepFinal : ActFinal {
         }
       }
     }
-    emark();   // [4] reward + masks done, rows visible to the bulk stores
+    emark();   // [7] reward + masks done, rows visible to the bulk stores
   }
 
   FLYB_D void begin_tile(const tcm::Smem& s, long long row0, int r, int nrows) {

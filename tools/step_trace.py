@@ -27,7 +27,7 @@ for rep in range(3):
     t = trace.cpu().tolist()
     t0 = t[190]
     print(f"--- launch {rep}: kernel entry -> exit {t[191] - t0} cycles (thread 0 of CTA 0)")
-    print("env phase [entered, loads issued, tile staged, math done, reward+masks done]:", [x - t0 for x in t[172:190] if x > 0])
+    print("env phase [entered, warps met, tables built, root+scalars issued, all loads issued, tile staged, math done, reward+masks done]:", [x - t0 for x in t[172:190] if x > 0])
     print("MMA warp   :", [x - t0 for x in t[:64] if x > 0])
     print("epilogue w0:", [x - t0 for x in t[64:128] if x > 0])
     print("finaliser  :", [x - t0 for x in t[128:160] if x > 0])
