@@ -291,6 +291,7 @@ def run_own(args, cfg):
     roll_ms = timed_blocks(lambda: agent.collect_rollout(use_graph=True), max(K, 10))
     upd_ms = timed_blocks(lambda: agent.update(use_graph=True), max(2, min(K, 10)))
     clocks = sampler.stop()
+    reset_fraction = float(env.reset_count.item()) / n     # envs flagged by the rollout's last step (termination mix)
     roll_value = env_steps / (roll_ms * 1e-3)
     upd_value = n_minibatches * rows_mb * world / (upd_ms * 1e-3)
     step_us = roll_ms * 1e3 / horizon                              # one env step INSIDE the rollout graph
@@ -476,6 +477,7 @@ def run_own(args, cfg):
             "roofline": roofline, "kernels": kernels,
             "rollout": {"metric": "fused_env_steps_per_sec", "value": roll_value, "unit": UNIT, "ms_per_rollout": roll_ms,
                         "us_per_env_step": step_us, "launches_per_rollout": launches_rollout,
+                        "reset_fraction_last_step": reset_fraction,
                         "includes": ("obs + reward + reset + id compaction + policy act + action scaling + reset "
                                      "bookkeeping, ") + ("one launch per env step" if fused else "two launches per env step")},
             "update": {"metric": "ppo_update_samples_per_sec", "value": upd_value, "unit": "samples/s",

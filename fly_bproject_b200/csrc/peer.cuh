@@ -53,16 +53,21 @@ FLYB_D float ld_relaxed_sys(const float* p) {
   return v;
 }
 
-// Entry i of this rank's gradient -> slot [parity][rank] of every rank (own one included), followed by a system-scope
-// fence of the WRITING thread: the stores are ordered before anything this thread (and, through the kernel boundary,
-// the flag-raising kernel that follows) does next, whatever the interconnect.  The fence costs nothing measurable: the
-// kernel cannot complete before its remote stores are acknowledged anyway.
+// Entry i of this rank's gradient -> slot [parity][rank] of every rank (own one included): posted NVLink stores.
 FLYB_D void peer_push(const PeerView& pv, uint32_t parity, int i, float val) {
   const size_t at = ((size_t)parity * pv.world + pv.rank) * pv.total_pad + i;
 #pragma unroll
   for (int r = 0; r < FLYB_MAX_PEERS; ++r)
     if (r < pv.world) pv.slots[r][at] = val;
-  __threadfence_system();
+}
+// Called by EVERY thread of a CTA after its last peer_push: a CTA barrier followed by one system-scope fence, which is
+// cumulative over the pushes the barrier ordered before it.  The pushed data is thereby ordered before anything that
+// follows this CTA — the kernel boundary, and behind it the flag-raising kernel — whatever the interconnect does.
+// (A fence per pushing thread, the first form of this, cost 5-7 us per optimiser step at 8 ranks: every one of them
+// waits for its own eight round trips.  One per CTA is not measurable.)
+FLYB_D void peer_push_fence() {
+  __syncthreads();
+  if (threadIdx.x == 0) __threadfence_system();
 }
 
 // Raise this rank's flag of epoch `want` on every rank.  Called by ONE CTA of the kernel that FOLLOWS the pushing

@@ -1027,11 +1027,12 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
         }
         const float g = (acc[0] + acc[1]) + (acc[2] + acc[3]);
         t.grad[i] = g;
-        if (t.has_peers) peer_push(t.pv, epoch & 1u, i, g);   // posted NVLink stores + system fence of the writer
+        if (t.has_peers) peer_push(t.pv, epoch & 1u, i, g);   // posted NVLink stores
         else sq = fmaf(g, g, sq);
       }
     }
     if (t.has_peers) {
+      peer_push_fence();
       // every push of this rank is fenced -> raise this rank's flag everywhere, wait for everybody's, add the slots in
       // rank order (bit-identical on every rank)
       grid_barrier(g_dw_grid_sync, gridDim.x);
@@ -1143,6 +1144,7 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
       if ((threadIdx.x & 31) == 0) s_sq[threadIdx.x >> 5] = sq;
     }
   }
+  if (PEERS) peer_push_fence();
   if (a.sq_part) {
     __syncthreads();
     if (threadIdx.x == 0) {

@@ -250,7 +250,7 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  * others' buffers with flyb_peer_open and fills a FlybPeerGroup.  With a group,
  *   flyb_ppo_grad  : its last kernel (the fixed-order reduction of the per-CTA partial gradients) stores every
  *                    gradient entry straight into slot [epoch & 1][rank] of EVERY rank's buffer (posted NVLink
- *                    writes, each writing thread ending with a system-scope fence);
+ *                    writes; every pushing CTA ends with a barrier + one system-scope fence);
  *   flyb_ppo_apply : its first kernel (global norm) raises this rank's flag on every rank, waits for all ranks'
  *                    flags of this epoch, sums the `world` slots in rank order (bit-identical on every rank), writes
  *                    `grad` and goes on as usual; the Adam kernel closes the epoch.

@@ -38,6 +38,8 @@ def main():
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":     # the banner goes to stdout at VERSION level
+            os.environ["NCCL_DEBUG"] = "WARN"
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device(dev))
     pk = bench.peaks()
