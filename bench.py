@@ -402,14 +402,25 @@ def run_own(args, cfg):
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         traffic = json.load(open(tpath))
-    # dominant kernel of the rollout: the (fused) env step, timed live inside the rollout graph
-    dom = "env_step_fused" if fused else ("policy_act" if kt["policy_act"] >= kt["post_physics"] else "post_physics")
-    roofline = dict(kernels["env_step_in_rollout"] if fused else kernels[dom])
-    roofline.update({"kernel": "env_step_tc_kernel" if fused else dom, "traffic": traffic.get(dom),
-                     "algorithmic_per_launch": {"flops": wm["flops_act"] * n, "bytes": wm["bytes_step"] * n},
-                     "peak_source": pk["tf_src" if roofline["bound"] == "tensor" else "hbm_src"] +
-                     (" (bf16 sustained: timed inside a long step)" if roofline["bound"] != "hbm" else "")})
+    # Dominant work of the bench step (the training iteration): the optimiser step — 5 x (T/mc - 1) of them are ~90 % of
+    # the iteration, and within one the forward/backward chain kernel and the weight-gradient kernel are ~50 % / ~44 %
+    # of the kernel time (ncu launch list under profiles/).  Timed live: CUDA events over a captured graph of 8 steps.
+    roofline = dict(kernels["ppo_minibatch_step"])
+    roofline.update({
+        "kernel": ("ppo_fwd_bwd_tc_kernel + ppo_dw_tc_kernel (+ ppo_reduce_tc_kernel, ppo_adam_kernel): one optimiser step"
+                   if tc_path else "ppo_fwd_bwd_kernel + ppo_dw_kernel (+ reduce, norm, Adam): one optimiser step"),
+        "traffic": traffic.get("ppo_minibatch_step"),
+        "algorithmic_per_launch": {"flops": wm["flops_update"] * rows_mb, "samples": rows_mb},
+        "share_of_bench_step": n_minibatches * kt["ppo_minibatch_step"] / iter_ms,
+        "peak_source": pk["tf_src"] + " (bf16 sustained: timed inside a long step)"})
     roofline.pop("ms", None)
+    roofline.pop("note", None)
+    # the rollout's dominant kernel: the (fused) env step, timed live inside the rollout graph
+    dom = "env_step_fused" if fused else ("policy_act" if kt["policy_act"] >= kt["post_physics"] else "post_physics")
+    roofline_rollout = dict(kernels["env_step_in_rollout"] if fused else kernels[dom])
+    roofline_rollout.update({"kernel": "env_step_tc_kernel" if fused else dom, "traffic": traffic.get(dom),
+                             "algorithmic_per_launch": {"flops": wm["flops_act"] * n, "bytes": wm["bytes_step"] * n}})
+    roofline_rollout.pop("ms", None)
 
     # ---------------- e2e: public API with HOST state buffers, H2D + D2H inside the timed region
     n_host = 4
@@ -474,7 +485,7 @@ def run_own(args, cfg):
                     "env_steps": ke, "ms_per_env_step": e2e_ms / ke, "h2d_gbs_per_rank": h2d_bytes * ke / e2e_ms / 1e6,
                     "api": "PPO.run() per env-step (the T-th call runs the update): state tensors H2D from pinned host "
                            "memory; obs, reward, reset mask, compacted ids + count and DOF targets read back D2H"},
-            "roofline": roofline, "kernels": kernels,
+            "roofline": roofline, "roofline_rollout": roofline_rollout, "kernels": kernels,
             "rollout": {"metric": "fused_env_steps_per_sec", "value": roll_value, "unit": UNIT, "ms_per_rollout": roll_ms,
                         "us_per_env_step": step_us, "launches_per_rollout": launches_rollout,
                         "reset_fraction_last_step": reset_fraction,

@@ -17,6 +17,13 @@ unsigned long long peer_timeout_ns(const FlybPeerGroup& g) {
   return (unsigned long long)(env_s * 1e9);
 }
 
+int peer_fence_mode() {
+  const char* e = getenv("FLYB_PEER_FENCE");   // read per call: one process can A/B the forms
+  if (e && e[0] == 'l') return 1;
+  if (e && e[0] == 'n') return 2;
+  return 0;
+}
+
 int peer_validate(const FlybPeerGroup* g, int total) {
   FLYB_REQUIRE(g->world >= 1 && g->world <= FLYB_MAX_PEERS, "FlybPeerGroup: world %d out of range", g->world);
   FLYB_REQUIRE(g->rank >= 0 && g->rank < g->world, "FlybPeerGroup: rank %d out of range", g->rank);

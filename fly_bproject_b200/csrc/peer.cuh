@@ -11,6 +11,8 @@ struct PeerView {   // FlybPeerGroup resolved into typed pointers (kernel argume
   uint32_t* flags[FLYB_MAX_PEERS];     // flags[r]: [FLYB_MAX_PEERS] in rank r's buffer
   uint32_t* epoch;                     // own: exchanges completed by this rank
   uint32_t* error;                     // own: sticky error word (0 = fine, 1 + r = gave up waiting for rank r)
+  uint32_t* push_count;                // own: pushing CTAs that have finished (fence mode "last")
+  int fence_mode;                      // 0: one system fence per pushing CTA; 1: one by the LAST pushing CTA; 2: none
   unsigned long long timeout_ns;       // how long peer_wait_all spins before it gives up
   unsigned long long* stamp;           // own: 8 x %globaltimer marks of the last exchange (flyb_peer_stamps)
 };
@@ -18,6 +20,7 @@ struct PeerView {   // FlybPeerGroup resolved into typed pointers (kernel argume
 inline size_t peer_slots_bytes(int total_pad, int world) { return (size_t)2 * world * total_pad * sizeof(float); }
 constexpr size_t PEER_CTRL_BYTES = 256;   // flags[8], epoch, error, (pad), 8 x u64 stamps at byte 64
 unsigned long long peer_timeout_ns(const FlybPeerGroup& g);   // peer.cu
+int peer_fence_mode();                                        // peer.cu (FLYB_PEER_FENCE = cta | last | none)
 
 inline PeerView make_peer_view(const FlybPeerGroup& g) {
   PeerView v{};
@@ -29,6 +32,8 @@ inline PeerView make_peer_view(const FlybPeerGroup& g) {
   }
   v.epoch = v.flags[g.rank] + FLYB_MAX_PEERS;
   v.error = v.epoch + 1;
+  v.push_count = v.epoch + 2;
+  v.fence_mode = peer_fence_mode();
   v.timeout_ns = peer_timeout_ns(g);
   v.stamp = (unsigned long long*)(v.flags[g.rank] + 16);
   return v;
@@ -60,14 +65,27 @@ FLYB_D void peer_push(const PeerView& pv, uint32_t parity, int i, float val) {
   for (int r = 0; r < FLYB_MAX_PEERS; ++r)
     if (r < pv.world) pv.slots[r][at] = val;
 }
-// Called by EVERY thread of a CTA after its last peer_push: a CTA barrier followed by one system-scope fence, which is
-// cumulative over the pushes the barrier ordered before it.  The pushed data is thereby ordered before anything that
-// follows this CTA — the kernel boundary, and behind it the flag-raising kernel — whatever the interconnect does.
-// (A fence per pushing thread, the first form of this, cost 5-7 us per optimiser step at 8 ranks: every one of them
-// waits for its own eight round trips.  One per CTA is not measurable.)
-FLYB_D void peer_push_fence() {
+// Called by EVERY thread of a CTA after its last peer_push.  The pushed data must be ordered before the flag the NEXT
+// kernel raises, and not by the kernel boundary alone (round-1 review).  Three forms, FLYB_PEER_FENCE:
+//   cta  (default)  CTA barrier + one system-scope fence per pushing CTA: cumulative over the pushes the barrier ordered
+//                   before it;
+//   last            CTA barrier + gpu-scope fence + counter; the LAST pushing CTA issues the one system-scope fence,
+//                   cumulative over every CTA it observed through the counter;
+//   none            nothing: the kernel boundary and the flag-raising kernel's own system fence (round 1's form).
+FLYB_D void peer_push_fence(const PeerView& pv) {
+  if (pv.fence_mode == 2) return;
   __syncthreads();
-  if (threadIdx.x == 0) __threadfence_system();
+  if (threadIdx.x == 0) {
+    if (pv.fence_mode == 0) {
+      __threadfence_system();
+    } else {
+      __threadfence();
+      if (atomicAdd(pv.push_count, 1u) == gridDim.x - 1u) {
+        *pv.push_count = 0u;
+        __threadfence_system();
+      }
+    }
+  }
 }
 
 // Raise this rank's flag of epoch `want` on every rank.  Called by ONE CTA of the kernel that FOLLOWS the pushing

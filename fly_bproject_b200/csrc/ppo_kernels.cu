@@ -352,7 +352,7 @@ ppo_reduce_kernel(const float* __restrict__ dw_part, int splits, int total, floa
     grad[i] = g;
     if (PEERS) peer_push(pv, epoch & 1u, i, g);
   }
-  if (PEERS) peer_push_fence();
+  if (PEERS) peer_push_fence(pv);
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
     float x = 0.0f, y = 0.0f;
     for (long long tt = threadIdx.x; tt < ntiles; tt += 32) {

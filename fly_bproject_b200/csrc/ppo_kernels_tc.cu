@@ -1032,7 +1032,7 @@ ppo_dw_tc_kernel(const __grid_constant__ DwArgs a) {
       }
     }
     if (t.has_peers) {
-      peer_push_fence();
+      peer_push_fence(t.pv);
       // every push of this rank is fenced -> raise this rank's flag everywhere, wait for everybody's, add the slots in
       // rank order (bit-identical on every rank)
       grid_barrier(g_dw_grid_sync, gridDim.x);
@@ -1144,7 +1144,7 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
       if ((threadIdx.x & 31) == 0) s_sq[threadIdx.x >> 5] = sq;
     }
   }
-  if (PEERS) peer_push_fence();
+  if (PEERS) peer_push_fence(pv);
   if (a.sq_part) {
     __syncthreads();
     if (threadIdx.x == 0) {
