@@ -309,10 +309,11 @@ int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* param
                    void* wpack, const FlybPeerGroup* peers, void* stream);
 /* Single-GPU optimiser step in one call: flyb_ppo_grad followed by flyb_ppo_apply(grad_scale = 1) with nothing in
  * between, which lets the library drop two launches: the gradient reduction also takes the squared norm and counts
- * the step, and Adam refreshes `wpack` in place through the index flyb_pack_weights built.  On the tensor-core path
- * the whole step is TWO launches: the forward/backward chain, and the weight-gradient kernel whose tail — behind grid
- * barriers, the kernel is launched cooperatively — sums the per-CTA partials in the fixed order of the stand-alone
- * reduction (bit-identical gradient), takes the norm and runs clip + Adam (FLYB_PPO_TAIL=0: the four-launch form).
+ * the step, and Adam refreshes `wpack` in place through the index flyb_pack_weights built: 4 launches (forward/backward
+ * chain, weight gradients, reduce, clip + Adam).  FLYB_PPO_TAIL=1 selects a two-launch form: the weight-gradient kernel
+ * launched cooperatively, its tail — behind grid barriers — summing the per-CTA partials in the fixed order of the
+ * stand-alone reduction (bit-identical gradient), taking the norm and running clip + Adam; measured 3 us slower per
+ * step than the four launches, hence opt-in.
  * Same results as the two calls up to the association of the norm's partial sums.  `grad` ends as p.grad after
  * clipping, as with flyb_ppo_apply. */
 int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack, const float* obs,
@@ -320,7 +321,8 @@ int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params
                   const float* action_var, int64_t rows, float* grad, float* loss, float* exp_avg, float* exp_avg_sq,
                   int64_t* step, float* grad_norm_out, void* workspace, void* stream);
 
-/* The same single call for a data-parallel run: flyb_ppo_grad + gradient sum over the peer group + flyb_ppo_apply in
+/* Opt-in (measured slower than flyb_ppo_grad + flyb_ppo_apply, which stay the default): the same single call for a
+ * data-parallel run: flyb_ppo_grad + gradient sum over the peer group + flyb_ppo_apply in
  * TWO launches — the weight-gradient kernel (launched cooperatively) reduces its partials behind a grid barrier, pushes
  * the result to every rank, raises / waits for the flags, adds the slots in rank order, takes the norm and runs Adam.
  * Same protocol and results as the two calls (FlybPeerGroup); needs the tensor-core path (wpack) and a peer group. */
