@@ -1104,43 +1104,60 @@ struct ReduceArgs {
   float* sq_part;   // nullable: [gridDim.x] sums of squares of this CTA's entries (flyb_ppo_step: saves the norm kernel)
   long long* step;  // with sq_part: Adam's step counter, += 1 (the norm kernel's other job)
 };
-constexpr int RED_ELEMS = 64, RED_GROUPS = 4;   // 256 threads: 64 gradient entries x 4 interleaved partial groups
+// 256 threads: 64 QUADS of gradient entries (four consecutive floats, one 128-bit load per partial) x 4 interleaved
+// partial groups.  Per entry the association is what it was with one entry per thread — group g adds partials g, g + 4,
+// ... in order, then (s0 + s1) + (s2 + s3) — so the gradient bits do not depend on the vector width.
+constexpr int RED_QUADS = 64, RED_ELEMS = 4 * RED_QUADS, RED_GROUPS = 4;
 template <bool PEERS>
-__global__ void __launch_bounds__(RED_ELEMS * RED_GROUPS)
+__global__ void __launch_bounds__(RED_QUADS * RED_GROUPS)
 ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restrict__ dw_part,
                      const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss,
                      const __grid_constant__ PeerView pv) {
-  __shared__ float s_acc[RED_GROUPS][RED_ELEMS];
+  __shared__ float4 s_acc[RED_GROUPS][RED_QUADS];
   __shared__ float s_sq[2];
-  const int e = threadIdx.x & (RED_ELEMS - 1), pg = threadIdx.x / RED_ELEMS;
-  const int i = blockIdx.x * RED_ELEMS + e;
+  const int e = threadIdx.x & (RED_QUADS - 1), pg = threadIdx.x / RED_QUADS;
+  const int i = blockIdx.x * RED_ELEMS + 4 * e;      // first entry of this thread's quad (total is a multiple of 4)
   uint32_t epoch = 0;
   if (PEERS) {
     epoch = *(volatile const uint32_t*)pv.epoch;   // bumped by ppo_adam_kernel, i.e. after this exchange
     if (blockIdx.x == 0 && threadIdx.x == 0) pv.stamp[0] = global_ns();
   }
-  float acc = 0.0f;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  bool valid[4] = {false, false, false, false};
   if (i < a.total) {
-    bool valid = false;
 #pragma unroll
-    for (int sg = 0; sg < 12; ++sg) valid = valid || (i >= a.off[sg] && i < a.off[sg] + a.size[sg]);
-    if (valid) {   // group pg sums partials pg, pg + 4, ... in order; the groups are combined in a fixed order below
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int sg = 0; sg < 12; ++sg) valid[j] = valid[j] || (i + j >= a.off[sg] && i + j < a.off[sg] + a.size[sg]);
+    if (valid[0] || valid[1] || valid[2] || valid[3]) {
+      const float4* src = reinterpret_cast<const float4*>(dw_part + i);
+      const size_t stride4 = (size_t)a.total / 4;
 #pragma unroll 8
-      for (int p = pg; p < a.nparts; p += RED_GROUPS) acc += dw_part[(size_t)p * a.total + i];
+      for (int p = pg; p < a.nparts; p += RED_GROUPS) {
+        const float4 v = src[(size_t)p * stride4];
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
     }
   }
   s_acc[pg][e] = acc;
   __syncthreads();
   if (pg == 0) {   // warps 0 and 1
-    float g = 0.0f;
+    float g[4] = {0.f, 0.f, 0.f, 0.f};
     if (i < a.total) {
-      g = (s_acc[0][e] + s_acc[1][e]) + (s_acc[2][e] + s_acc[3][e]);
-      grad[i] = g;
+      const float4 s0 = s_acc[0][e], s1 = s_acc[1][e], s2 = s_acc[2][e], s3 = s_acc[3][e];
+      g[0] = valid[0] ? (s0.x + s1.x) + (s2.x + s3.x) : 0.0f;
+      g[1] = valid[1] ? (s0.y + s1.y) + (s2.y + s3.y) : 0.0f;
+      g[2] = valid[2] ? (s0.z + s1.z) + (s2.z + s3.z) : 0.0f;
+      g[3] = valid[3] ? (s0.w + s1.w) + (s2.w + s3.w) : 0.0f;
+      *reinterpret_cast<float4*>(grad + i) = make_float4(g[0], g[1], g[2], g[3]);
       // posted NVLink stores into this rank's slot on every rank; the flags are raised by the next kernel (peer.cuh)
-      if (PEERS) peer_push(pv, epoch & 1u, i, g);
+      if (PEERS) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) peer_push(pv, epoch & 1u, i + j, g[j]);
+      }
     }
     if (a.sq_part) {
-      const float sq = warp_sum(g * g);
+      const float sq = warp_sum(((g[0] * g[0] + g[1] * g[1]) + g[2] * g[2]) + g[3] * g[3]);
       if ((threadIdx.x & 31) == 0) s_sq[threadIdx.x >> 5] = sq;
     }
   }
@@ -1298,10 +1315,10 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
     fuse->sq_parts = red_grid;
   }
   if (peers)
-    ppo_reduce_tc_kernel<true><<<red_grid, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+    ppo_reduce_tc_kernel<true><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
                                                                             make_peer_view(*peers));
   else
-    ppo_reduce_tc_kernel<false><<<red_grid, RED_ELEMS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+    ppo_reduce_tc_kernel<false><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
                                                                              PeerView{});
   FLYB_LAUNCH_CHECK("ppo_reduce_tc_kernel");
   return FLYB_OK;
