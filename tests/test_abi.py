@@ -64,6 +64,22 @@ def test_net_layout_and_argument_errors(built_lib):
     assert lib.flyb_env_pre_physics(C.byref(cfg), *([None] * 10)) == -1
 
 
+def test_tensor_core_shapes(built_lib):
+    """flyb_wpack_bytes (host-side, no GPU needed): both compiled shapes of the tcgen05 path announce themselves — the
+    18-joint actuation (O = 73, A = 18) and the 42-joint set of BASELINE configs[3] (O = 145, A = 42) — and shapes beyond
+    the wide layout report 0 (-> exact-fp32 CUDA-core kernels)."""
+    from fly_bproject_b200 import _lib
+    lib = _lib.lib()
+    sizes = {}
+    for o, a in [(73, 18), (145, 42), (100, 27), (37, 6), (163, 48), (145, 49)]:
+        lay = _lib.NetLayout()
+        assert lib.flyb_net_layout(o, a, C.byref(lay)) == 0
+        sizes[(o, a)] = lib.flyb_wpack_bytes(C.byref(lay))
+    assert sizes[(73, 18)] > 0 and sizes[(145, 42)] > sizes[(73, 18)]
+    assert sizes[(100, 27)] > 0 and sizes[(37, 6)] > 0           # anything up to O = 160 / A = 48 runs the wide forward
+    assert sizes[(163, 48)] == 0 and sizes[(145, 49)] == 0
+
+
 def test_product_path_fails_loudly_without_cuda(built_lib):
     import torch
     if torch.cuda.is_available():
