@@ -65,6 +65,13 @@ FLYB_D void peer_push(const PeerView& pv, uint32_t parity, int i, float val) {
   for (int r = 0; r < FLYB_MAX_PEERS; ++r)
     if (r < pv.world) pv.slots[r][at] = val;
 }
+// Four consecutive entries (i a multiple of 4) as ONE 128-bit store per rank: a warp's push is 512 contiguous bytes.
+FLYB_D void peer_push4(const PeerView& pv, uint32_t parity, int i, const float4& val) {
+  const size_t at = ((size_t)parity * pv.world + pv.rank) * pv.total_pad + i;   // total_pad % 64 == 0: 16-byte aligned
+#pragma unroll
+  for (int r = 0; r < FLYB_MAX_PEERS; ++r)
+    if (r < pv.world) *reinterpret_cast<float4*>(pv.slots[r] + at) = val;
+}
 // Called by EVERY thread of a CTA after its last peer_push.  The pushed data must be ordered before the flag the NEXT
 // kernel raises, and not by the kernel boundary alone (round-1 review).  Three forms, FLYB_PEER_FENCE:
 //   last (default)  CTA barrier + gpu-scope fence + counter; the LAST pushing CTA issues the one system-scope fence,

@@ -1151,10 +1151,7 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
       g[3] = valid[3] ? (s0.w + s1.w) + (s2.w + s3.w) : 0.0f;
       *reinterpret_cast<float4*>(grad + i) = make_float4(g[0], g[1], g[2], g[3]);
       // posted NVLink stores into this rank's slot on every rank; the flags are raised by the next kernel (peer.cuh)
-      if (PEERS) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) peer_push(pv, epoch & 1u, i + j, g[j]);
-      }
+      if (PEERS) peer_push4(pv, epoch & 1u, i, make_float4(g[0], g[1], g[2], g[3]));
     }
     if (a.sq_part) {
       const float sq = warp_sum(((g[0] * g[0] + g[1] * g[1]) + g[2] * g[2]) + g[3] * g[3]);
