@@ -428,10 +428,20 @@ def run_own(args, cfg):
     live = {k: torch.empty_like(v) for k, v in env.state.pool[0].items()}
     step_no = [0]
 
+    # The caller's loop is double-buffered over the two PCIe directions: the DOF targets, reset mask, ids and count (what a
+    # host-resident simulator needs before it can advance) are read back on the compute stream and waited for; the
+    # observation / reward read-back (4.8 MB of the 6.2) rides a second stream UNDER the next step's H2D state copy, and
+    # the kernels that overwrite obs_buf / reward_buf wait for it (wait_event at the end of h2d).  Every byte still moves
+    # inside the timed region, every step.
+    side = torch.cuda.Stream()
+    ev_step, ev_side = torch.cuda.Event(), torch.cuda.Event()
+    ev_side.record(side)
+
     def h2d(src):
         hp = host_pool[step_no[0] % n_host]
         for k in ("root", "dof_state", "force"):
             live[k].copy_(hp[k], non_blocking=True)
+        torch.cuda.current_stream().wait_event(ev_side)    # post_physics may not overwrite obs / reward before they left
         step_no[0] += 1
 
     a2 = fb.make_args(num_envs=n, sim_device=dev, horizon=horizon, verbose=False, seed=99, asset=cfg["asset"],
@@ -442,13 +452,24 @@ def run_own(args, cfg):
     env2 = agent2.env
     back = {"obs": env2.obs_buf, "reward": env2.reward_buf, "reset": env2.reset_buf, "reset_ids": env2.reset_ids,
             "reset_count": env2.reset_count, "dof_targets": env2.dof_targets}
-    host_back = {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in back.items()}
+    late = ("obs", "reward")                               # written by post_physics only (fly.py:676-681)
+    host_back = [{k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in back.items()} for _ in range(2)]
 
     def e2e_step():
+        hb = host_back[step_no[0] & 1]
         agent2.run()                                       # the T-th call of a rollout also runs the update
+        ev_side.synchronize()                              # the PREVIOUS step's obs / reward are on the host by now
+        main = torch.cuda.current_stream()
+        ev_step.record(main)
+        side.wait_event(ev_step)
+        with torch.cuda.stream(side):
+            for k in late:
+                hb[k].copy_(back[k], non_blocking=True)
+            ev_side.record(side)
         for k, v in back.items():
-            host_back[k].copy_(v, non_blocking=True)
-        torch.cuda.current_stream().synchronize()          # the caller consumes the step's result
+            if k not in late:
+                hb[k].copy_(v, non_blocking=True)
+        main.synchronize()                                 # the simulator consumes targets / reset ids before it advances
 
     for _ in range(horizon):                               # one warm-up iteration (includes an update)
         e2e_step()
@@ -457,6 +478,7 @@ def run_own(args, cfg):
     e0.record()
     for _ in range(ke):
         e2e_step()
+    torch.cuda.current_stream().wait_event(ev_side)        # the last read-back ends inside the timed region
     e1.record()
     barrier()
     e2e_ms = max_over_ranks(e0.elapsed_time(e1))
@@ -484,7 +506,8 @@ def run_own(args, cfg):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "env_steps": ke, "ms_per_env_step": e2e_ms / ke, "h2d_gbs_per_rank": h2d_bytes * ke / e2e_ms / 1e6,
                     "api": "PPO.run() per env-step (the T-th call runs the update): state tensors H2D from pinned host "
-                           "memory; obs, reward, reset mask, compacted ids + count and DOF targets read back D2H"},
+                           "memory; DOF targets, reset mask, compacted ids + count read back D2H and waited for, obs + reward read back "
+                           "on a second stream under the next step's H2D (double-buffered pinned buffers)"},
             "roofline": roofline, "roofline_rollout": roofline_rollout, "kernels": kernels,
             "rollout": {"metric": "fused_env_steps_per_sec", "value": roll_value, "unit": UNIT, "ms_per_rollout": roll_ms,
                         "us_per_env_step": step_us, "launches_per_rollout": launches_rollout,

@@ -98,7 +98,9 @@ def reward_reset(obs: Tensor, reset_buf: Tensor, progress_buf: Tensor, actions: 
     """reference fly.py:685-768 (compute_fly_reward2).
 
     ``walking=False`` is the live standing total (fly.py:750).  ``walking=True`` is the commented-out
-    walking total of fly.py:747-748 plus the leg term the report (p.7) includes — pinned by prose only.
+    walking total of fly.py:747-748 plus the leg term the report (p.7) includes — pinned by executing the reference's
+    function with those two lines switched back on (ref_harness.load_walking_reward, tests/test_oracle_vs_reference.py,
+    fixture tests/golden/env_walking_d18_a18_n211.npz).
     """
     n = obs.shape[0]
     height = obs[:, 0]

@@ -4,7 +4,8 @@ TEST / MEASUREMENT INFRASTRUCTURE (see oracle/__init__.py) — never on the prod
 
 What runs is the reference's unmodified `ppo.PPO` (`run`, `make_data`, `update`: reference ppo.py:105-264) driving an
 env object behind the same duck-typed surface `Fly` offers (ppo.py:110-112, 210-211, 223, 228-230), whose `step` calls
-the reference's unmodified `fly.compute_fly_observations` / `fly.compute_fly_reward2` (fly.py:685-805) — imported from
+the reference's unmodified `fly.compute_fly_observations` / `fly.compute_fly_reward2` (fly.py:685-805; for the walking
+configuration the same function with its commented-out total switched back on, ref_harness.load_walking_reward) — imported from
 `/root/reference`, or from the byte-for-byte staged copy `oracle/_ref` on the GPU box (oracle/make_ref.py,
 oracle/ref_harness.py).  The ~40 lines of `Fly.step` / `Fly.reset` tensor math that cannot be imported (they sit between
 gymapi calls, fly.py:626-657, 446-480) are the oracle's line-by-line restatement (fly_oracle.scale_actions /
@@ -38,6 +39,9 @@ from . import ref_harness
 def _make_env_class(fly_mod, t: fo.EnvTables, states, walking: bool):
     """Env behind the surface ppo.py uses.  `fly_mod`: the reference's fly module (its jit functions) or None (port)."""
     n = t.num_envs
+    reward_fn = None
+    if fly_mod is not None:     # the live total is the standing one (fly.py:750); walking = its commented-out lines, run
+        reward_fn = ref_harness.load_walking_reward() if walking else fly_mod.compute_fly_reward2
 
     class SynthFly:
         def __init__(self, args):
@@ -53,7 +57,7 @@ def _make_env_class(fly_mod, t: fo.EnvTables, states, walking: bool):
             st = states[self.k % len(states)]
             self.k += 1
             s.root, s.dof_states, s.force = st["root"], st["dof_states"], st["force"]   # gym.simulate + refresh_*
-            if fly_mod is None or walking:      # the reference's live reward is the standing total (fly.py:750)
+            if fly_mod is None:
                 fo.post_physics(t, s, walking=walking)
             else:
                 dof = s.dof_states.view(n, t.num_dof, 2)
@@ -64,7 +68,7 @@ def _make_env_class(fly_mod, t: fo.EnvTables, states, walking: bool):
                         t.action_idx_one, s.force, t.leg_tip_ids, n)            # fly.py:405-411
                 s.progress_buf += 1                                             # fly.py:678
                 s.progress_buf[s.progress_buf == 0] = 1                         # fly.py:415-416
-                s.reward_buf[:], s.reset_buf[:] = fly_mod.compute_fly_reward2(
+                s.reward_buf[:], s.reset_buf[:] = reward_fn(
                     s.obs_buf, s.reset_buf, s.progress_buf, s.actions.view(n, -1), fo.UP_WEIGHT, fo.HEADING_WEIGHT,
                     s.potentials, s.prev_potentials, fo.ACTIONS_COST_SCALE, fo.ENERGY_COST_SCALE,
                     fo.JOINTS_AT_LIMIT_COST_SCALE, fo.TERMINATION_HEIGHT, fo.TERMINATION_HEIGHT_UP, fo.DEATH_COST,

@@ -97,6 +97,53 @@ def load_fly_lowgrav():
     return _lowgrav
 
 
+_walking = None
+
+
+def load_walking_reward():
+    """``compute_fly_reward2`` with the reference's OWN commented-out walking total switched back on.
+
+    reference fly.py:747-748 keeps the walking total as two ``#`` lines (its trailing ``#+ leg_ground_reward`` is the leg
+    term BASELINE.json configs[2] names); fly.py:750 is the live standing total.  The function's source is taken from
+    the reference file as it lies, the ``#`` in front of those two lines (and of the leg term) is removed, the standing
+    total line is dropped, and the result is compiled by ``torch.jit.script`` in the reference module's own namespace —
+    every other line of the function runs as written.  Returns the scripted function.
+    """
+    global _walking
+    if _walking is None:
+        load_fly()                                          # stubs in place, reference importable
+        with open(os.path.join(REFERENCE_ROOT, "fly.py")) as f:
+            lines = f.read().split("\n")
+        start = next(i for i, ln in enumerate(lines) if ln.startswith("def compute_fly_reward2("))
+        end = next(i for i in range(start + 1, len(lines)) if lines[i].startswith("def ") or lines[i].startswith("@"))
+        body, out, seen = lines[start:end], [], 0
+        for ln in body:
+            st = ln.strip()
+            if st.startswith("#total_reward = progress_reward * 2"):
+                out.append("    " + st[1:]); seen += 1
+            elif st.startswith("#") and "actions_cost_scale * actions_cost" in st and seen == 1:
+                out.append("        " + st[1:].strip().replace("#+ leg_ground_reward", "+ leg_ground_reward")); seen += 1
+            elif st.startswith("total_reward = alive_reward + up_reward * orient_reward") and seen == 2:
+                seen += 1                                   # the standing total (fly.py:750) gives way
+            else:
+                out.append(ln)
+        if seen != 3:
+            raise RuntimeError("reference fly.py:747-750 does not look the way this edit expects")
+        src = "\n".join(out).replace("def compute_fly_reward2(", "def compute_fly_reward_walking(")
+        # torch.jit.script needs the source on disk (inspect.getsource): a temp module file
+        import tempfile
+        import importlib.util
+        d = tempfile.mkdtemp(prefix="flyb_walking_")
+        path = os.path.join(d, "fly_walking_total.py")
+        with open(path, "w") as f:
+            f.write("import torch\nfrom typing import Tuple\n\n\n" + src + "\n")
+        spec = importlib.util.spec_from_file_location("fly_walking_total", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _walking = torch.jit.script(mod.compute_fly_reward_walking)
+    return _walking
+
+
 def load_ppo(env_cls):
     """The reference ``ppo`` module with ``fly.Fly`` replaced by ``env_cls``.
 

@@ -36,7 +36,8 @@ def tables_for(asset: str, n: int, full_actions: bool) -> fo.EnvTables:
                         t["num_bodies"])
 
 
-def env_case(fly, asset: str, n: int, full_actions: bool, seed: int, prev_reset_frac: float):
+def env_case(fly, asset: str, n: int, full_actions: bool, seed: int, prev_reset_frac: float, reward_fn=None):
+    """`reward_fn`: stands in for fly.compute_fly_reward2 — the walking total (ref_harness.load_walking_reward)."""
     t = tables_for(asset, n, full_actions)
     st = fo.synth_state(t, seed)
     g = torch.Generator().manual_seed(seed + 99)
@@ -45,13 +46,21 @@ def env_case(fly, asset: str, n: int, full_actions: bool, seed: int, prev_reset_
     scaled, targets = fo.scale_actions(t, st["actions"])
     dof = st["dof_states"].view(n, t.num_dof, 2)
     a, o = t.num_act, t.num_obs
+    if reward_fn is not None:
+        # the walking total holds 2 * (potential - previous potential): previous potentials one plausible step behind the
+        # ones this state yields (a first evaluation tells them), so that the term is O(1) as it is in a live rollout
+        pot0 = fly.compute_fly_observations(
+            torch.zeros(n, o), st["root"], t.targets, potentials.clone(), t.inv_start_rot, dof[..., 0], dof[..., 1],
+            t.lower, t.upper, 0.2, scaled.view(n, -1), 1 / 60, t.basis0, t.basis1, 2, t.action_idx_one, st["force"],
+            t.leg_tip_ids, n)[1]
+        potentials = (pot0 - (torch.rand(n, generator=g) * 3.0 - 1.0)).clone()
     obs, pot, prev, up, head = fly.compute_fly_observations(
         torch.zeros(n, o), st["root"], t.targets, potentials.clone(), t.inv_start_rot, dof[..., 0], dof[..., 1],
         t.lower, t.upper, 0.2, scaled.view(n, -1), 1 / 60, t.basis0, t.basis1, 2, t.action_idx_one, st["force"],
         t.leg_tip_ids, n)
     progress = st["progress"].clone() + 1                                   # fly.py:678
     progress[progress == 0] = 1                                             # fly.py:415-416
-    rew, reset = fly.compute_fly_reward2(
+    rew, reset = (reward_fn or fly.compute_fly_reward2)(
         obs, reset_prev.clone(), progress, scaled.view(n, -1), 0.75, 0.5, pot, prev, 0.005, 0.005, 0.1, 1.1, 6, -2.0,
         1500, t.action_idx_one, t.upper, t.lower, n, st["root"][:, 3:7], a, st["force"], t.abdomen_ids,
         t.leg_tip_ids)
@@ -220,7 +229,13 @@ def main():
         save("env_lowgrav_d18_a18_n193.npz",
              lowgrav_case(ref_harness.load_fly_lowgrav(), "limited_18", 193, True, 2024, 0.25))
         return
+    if "--walking-only" in sys.argv:        # later addition, same rule
+        save("env_walking_d18_a18_n211.npz",
+             env_case(fly, "limited_18", 211, True, 515, 0.2, reward_fn=ref_harness.load_walking_reward()))
+        return
     save("env_lowgrav_d18_a18_n193.npz", lowgrav_case(ref_harness.load_fly_lowgrav(), "limited_18", 193, True, 2024, 0.25))
+    save("env_walking_d18_a18_n211.npz",
+         env_case(fly, "limited_18", 211, True, 515, 0.2, reward_fn=ref_harness.load_walking_reward()))
     save("env_d18_a18_n257.npz", env_case(fly, "limited_18", 257, True, 1234, 0.2))
     save("env_d42_a18_n131.npz", env_case(fly, "full_42", 131, False, 4321, 0.1))
     save("env_d42_a42_n131.npz", env_case(fly, "full_42", 131, True, 999, 0.0))

@@ -196,6 +196,29 @@ def test_lowgrav_variant_matches_reference_golden():
     assert cnt == want_ids.numel() and torch.equal(env.reset_ids[:cnt].cpu(), want_ids)
 
 
+def test_walking_total_matches_reference_golden():
+    """args.walking: the walking total + leg term (configs[2]) against the reference's reward function run with its own
+    commented-out total (fly.py:747-748) switched back on (tests/golden/make_golden.py --walking-only)."""
+    g = load_golden("env_walking_d18_a18_n211.npz")
+    n = 211
+    env = make_env(n, "limited_18", True, g["root"], g["dof_states"], g["force"], walking=True)
+    env.reset_buf.zero_()
+    env.pre_physics(g["actions_in"].to(DEV))
+    env.reset_buf.copy_(g["reset_in"])
+    env.progress_buf.copy_(g["progress_in"])
+    env.potentials.copy_(g["potentials_in"])
+    env.post_physics()
+    torch.cuda.synchronize()
+    assert torch.equal(env.reset_buf.cpu(), g["reset"])
+    assert_obs_close(env.obs_buf.cpu(), g["obs"], env.num_act)
+    torch.testing.assert_close(env.potentials.cpu(), g["potentials"], rtol=1e-6, atol=0)
+    # 2 * (potential - previous): the potentials are O(6e4), one ulp there is 2^-8, so the total carries 2 * 2 ulps
+    torch.testing.assert_close(env.reward_buf.cpu(), g["reward"], rtol=RTOL_ENV, atol=0.016)
+    live = g["reset"] == 0
+    err = (env.reward_buf.cpu() - g["reward"])[live].abs()
+    assert float(err.median()) <= 1e-5                           # typical env: no ulp flips at all
+
+
 def test_reset_method_resets_flagged_envs():
     """Fly.reset() (fly.py:446-480) performs the reset and reports whether any env was flagged."""
     n = 500

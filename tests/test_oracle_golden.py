@@ -30,6 +30,26 @@ def test_env_oracle_matches_reference_golden(name, asset, n, full):
     assert 0 < int(g["reset"].sum()) < n
 
 
+def test_walking_total_matches_reference_golden():
+    """configs[2]'s reward against the fixture frozen from the reference's reward function with its commented-out walking
+    total (fly.py:747-748) switched back on (oracle/ref_harness.py:load_walking_reward)."""
+    g = load_golden("env_walking_d18_a18_n211.npz")
+    n = 211
+    t = oracle_tables("limited_18", n, True)
+    s = fo.EnvState(t)
+    s.root, s.dof_states, s.force = g["root"].clone(), g["dof_states"].clone(), g["force"].clone()
+    s.progress_buf, s.reset_buf = g["progress_in"].clone(), g["reset_in"].clone()
+    s.potentials = g["potentials_in"].clone()
+    s.actions, _ = fo.scale_actions(t, g["actions_in"])
+    fo.post_physics(t, s, walking=True)
+    torch.testing.assert_close(s.obs_buf, g["obs"], rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(s.reward_buf, g["reward"], rtol=1e-6, atol=1e-6)
+    assert torch.equal(s.reset_buf, g["reset"]) and 0 < int(g["reset"].sum()) < n
+    live = g["reset"] == 0
+    progress2 = 2 * (g["potentials"] - g["prev_potentials"])[live]
+    assert 0.5 < float(progress2.abs().max()) < 8.0          # the term is there, at a live rollout's scale
+
+
 def _params(g, tag="w0"):
     return {k: g[f"{tag}/{k}"].clone() for k in fo.PARAM_ORDER}
 

@@ -66,6 +66,35 @@ def test_env_oracle_equals_executed_reference(asset, n, full, seed, variant):
     assert 0 < int(reset.sum()) < n
 
 
+@pytest.mark.parametrize("asset,n,full,seed", [("limited_18", 513, True, 41), ("full_42", 97, True, 42)])
+def test_walking_total_equals_the_references_commented_out_line_executed(asset, n, full, seed):
+    """configs[2]'s reward: the oracle's `walking=True` branch against compute_fly_reward2 with the reference's own
+    commented-out total (fly.py:747-748, leg term included) switched back on (ref_harness.load_walking_reward)."""
+    mod = ref_harness.load_fly()
+    walking = ref_harness.load_walking_reward()
+    t = oracle_tables(asset, n, full)
+    st = fo.synth_state(t, seed)
+    g = torch.Generator().manual_seed(seed + 1)
+    reset_prev = (torch.rand(n, generator=g) < 0.15).long()
+    potentials = -torch.rand(n, generator=g) * 60000.0
+    a = t.num_act
+    scaled, obs, pot, prev, up, head, progress, rew_standing, reset_standing = _run_reference_env(
+        mod, t, st, reset_prev, potentials)
+    rew, reset = walking(
+        obs, reset_prev.clone(), progress, scaled.view(n, -1), 0.75, 0.5, pot, prev, 0.005, 0.005, 0.1, 1.1, 6, -2.0,
+        1500, t.action_idx_one, t.upper, t.lower, n, st["root"][:, 3:7], a, st["force"], t.abdomen_ids, t.leg_tip_ids)
+    s = fo.EnvState(t)
+    s.root, s.dof_states, s.force = st["root"].clone(), st["dof_states"].clone(), st["force"].clone()
+    s.progress_buf, s.reset_buf, s.potentials = st["progress"].clone(), reset_prev.clone(), potentials.clone()
+    s.actions = scaled
+    fo.post_physics(t, s, walking=True)
+    assert torch.equal(s.reset_buf, reset) and torch.equal(reset, reset_standing)
+    # same operations in the same order on the same obs: the totals agree to the last bit or one rounding
+    torch.testing.assert_close(s.reward_buf, rew, rtol=1e-6, atol=1e-6)
+    live = reset == 0
+    assert float((rew - rew_standing)[live].abs().max()) > 1.0      # it IS a different total (progress term)
+
+
 def _reference_agent(n, o, a):
     class SynthEnv:
         def __init__(self, args):
