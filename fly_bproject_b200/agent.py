@@ -238,7 +238,15 @@ class PPO:
         # data-parallel: one process per GPU, the only collective is the gradient all-reduce
         self.rank, self.world_size = dp.world()
         self._peers = None                  # dp.PeerExchange: gradient sum by the library's own kernels over NVLink
-        self._dp_tail = os.environ.get("FLYB_DP_TAIL", "0") == "1"      # exchange inside the weight-gradient kernel's tail
+        # how a data-parallel optimiser step exchanges gradients over peer memory (FLYB_DP_STEP):
+        #   "fused"  flyb_ppo_step_dp: the reducing threads push self-validating words, await and sum the peers' ones; 4 launches
+        #   "split"  flyb_ppo_grad (push + fence) + flyb_ppo_apply (norm kernel: flags, sum); 5 launches
+        # FLYB_DP_TAIL=1 (with "fused"): the cooperative two-launch form of flyb_ppo_step_dp instead
+        self._dp_step = os.environ.get("FLYB_DP_STEP", "fused").lower()
+        if self._dp_step not in ("fused", "split"):
+            raise ValueError(f"FLYB_DP_STEP={self._dp_step!r}: expected 'fused' or 'split'")
+        if os.environ.get("FLYB_DP_TAIL", "0") == "1":
+            self._dp_step = "fused"
         if self.world_size > 1:
             dp.broadcast_params_(self.net.flat, src=0)
             self.net.repack()
@@ -427,9 +435,9 @@ class PPO:
                 p(self.adam_step), p(self.grad_norm), self._ws_ptr, stream), "flyb_ppo_step")
             return
         peers = self._peers.byref() if self._peers is not None else None
-        if peers is not None and self.net.wpack is not None and self._dp_tail:
-            # chain kernel + ONE cooperative launch: weight gradients, reduction, push / flags / rank-ordered sum over
-            # NVLink peer memory, norm, clip + Adam
+        if peers is not None and self._dp_step == "fused":
+            # chain, weight gradients, reduction WITH the exchange (push / await / rank-ordered sum over NVLink peer
+            # memory), clip + Adam
             _lib.check(self.lib.flyb_ppo_step_dp(
                 lay, C.byref(self.ppo_cfg), p(self.net.flat), p(self.net.wpack), p(self._obs_ring[k:j]),
                 p(self.all_acts[k:j]), p(self.all_log_prob[k:j]), p(self._target[k:j]), p(self.all_advantage[k:j]),

@@ -43,7 +43,8 @@ extern "C" int32_t flyb_peer_total_pad(int32_t total) { return (total + 63) / 64
 
 extern "C" size_t flyb_peer_bytes(int32_t total, int32_t world) {
   if (total <= 0 || world < 1 || world > FLYB_MAX_PEERS) return 0;
-  return peer_slots_bytes(flyb_peer_total_pad(total), world) + PEER_CTRL_BYTES;
+  const int tp = flyb_peer_total_pad(total);
+  return peer_slots_bytes(tp, world) + PEER_CTRL_BYTES + peer_ll_bytes(tp, world);
 }
 
 extern "C" int flyb_peer_alloc(size_t bytes, void** ptr_out, void* handle_out) {

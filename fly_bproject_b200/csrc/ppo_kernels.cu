@@ -35,8 +35,10 @@ struct StepFuse {
   int tail;
   float *params, *exp_avg, *exp_avg_sq, *grad_norm_out;
   double lr, beta1, beta2, eps, max_norm;
-  int done;   // out: 1 = the step was completed by the tail (no Adam launch needed)
+  int done;   // out: 1 = the step was completed by the tail (no Adam launch needed); 2 = the reduction did the
+              // fused exchange (grad = sum over ranks, sq_part filled): clip + Adam are left
   float grad_scale;   // 1 / world when the tail also does the data-parallel exchange (peers != NULL), else 1
+  int exchange;   // in: with peers and no tail, the reducing kernel does the exchange itself (flyb_ppo_step_dp)
 };
 constexpr int DW_SPLITS_MAX = 64;
 constexpr int NORM_BLOCKS = 256;
@@ -565,29 +567,38 @@ extern "C" int flyb_ppo_step_dp(const FlybNetLayout* net, const FlybPpoCfg* cfg,
                                 const float* advantage, const float* action_var, int64_t rows, float* grad, float* loss,
                                 float* exp_avg, float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out,
                                 void* workspace, const FlybPeerGroup* peers, void* stream) {
+  FLYB_REQUIRE(peers, "flyb_ppo_step_dp: NULL peer group");
+  if (!wpack || !tc_ppo_supported(net)) {   // CUDA-core gradient: the two halves as they are (whole-buffer exchange)
+    int rc0 = flyb_ppo_grad(net, cfg, params, nullptr, obs, action, old_logp, target, advantage, action_var, rows, grad,
+                            loss, workspace, peers, stream);
+    if (rc0 != FLYB_OK) return rc0;
+    return flyb_ppo_apply(net, cfg, params, grad, exp_avg, exp_avg_sq, step, grad_scale, grad_norm_out, workspace, wpack,
+                          peers, stream);
+  }
   int rc = validate_net(net, params);
   if (rc != FLYB_OK) return rc;
-  FLYB_REQUIRE(cfg && wpack && peers && obs && action && old_logp && target && advantage && action_var && grad && loss &&
-                   exp_avg && exp_avg_sq && step && workspace,
-               "flyb_ppo_step_dp: NULL argument (it needs the tensor-core path and a peer group)");
+  FLYB_REQUIRE(cfg && obs && action && old_logp && target && advantage && action_var && grad && loss && exp_avg &&
+                   exp_avg_sq && step && workspace,
+               "flyb_ppo_step_dp: NULL argument");
   FLYB_REQUIRE(rows > 0, "flyb_ppo_step_dp: rows must be > 0");
   FLYB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "flyb_ppo_step_dp: workspace must be 256-byte aligned");
-  FLYB_REQUIRE(tc_ppo_supported(net), "flyb_ppo_step_dp: the tensor-core PPO step does not cover this shape");
   if ((rc = peer_validate(peers, net->total)) != FLYB_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   StepFuse fuse{};
   fuse.step = (long long*)step;
-  fuse.tail = 1;
+  const char* tail_env = getenv("FLYB_DP_TAIL");   // read per call: a test flips it
+  fuse.tail = (tail_env && tail_env[0] == '1') ? 1 : 0;
+  fuse.exchange = 1;
   fuse.params = params; fuse.exp_avg = exp_avg; fuse.exp_avg_sq = exp_avg_sq; fuse.grad_norm_out = grad_norm_out;
   fuse.lr = cfg->lr; fuse.beta1 = cfg->beta1; fuse.beta2 = cfg->beta2; fuse.eps = cfg->eps; fuse.max_norm = cfg->max_grad_norm;
   fuse.grad_scale = grad_scale;
   rc = tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
                    workspace, peers, st, &fuse);
   if (rc != FLYB_OK) return rc;
-  if (fuse.done) return FLYB_OK;
-  // the weight-gradient grid does not fit one wave on this device: the split path (the reduce kernel has pushed)
-  return flyb_ppo_apply(net, cfg, params, grad, exp_avg, exp_avg_sq, step, grad_scale, grad_norm_out, workspace, wpack,
-                        peers, stream);
+  if (fuse.done == 1) return FLYB_OK;   // cooperative tail: everything happened in the weight-gradient kernel
+  // fused exchange: the reduction left the sum over ranks in `grad` and its squared-norm partials; Adam closes the epoch
+  return launch_adam(net, cfg, params, grad, exp_avg, exp_avg_sq, (const long long*)step, grad_scale, grad_norm_out,
+                     fuse.sq_part, fuse.sq_parts, wpack, peers, st);
 }
 
 extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack,

@@ -49,6 +49,7 @@ struct StepFuse {   // see ppo_kernels.cu
   double lr, beta1, beta2, eps, max_norm;
   int done;
   float grad_scale;   // 1 / world when the tail also does the data-parallel exchange (peers != NULL), else 1
+  int exchange;
 };
 #endif
 
@@ -1103,12 +1104,18 @@ struct ReduceArgs {
   float inv_rows;
   float* sq_part;   // nullable: [gridDim.x] sums of squares of this CTA's entries (flyb_ppo_step: saves the norm kernel)
   long long* step;  // with sq_part: Adam's step counter, += 1 (the norm kernel's other job)
+  float scale;      // PEERS == 2: the squares are taken of scale * (sum over ranks), scale = 1 / world
 };
 // 256 threads: 64 QUADS of gradient entries (four consecutive floats, one 128-bit load per partial) x 4 interleaved
 // partial groups.  Per entry the association is what it was with one entry per thread — group g adds partials g, g + 4,
 // ... in order, then (s0 + s1) + (s2 + s3) — so the gradient bits do not depend on the vector width.
+// PEERS: 0 one GPU; 1 push the result to every rank, the norm kernel of flyb_ppo_apply completes the sum (fence + flags);
+// 2 the FUSED exchange (flyb_ppo_step_dp): the thread that has reduced a quad pushes it as self-validating 64-bit words,
+// awaits the peers' words of the same quad and adds them in rank order right here (peer.cuh: peer_ll_push4 /
+// peer_ll_sum4), so that `grad` leaves this kernel as the sum over ranks, with its squared-norm partials, and clip + Adam
+// follow with no norm kernel.
 constexpr int RED_QUADS = 64, RED_ELEMS = 4 * RED_QUADS, RED_GROUPS = 4;
-template <bool PEERS>
+template <int PEERS>
 __global__ void __launch_bounds__(RED_QUADS * RED_GROUPS)
 ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restrict__ dw_part,
                      const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss,
@@ -1129,7 +1136,7 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
     for (int j = 0; j < 4; ++j)
 #pragma unroll
       for (int sg = 0; sg < 12; ++sg) valid[j] = valid[j] || (i + j >= a.off[sg] && i + j < a.off[sg] + a.size[sg]);
-    if (valid[0] || valid[1] || valid[2] || valid[3]) {
+    if (valid[0] || valid[1] || valid[2] || valid[3]) {   // (alignment padding is never summed: it stays 0)
       const float4* src = reinterpret_cast<const float4*>(dw_part + i);
       const size_t stride4 = (size_t)a.total / 4;
 #pragma unroll 8
@@ -1141,29 +1148,38 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
   }
   s_acc[pg][e] = acc;
   __syncthreads();
+  float g[4] = {0.f, 0.f, 0.f, 0.f};
   if (pg == 0) {   // warps 0 and 1
-    float g[4] = {0.f, 0.f, 0.f, 0.f};
     if (i < a.total) {
       const float4 s0 = s_acc[0][e], s1 = s_acc[1][e], s2 = s_acc[2][e], s3 = s_acc[3][e];
       g[0] = valid[0] ? (s0.x + s1.x) + (s2.x + s3.x) : 0.0f;
       g[1] = valid[1] ? (s0.y + s1.y) + (s2.y + s3.y) : 0.0f;
       g[2] = valid[2] ? (s0.z + s1.z) + (s2.z + s3.z) : 0.0f;
       g[3] = valid[3] ? (s0.w + s1.w) + (s2.w + s3.w) : 0.0f;
-      *reinterpret_cast<float4*>(grad + i) = make_float4(g[0], g[1], g[2], g[3]);
-      // posted NVLink stores into this rank's slot on every rank; the flags are raised by the next kernel (peer.cuh)
-      if (PEERS) peer_push4(pv, epoch & 1u, i, make_float4(g[0], g[1], g[2], g[3]));
-    }
-    if (a.sq_part) {
-      const float sq = warp_sum(((g[0] * g[0] + g[1] * g[1]) + g[2] * g[2]) + g[3] * g[3]);
-      if ((threadIdx.x & 31) == 0) s_sq[threadIdx.x >> 5] = sq;
+      if (PEERS != 2) *reinterpret_cast<float4*>(grad + i) = make_float4(g[0], g[1], g[2], g[3]);
+      // posted NVLink stores into this rank's slot on every rank; the flags are raised by the next kernel
+      if (PEERS == 1) peer_push4(pv, epoch & 1u, i, make_float4(g[0], g[1], g[2], g[3]));
+      if (PEERS == 2) {
+        peer_ll_push4(pv, epoch & 1u, epoch + 1u, i, g);
+        if (blockIdx.x == 0 && threadIdx.x == 0) pv.stamp[3] = global_ns();
+        const float4 t = peer_ll_sum4(pv, epoch & 1u, epoch + 1u, i);
+        if (blockIdx.x == 0 && threadIdx.x == 0) pv.stamp[4] = global_ns();
+        *reinterpret_cast<float4*>(grad + i) = t;
+        g[0] = t.x * a.scale; g[1] = t.y * a.scale; g[2] = t.z * a.scale; g[3] = t.w * a.scale;
+      }
     }
   }
-  if (PEERS) peer_push_fence(pv);
+  if (pg == 0 && a.sq_part) {
+    const float sq = warp_sum(((g[0] * g[0] + g[1] * g[1]) + g[2] * g[2]) + g[3] * g[3]);
+    if ((threadIdx.x & 31) == 0) s_sq[threadIdx.x >> 5] = sq;
+  }
+  if (PEERS == 1) peer_push_fence(pv);
   if (a.sq_part) {
     __syncthreads();
     if (threadIdx.x == 0) {
       a.sq_part[blockIdx.x] = s_sq[0] + s_sq[1];
       if (blockIdx.x == 0) *a.step += 1;
+      if (PEERS == 2 && blockIdx.x == 0) pv.stamp[5] = global_ns();
     }
   }
   if (blockIdx.x == 0 && threadIdx.x < 32) {   // loss = mean(-surr) + smooth_l1 mean (ppo.py:194, 197)
@@ -1305,18 +1321,26 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   for (int i = 0; i < 12; ++i) { r.off[i] = net->off[i]; r.size[i] = sizes[i]; }
   r.total = net->total; r.nparts = w.ctas_per_role; r.nloss = w.grid1; r.inv_rows = ga.inv_rows;
   const int red_grid = w.red_grid;
-  if (fuse) {   // the caller goes straight on to Adam: the reduction also takes the squared norm and counts the step
-    r.sq_part = w.sq_part;
+  r.scale = 1.0f;
+  const bool fused_exchange = fuse && peers && fuse->exchange;
+  if (fuse && (!peers || fused_exchange)) {   // the caller goes straight on to Adam: the reduction also takes the squared norm
+    r.sq_part = w.sq_part;             // (of the sum over ranks, scaled, when it does the exchange too) and counts the step
     r.step = fuse->step;
     fuse->sq_part = w.sq_part;
     fuse->sq_parts = red_grid;
   }
-  if (peers)
-    ppo_reduce_tc_kernel<true><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
-                                                                            make_peer_view(*peers));
-  else
-    ppo_reduce_tc_kernel<false><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
-                                                                             PeerView{});
+  if (fused_exchange) {
+    r.scale = fuse->grad_scale;
+    ppo_reduce_tc_kernel<2><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+                                                                         make_peer_view(*peers));
+    fuse->done = 2;   // exchanged: only clip + Adam are left
+  } else if (peers) {
+    ppo_reduce_tc_kernel<1><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+                                                                         make_peer_view(*peers));
+  } else {
+    ppo_reduce_tc_kernel<0><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
+                                                                         PeerView{});
+  }
   FLYB_LAUNCH_CHECK("ppo_reduce_tc_kernel");
   return FLYB_OK;
 }

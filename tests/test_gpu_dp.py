@@ -1,7 +1,7 @@
 """Data-parallel PPO update on real GPUs (NCCL): needs >= 2 CUDA devices, skipped otherwise.
 
 Two ranks, each with its own env shard and RNG stream but the same initial parameters, run one rollout + two full
-updates (150 optimiser steps, gradient sum between flyb_ppo_grad and flyb_ppo_apply).  Every rank must end with
+updates (150 optimiser steps, gradient sum inside flyb_ppo_step_dp, or between flyb_ppo_grad and flyb_ppo_apply).  Every rank must end with
 bit-identical parameters / Adam state.  The sum runs once through the library's own peer-memory kernels (captured in a
 CUDA graph and replayed) and once through NCCL (eager): with two ranks a + b is one rounding either way, so the two
 exchanges must agree bit for bit.
@@ -22,12 +22,24 @@ def _free_port():
         return s.getsockname()[1]
 
 
+def _spawn(fn, world, *args):
+    """mp.spawn with a fresh rendezvous port; the port probe can lose a race against another socket on the box."""
+    for attempt in range(3):
+        try:
+            mp.spawn(fn, args=(world, _free_port()) + args, nprocs=world, join=True)
+            return
+        except Exception as e:      # noqa: BLE001
+            if "address already in use" not in str(e).lower() or attempt == 2:
+                raise
+
+
 def _worker(rank, world, port, out, mode):
     import torch.distributed as dist
     import fly_bproject_b200 as fb
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     os.environ["FLYB_DP"] = "nccl" if mode == "nccl" else "peer"
     os.environ["FLYB_DP_TAIL"] = "1" if mode == "peer_tail" else "0"
+    os.environ["FLYB_DP_STEP"] = "split" if mode == "peer_split" else "fused"
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{rank}"))
     try:
@@ -36,7 +48,7 @@ def _worker(rank, world, port, out, mode):
                             seed=1234)           # IDENTICAL args on every rank: the library decorrelates the shards
         agent = fb.PPO(args)
         assert agent.world_size == world and (agent._peers is not None) == (mode != "nccl")
-        assert agent._dp_tail == (mode == "peer_tail")
+        assert agent._dp_step == ("split" if mode == "peer_split" else "fused")
         agent.collect_rollout(use_graph=False)
         acts_sum, obs_sum = float(agent.all_acts.double().sum()), float(agent._obs_ring.double().sum())
         for _ in range(2):      # peer modes: eager warm-up + capture, then a replay; NCCL mode: eager twice
@@ -57,8 +69,10 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
         pytest.skip(f"needs {world} CUDA devices")
     out = str(tmp_path / "dp")
     res = {}
-    for mode in ("peer", "nccl", "peer_tail"):   # peer_tail: the exchange inside the weight-gradient kernel's tail
-        mp.spawn(_worker, args=(world, _free_port(), out, mode), nprocs=world, join=True)
+    # peer: exchange inside the reducing kernel, self-validating words (default); peer_split: push + fence, then flags +
+    # sum in the norm kernel; peer_tail: the exchange inside the weight-gradient kernel's cooperative tail
+    for mode in ("peer", "peer_split", "nccl", "peer_tail"):
+        _spawn(_worker, world, out, mode)
         rs = [torch.load(f"{out}.{mode}.{r}") for r in range(world)]
         for r in rs[1:]:
             assert r["steps"] == rs[0]["steps"] == 150
@@ -71,13 +85,14 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
         assert bool(torch.isfinite(rs[0]["flat"]).all())
         res[mode] = rs[0]
     for k in ("flat", "m", "v"):
-        if world == 2:      # a + b is one rounding in any order
-            assert torch.equal(res["peer"][k], res["nccl"][k]), k
+        if world == 2:      # a + b is one rounding in any order (and both run the same norm kernel)
+            assert torch.equal(res["peer_split"][k], res["nccl"][k]), k
     # more ranks: NCCL's tree / ring order differs from the rank order, and 150 Adam steps (each ~lr in size whatever
     # the gradient's magnitude) amplify the reassociation noise: only the bulk has to agree
-    assert float((res["peer"]["flat"] - res["nccl"]["flat"]).abs().mean()) < 1e-3
+    assert float((res["peer_split"]["flat"] - res["nccl"]["flat"]).abs().mean()) < 1e-3
     # same sums in the same order; only the association of the norm's partial sums differs (an ulp in the clip coefficient)
-    assert float((res["peer_tail"]["flat"] - res["peer"]["flat"]).abs().mean()) < 1e-3
+    assert float((res["peer_tail"]["flat"] - res["peer_split"]["flat"]).abs().mean()) < 1e-3
+    assert float((res["peer"]["flat"] - res["peer_split"]["flat"]).abs().mean()) < 1e-3
 
 
 def _soak_worker(rank, world, port, out, exchanges):
@@ -116,7 +131,7 @@ def test_peer_exchange_soak(tmp_path):
         pytest.skip(f"needs {world} CUDA devices")
     exchanges = int(os.environ.get("FLYB_SOAK_EXCHANGES", "10000"))
     out = str(tmp_path / "dp")
-    mp.spawn(_soak_worker, args=(world, _free_port(), out, exchanges), nprocs=world, join=True)
+    _spawn(_soak_worker, world, out, exchanges)
     rs = [torch.load(f"{out}.soak.{r}") for r in range(world)]
     assert rs[0]["steps"] >= exchanges
     for r in rs:

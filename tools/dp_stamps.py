@@ -34,10 +34,14 @@ def main():
     all_rows = [None] * dist.get_world_size()
     dist.all_gather_object(all_rows, rows)
     if rank == 0:
-        names = ["norm kernel entry (flags raised)", "all flags seen", "norm CTA 0 done"]
+        if agent._dp_step == "fused":   # everything happens inside the reducing kernel
+            names, cols = ["CTA 0 thread 0: quad pushed", "every rank's quad seen + summed", "CTA 0 done"], (3, 4, 5)
+        else:
+            names, cols = ["norm kernel entry (flags raised)", "all flags seen", "norm CTA 0 done"], (3, 4, 5)
+        print(f"FLYB_DP_STEP={agent._dp_step}")
         for it in range(4, 12):     # %globaltimer is per GPU: only differences within a rank mean anything
             print(f"step {it}: " + " | ".join(
-                f"r{k}: " + " ".join(f"{(r[it][j] - r[it][0]) / 1e3:6.1f}" for j in (3, 4, 5)) for k, r in enumerate(all_rows)))
+                f"r{k}: " + " ".join(f"{(r[it][j] - r[it][0]) / 1e3:6.1f}" for j in cols) for k, r in enumerate(all_rows)))
         print("columns per rank (us after that rank's reduce-kernel entry): " + ", ".join(names))
     agent.exit()
     dist.destroy_process_group()
