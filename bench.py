@@ -519,7 +519,8 @@ def run_own(args, cfg):
                        "us_per_optimiser_step_isolated": kt["ppo_minibatch_step"] * 1e3,
                        "includes": "value forward over (T+1)N rows + GAE scan + optimiser steps (fwd/bwd/clip/Adam)" +
                                    ("" if world == 1 else " + NCCL all-reduce" if agent._peers is None else
-                                    " with the gradient sum over NVLink peer memory inside the reduce/norm kernels")},
+                                    " with the gradient sum over NVLink peer memory inside the gradient-reducing kernel (FLYB_DP_STEP=" +
+                                    agent._dp_step + ")")},
         }
         if world == 1 and not args.no_cpu:
             cores = os.cpu_count() or 1

@@ -129,7 +129,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)  # AttributeError if the .so does not export it
             fn.restype = restype
             fn.argtypes = argtypes
-        if handle.flyb_abi_version() != 6:
+        if handle.flyb_abi_version() != 7:
             raise FlybError("libflyb200.so ABI version mismatch")
         _lib = handle
     return _lib

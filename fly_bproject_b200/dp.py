@@ -8,9 +8,10 @@ mean of the shard means the global mean of both loss terms (reference ppo.py:194
 reference's single-process step on the concatenated batch up to fp reassociation.
 
 On NVLink-connected GPUs the exchange does not go through NCCL at all: `PeerExchange` maps every rank's exchange
-buffer into every process (CUDA IPC) and the library's own kernels do the sum — the reducing kernel of
-``flyb_ppo_grad`` pushes its result into all ranks' buffers, the norm kernel of ``flyb_ppo_apply`` adds the slots
-(include/flyb200.h, FlybPeerGroup).  ``FLYB_DP=nccl`` keeps the NCCL all-reduce (the baseline the fused path is
+buffer into every process (CUDA IPC) and the library's own kernels do the sum — inside ``flyb_ppo_step_dp`` the threads
+of the gradient-reducing kernel push their entries into all ranks' buffers as self-validating 64-bit words, await the
+peers' ones and add them in rank order (the split form: the reducing kernel of ``flyb_ppo_grad`` pushes, the norm kernel
+of ``flyb_ppo_apply`` waits for flags and adds the slots; include/flyb200.h, FlybPeerGroup).  ``FLYB_DP=nccl`` keeps the NCCL all-reduce (the baseline the fused path is
 measured against); torch.distributed is then only the side channel for the IPC handles and the parameter broadcast.
 
 The plain helpers are device-agnostic (NCCL on the GPUs, gloo in the CPU tests).
@@ -119,7 +120,7 @@ class PeerExchange:
         return C.byref(self.group)
 
     def status(self) -> int:
-        """Sticky error word of this rank's exchange (flyb_peer_status; synchronises): 0 = fine, 1 + r = the norm kernel
+        """Sticky error word of this rank's exchange (flyb_peer_status; synchronises): 0 = fine, 1 + r = the waiting kernel
         gave up waiting for rank r."""
         st = C.c_int32(0)
         self._lib.check(self._L.flyb_peer_status(self.byref(), C.byref(st)), "flyb_peer_status")

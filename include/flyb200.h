@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FLYB_ABI_VERSION 6
+#define FLYB_ABI_VERSION 7
 #define FLYB_MAX_DOF 64      /* asset DOF count D: 18 (nmf_no_limits_limited_Dofs.urdf) or 42 (nmf_no_limits.urdf) */
 #define FLYB_NUM_ABDOMEN 5   /* reference fly.py:299 */
 #define FLYB_NUM_LEGTIPS 6   /* reference fly.py:300 */
@@ -247,20 +247,34 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
 /* ---- data-parallel gradient exchange over NVLink peer memory (the one collective of the path).
  * One process per GPU.  Every rank allocates one exchange buffer with flyb_peer_alloc, publishes its 64-byte IPC
  * handle to the other ranks (any side channel; the Python host uses torch.distributed.all_gather_object), maps the
- * others' buffers with flyb_peer_open and fills a FlybPeerGroup.  With a group,
+ * others' buffers with flyb_peer_open and fills a FlybPeerGroup.  Two forms of the exchange share the buffer.
+ * FUSED (flyb_ppo_step_dp, the default of the Python host): the exchange happens inside the kernel that reduces the
+ *   per-CTA partial gradients.  Every gradient entry travels as ONE 64-bit word {epoch + 1 << 32 | float bits}; 64-bit
+ *   accesses are single-copy atomic, so a word that shows the awaited epoch carries its value — no fence, no flag.  The
+ *   thread that has reduced four entries stores them into slot [epoch & 1][rank] of EVERY rank's buffer (posted NVLink
+ *   stores), then polls the same four entries of every rank's slot in its OWN buffer and adds them in rank order
+ *   (bit-identical on every rank), writes `grad` and its share of the squared norm; clip + Adam follow with no norm
+ *   kernel: 4 launches, as on one GPU.  One NVLink crossing of latency.  Measured per optimiser step of 32 768 samples
+ *   per rank: 138.9 us at 2 GPUs against 138.4 us on one (split form 148.5); 144.3 at 8 GPUs against 137.8 (split 151.6).
+ *   A thread waits only for the peers' threads of the same index, which store before THEY wait: no dead-lock however
+ *   the grids are scheduled.
+ * SPLIT (flyb_ppo_grad + flyb_ppo_apply; what a caller with its own work between the halves uses):
  *   flyb_ppo_grad  : its last kernel (the fixed-order reduction of the per-CTA partial gradients) stores every
  *                    gradient entry straight into slot [epoch & 1][rank] of EVERY rank's buffer (posted NVLink
  *                    writes; every pushing CTA ends with a barrier + one system-scope fence);
  *   flyb_ppo_apply : its first kernel (global norm) raises this rank's flag on every rank, waits for all ranks'
  *                    flags of this epoch, sums the `world` slots in rank order (bit-identical on every rank), writes
  *                    `grad` and goes on as usual; the Adam kernel closes the epoch.
- * The two calls must alternate, on one stream.  No kernel waits for a peer except that norm kernel, and what it
- * waits for is raised at the ENTRY of the peers' norm kernels: no dead-lock however CTAs are scheduled.  Slots are
- * double-buffered by epoch parity: a rank can be at most one push ahead of the slowest one.  Everything is
- * stream-ordered device code: a whole data-parallel update is CUDA-graph capturable.
+ *   The two calls must alternate, on one stream.  No kernel waits for a peer except that norm kernel, and what it
+ *   waits for is raised at the ENTRY of the peers' norm kernels: no dead-lock however CTAs are scheduled.
+ * Both: slots are double-buffered by epoch parity and a rank's next reducing kernel starts only after its current
+ * exchange has ended (stream order): a rank can be at most one exchange ahead of the slowest one and never overwrites
+ * what a peer still has to read.  The Adam kernel closes the epoch.  Everything is stream-ordered device code: a whole
+ * data-parallel update is CUDA-graph capturable.  All ranks must use the same form for a given exchange.
  * Layout of a buffer of flyb_peer_bytes(total, world) bytes (zero-filled by flyb_peer_alloc):
  *   float slots[2][world][total_pad]; uint32 flags[FLYB_MAX_PEERS] (one epoch per source rank); uint32 epoch;
- *   uint32 error (sticky, see flyb_peer_status); time stamps. */
+ *   uint32 error (sticky, see flyb_peer_status); time stamps (256 bytes of control in all);
+ *   uint64 words[2][world][total_pad] (the fused form's slots). */
 #define FLYB_MAX_PEERS 8
 typedef struct FlybPeerGroup {
   int32_t rank, world;                 /* world <= FLYB_MAX_PEERS */
@@ -276,9 +290,10 @@ int flyb_peer_open(const void* handle, void** ptr_out);   /* cudaIpcOpenMemHandl
 int flyb_peer_close(void* ptr);                            /* cudaIpcCloseMemHandle */
 int flyb_peer_free(void* ptr);                             /* cudaFree of an own buffer */
 /* Debug aid (synchronises the device): %globaltimer marks in ns of this rank's LAST exchange:
- * [0] reduce kernel entry, [3] norm kernel entry (flags raised), [4] all ranks' flags seen, [5] norm CTA 0 done. */
+ * [0] reduce kernel entry, [3] norm kernel entry (flags raised), [4] all ranks' flags seen, [5] norm CTA 0 done;
+ * fused form: [3] thread 0 has pushed its entries, [4] has seen and summed every rank's, [5] reducing CTA 0 done. */
 int flyb_peer_stamps(const FlybPeerGroup* group, uint64_t* out8);
-/* Sticky error word of this rank's exchange (synchronises the device): 0 = fine; 1 + r = the norm kernel gave up
+/* Sticky error word of this rank's exchange (synchronises the device): 0 = fine; 1 + r = the waiting kernel gave up
  * waiting for rank r after the timeout.  The wait does not trap (the CUDA context survives): the stream drains, every
  * later exchange returns at once, results are meaningless from then on and the host must stop — or restart with the
  * NCCL exchange (FLYB_DP=nccl), which simply waits. */
@@ -321,11 +336,13 @@ int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params
                   const float* action_var, int64_t rows, float* grad, float* loss, float* exp_avg, float* exp_avg_sq,
                   int64_t* step, float* grad_norm_out, void* workspace, void* stream);
 
-/* Opt-in (measured slower than flyb_ppo_grad + flyb_ppo_apply, which stay the default): the same single call for a
- * data-parallel run: flyb_ppo_grad + gradient sum over the peer group + flyb_ppo_apply in
- * TWO launches — the weight-gradient kernel (launched cooperatively) reduces its partials behind a grid barrier, pushes
- * the result to every rank, raises / waits for the flags, adds the slots in rank order, takes the norm and runs Adam.
- * Same protocol and results as the two calls (FlybPeerGroup); needs the tensor-core path (wpack) and a peer group. */
+/* The data-parallel optimiser step in one call: flyb_ppo_grad + gradient sum over the peer group + flyb_ppo_apply
+ * (grad_scale = 1 / world) with the FUSED exchange (see FlybPeerGroup): 4 launches — chain, weight gradients, reduction
+ * with the exchange inside, clip + Adam.  Same sums in the same rank order as the split form; the association of the
+ * norm's partial sums is the single-GPU flyb_ppo_step's.  FLYB_DP_TAIL=1 selects the cooperative TWO-launch form instead
+ * (the weight-gradient kernel reduces behind a grid barrier, pushes, raises / waits for the flags, adds the slots, takes
+ * the norm and runs Adam; measured slower: 155.3 vs 146.8 us at 2 GPUs).  Without `wpack`, or for a shape the
+ * tensor-core PPO step does not cover, it runs the split form. */
 int flyb_ppo_step_dp(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack, const float* obs,
                      const float* action, const float* old_logp, const float* target, const float* advantage,
                      const float* action_var, int64_t rows, float* grad, float* loss, float* exp_avg, float* exp_avg_sq,

@@ -25,7 +25,7 @@ def test_header_symbols_are_exported_and_bound(built_lib):
         assert s in _lib.SIGNATURES, f"{s} has no ctypes signature in fly_bproject_b200/_lib.py"
     assert sorted(_lib.SIGNATURES) == syms
     lib = _lib.lib()
-    assert lib.flyb_abi_version() == 6
+    assert lib.flyb_abi_version() == 7
 
 
 def test_library_is_sm100a_only(built_lib):
