@@ -296,9 +296,11 @@ def run_own(args, cfg):
     upd_value = n_minibatches * rows_mb * world / (upd_ms * 1e-3)
     step_us = roll_ms * 1e3 / horizon                              # one env step INSIDE the rollout graph
     launches_rollout = (horizon + 1) if fused else 2 * horizon
-    # per optimiser step: chain, weight gradients, reduce (+ norm), clip + Adam on one GPU (tensor-core path); chain,
-    # weight gradients, reduce (+ push), norm (+ sum), Adam otherwise
-    launches_update = 2 + n_minibatches * (4 if (world == 1 and tc_path) else 5)
+    # per optimiser step: chain, weight gradients, reduce (+ norm partials; data-parallel: + the gradient exchange),
+    # clip + Adam on the tensor-core path; with the split exchange (or the CUDA-core path) a norm kernel in between
+    ppo_tc = tc_path and int(agent.net.layout.k0_pad) in (80, 160)     # the two compiled shapes of the PPO step
+    four = ppo_tc and (world == 1 or (agent._peers is not None and agent._dp_step == "fused"))
+    launches_update = 2 + n_minibatches * (4 if four else 5)
     launches = K * REPEATS * (launches_rollout + launches_update)
 
     # ---------------- per-kernel device times, each kernel alone in a graph (pool rotation keeps L2 cold)

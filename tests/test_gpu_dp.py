@@ -37,6 +37,8 @@ def _worker(rank, world, port, out, mode):
     import torch.distributed as dist
     import fly_bproject_b200 as fb
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    wide = mode.startswith("wide_")          # the 42-joint set: the wide tensor-core shape's kernels (O = 145, A = 42)
+    mode = mode[5:] if wide else mode
     os.environ["FLYB_DP"] = "nccl" if mode == "nccl" else "peer"
     os.environ["FLYB_DP_TAIL"] = "1" if mode == "peer_tail" else "0"
     os.environ["FLYB_DP_STEP"] = "split" if mode == "peer_split" else "fused"
@@ -45,8 +47,10 @@ def _worker(rank, world, port, out, mode):
     try:
         torch.manual_seed(100 + rank)          # different initial nets per rank: the broadcast must align them
         args = fb.make_args(num_envs=2048, sim_device=f"cuda:{rank}", horizon=16, verbose=False, state_pool=4,
-                            seed=1234)           # IDENTICAL args on every rank: the library decorrelates the shards
+                            seed=1234,           # IDENTICAL args on every rank: the library decorrelates the shards
+                            **({"asset": "full_42", "full_actions": True} if wide else {}))
         agent = fb.PPO(args)
+        assert agent.net.wpack is not None and agent.num_act == (42 if wide else 18)
         assert agent.world_size == world and (agent._peers is not None) == (mode != "nccl")
         assert agent._dp_step == ("split" if mode == "peer_split" else "fused")
         agent.collect_rollout(use_graph=False)
@@ -56,7 +60,8 @@ def _worker(rank, world, port, out, mode):
         torch.cuda.synchronize()
         torch.save({"flat": agent.net.flat.cpu(), "m": agent.exp_avg.cpu(), "v": agent.exp_avg_sq.cpu(),
                     "steps": agent.optim_step, "loss": float(agent.loss), "acts_sum": acts_sum, "obs_sum": obs_sum,
-                    "peer_status": agent._peers.status() if agent._peers is not None else 0}, f"{out}.{mode}.{rank}")
+                    "peer_status": agent._peers.status() if agent._peers is not None else 0},
+                   f"{out}.{'wide_' if wide else ''}{mode}.{rank}")
         agent.exit()
     finally:
         dist.destroy_process_group()
@@ -71,7 +76,7 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
     res = {}
     # peer: exchange inside the reducing kernel, self-validating words (default); peer_split: push + fence, then flags +
     # sum in the norm kernel; peer_tail: the exchange inside the weight-gradient kernel's cooperative tail
-    for mode in ("peer", "peer_split", "nccl", "peer_tail"):
+    for mode in ("peer", "peer_split", "nccl", "peer_tail", "wide_peer", "wide_peer_split"):
         _spawn(_worker, world, out, mode)
         rs = [torch.load(f"{out}.{mode}.{r}") for r in range(world)]
         for r in rs[1:]:
@@ -93,6 +98,7 @@ def test_data_parallel_update_keeps_ranks_identical(tmp_path):
     # same sums in the same order; only the association of the norm's partial sums differs (an ulp in the clip coefficient)
     assert float((res["peer_tail"]["flat"] - res["peer_split"]["flat"]).abs().mean()) < 1e-3
     assert float((res["peer"]["flat"] - res["peer_split"]["flat"]).abs().mean()) < 1e-3
+    assert float((res["wide_peer"]["flat"] - res["wide_peer_split"]["flat"]).abs().mean()) < 1e-3
 
 
 def _soak_worker(rank, world, port, out, exchanges):
