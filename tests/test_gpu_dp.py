@@ -50,7 +50,7 @@ def _worker(rank, world, port, out, mode):
                             seed=1234,           # IDENTICAL args on every rank: the library decorrelates the shards
                             **({"asset": "full_42", "full_actions": True} if wide else {}))
         agent = fb.PPO(args)
-        assert agent.net.wpack is not None and agent.num_act == (42 if wide else 18)
+        assert agent.net.wpack is not None and agent.net.num_act == (42 if wide else 18)
         assert agent.world_size == world and (agent._peers is not None) == (mode != "nccl")
         assert agent._dp_step == ("split" if mode == "peer_split" else "fused")
         agent.collect_rollout(use_graph=False)
