@@ -427,8 +427,8 @@ pre_physics_finish_kernel(const __grid_constant__ FlybEnvCfg cfg, long long* __r
 using namespace flyb;
 
 extern "C" size_t flyb_env_scratch_bytes(int32_t num_envs) {
-  const size_t nblk = num_envs > 0 ? (size_t)(num_envs + ENVS - 1) / ENVS : 1;
-  return 16 + (nblk + 1) * sizeof(unsigned long long);   // + 1: the fused step publishes two words per 128-env tile
+  // masks: one word per 64 envs (+ 1: the fused step publishes two words per 128-env tile); tile counts behind them
+  return scan_scratch_bytes(num_envs > 0 ? num_envs : 1);
 }
 
 static int validate_cfg(const FlybEnvCfg* cfg) {

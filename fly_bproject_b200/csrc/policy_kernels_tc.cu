@@ -433,6 +433,7 @@ struct StepEnvArgs {
   int* reset_ids;
   int* reset_count;
   ScanScratch* scratch;
+  unsigned* tile_cnt;    // tagged per-tile reset counts behind the scratch's masks (env_scan.cuh)
 };
 
 constexpr int STEP_THREADS = tcm::THREADS + 32;   // + the mask / scan warp
@@ -772,26 +773,24 @@ struct StepFinal : ActFinal {
     if ((threadIdx.x & 31) == 0) tc::mbar_arrive(s.obs_empty);
   }
 
-  // the spare warp: publish the tile's masks, count the tile as done, scan the bitmap if it was the last one
+  // the spare warp: the tile's share of the reset-id compaction (env_scan.cuh: every tile writes its own ids once the
+  // tiles in front have published their counts); the last tile to get there closes the launch's ticket
   FLYB_D void aux_warp(const tcm::Smem&, long long ntiles) {
     if ((threadIdx.x >> 5) != STEP_AUX_WARP) return;
     const int lane = threadIdx.x & 31;
+    const unsigned tag = ld_relaxed_u32(&e.scratch->ticket) + 1u;   // bumped only after every tile of this launch is through
     unsigned par = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1u) {
       asm volatile("bar.sync 3, %0;" ::"n"(STEP_AUX_BAR_THREADS) : "memory");
-      unsigned last = 0;
+      const unsigned m[4] = {st->mask[par][0], st->mask[par][1], st->mask[par][2], st->mask[par][3]};
+      compact_tile_warp(e.tile_cnt, tag, tile, ntiles, m, e.reset_ids, e.reset_count);
       if (lane == 0) {
-        unsigned long long* bitmap = e.scratch->status;
-        const unsigned* m = st->mask[par];
-        st_status(bitmap + 2 * tile, ((unsigned long long)m[1] << 32) | (unsigned long long)m[0]);
-        st_status(bitmap + 2 * tile + 1, ((unsigned long long)m[3] << 32) | (unsigned long long)m[2]);
         __threadfence();
-        const unsigned prev = atomicAdd(&e.scratch->done, 1u);
-        last = (prev == (unsigned)(ntiles - 1)) ? 1u : 0u;
-        if (last) __threadfence();
+        if (atomicAdd(&e.scratch->done, 1u) == (unsigned)(ntiles - 1)) {
+          e.scratch->done = 0u;        // re-armed for the next launch (of this kernel or of post_physics_kernel)
+          e.scratch->ticket = tag;
+        }
       }
-      last = __shfl_sync(0xffffffffu, last, 0);
-      if (last) scan_masks_warp(e.scratch, (int)(2 * ntiles), e.reset_ids, e.reset_count);
     }
   }
 };
@@ -1014,6 +1013,7 @@ int tc_launch_step(const FlybNetLayout* net, const float* params, const void* wp
   y.env.force = io->force; y.env.obs_out = io->obs; y.env.reward = io->reward; y.env.reward_ring = io->reward_ring;
   y.env.reward_sum = io->reward_sum; y.env.up_vec = io->up_vec; y.env.heading_vec = io->heading_vec;
   y.env.reset_ids = io->reset_ids; y.env.reset_count = io->reset_count; y.env.scratch = (ScanScratch*)io->scratch;
+  y.env.tile_cnt = scan_tile_counts(y.env.scratch, cfg->num_envs);
   y.anneal_steps = io->anneal_steps; y.anneal_decay = io->anneal_decay; y.anneal_floor = io->anneal_floor;
   const size_t smem = tcm::smem_bytes(net->num_obs, out);
   const long long ntiles = (rows + tcm::TM - 1) / tcm::TM;

@@ -541,6 +541,44 @@ def test_env_counts_that_misalign_the_rollout_rows(n):
     assert agent.optim_step == 75 and bool(torch.isfinite(agent.net.flat).all())
 
 
+@pytest.mark.parametrize("n", [16384, 100, 4096 + 77, 128 * 148, 128 * 148 - 5, 40000, 1])
+def test_fused_step_compacts_its_own_reset_ids(n):
+    """The id list the fused env step leaves behind (every tile writes its own ids once the tiles in front have published
+    their counts) == the envs flagged by that step (reset_buf.nonzero() at fly.py:447), ascending, with the count — checked on the LAST fused launch of a
+    rollout, i.e. with the closing obs / reward / reset launch (which would rewrite the list) left out; repeated, so that
+    the launch ticket and the counter re-arm are exercised across launches and across the two kernels."""
+    if not TC:
+        pytest.skip("the fused step exists on the tensor-core path only")
+    horizon = 6
+    ag = fb.PPO(fb.make_args(num_envs=n, sim_device=DEV, horizon=horizon, verbose=False, state_pool=3, seed=5,
+                             fused_steps=True))
+    env = ag.env
+    closing = env.post_physics
+    seen = set()
+    for rep in range(3):
+        env.post_physics = lambda **kw: None          # rollout without its closing launch
+        try:
+            ag._rollout_kernels()
+        finally:
+            env.post_physics = closing
+        torch.cuda.synchronize()
+        # the launch's act half has already performed the reset and cleared the mask (fly.py:476-477): the envs it listed
+        # are the ones whose progress counter is back at 0 (everyone else's was incremented, fly.py:678)
+        want = (env.progress_buf == 0).nonzero().squeeze(-1).to(torch.int32)
+        assert int(env.reset_buf.sum()) == 0
+        cnt = int(env.reset_count.item())
+        assert cnt == want.numel(), (rep, cnt, want.numel())
+        assert torch.equal(env.reset_ids[:cnt], want), rep
+        seen.add(cnt)
+        if rep == 1:                                   # a stand-alone launch in between shares the counter
+            env.post_physics()
+            torch.cuda.synchronize()
+            want = env.reset_buf.nonzero().squeeze(-1).to(torch.int32)
+            assert int(env.reset_count.item()) == want.numel()
+            assert torch.equal(env.reset_ids[:want.numel()], want)
+    assert n < 64 or max(seen) > 0
+
+
 @pytest.mark.parametrize("n,horizon,pool,explicit_noise", [(16384, 32, 16, False), (40000, 8, 4, True), (100, 4, 2, False),
                                                            (4096 + 77, 16, 4, True)])
 def test_fused_rollout_is_bit_identical_to_the_two_kernel_rollout(n, horizon, pool, explicit_noise):
