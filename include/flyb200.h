@@ -142,7 +142,9 @@ int flyb_pack_weights(const FlybNetLayout* net, const float* params, void* wpack
  *      reset_count (1) i32.  obs_copy / reward_copy (nullable) receive a second copy (rollout rows, ppo.py:228-229);
  *      reward_sum (1, nullable) += sum(reward) — the device-side accumulator behind the score log (ppo.py:233).
  *      tail (nullable): FlybStepTail applied by the last CTA to finish.
- * scratch: flyb_env_scratch_bytes(N) bytes, zeroed once by the caller before first use. */
+ * scratch: flyb_env_scratch_bytes(N) bytes, zeroed once by the caller before first use (a counter pair, one 64-bit
+ *      reset mask per 64 envs, one tagged reset count per 128-env tile for the fused step's compaction); one scratch
+ *      buffer serves flyb_env_post_physics and flyb_env_step_fused of the same env batch, on one stream. */
 size_t flyb_env_scratch_bytes(int32_t num_envs);
 int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, const float* dof_state, const float* force,
                           const float* actions_scaled, float* potentials, float* prev_potentials, int64_t* progress,
