@@ -80,6 +80,22 @@ def test_tensor_core_shapes(built_lib):
     assert sizes[(163, 48)] == 0 and sizes[(145, 49)] == 0
 
 
+def test_exchange_and_scratch_buffer_sizes(built_lib):
+    """Host-side size functions (no GPU): the peer exchange buffer holds the float slots of the split exchange, 256 bytes
+    of control and the 64-bit words of the fused one (include/flyb200.h, FlybPeerGroup); the env scratch holds a counter
+    pair, one mask per 64 envs (+ 1) and one tagged count per 128-env tile."""
+    from fly_bproject_b200 import _lib
+    lib = _lib.lib()
+    for total, world in [(69587, 2), (69587, 8), (95000, 4), (1, 1)]:
+        pad = lib.flyb_peer_total_pad(total)
+        assert pad >= total and pad % 64 == 0 and pad - total < 64
+        assert lib.flyb_peer_bytes(total, world) == 2 * world * pad * 4 + 256 + 2 * world * pad * 8
+    assert lib.flyb_peer_bytes(69587, 9) == 0 and lib.flyb_peer_bytes(0, 2) == 0
+    for n in (1, 64, 100, 16384, 18944, 100003):
+        masks, tiles = (n + 63) // 64 + 1, (n + 127) // 128 + 1
+        assert lib.flyb_env_scratch_bytes(n) == 16 + 8 * masks + 8 * ((tiles + 1) // 2)
+
+
 def test_product_path_fails_loudly_without_cuda(built_lib):
     import torch
     if torch.cuda.is_available():
