@@ -300,7 +300,10 @@ def run_own(args, cfg):
     # clip + Adam on the tensor-core path; with the split exchange (or the CUDA-core path) a norm kernel in between
     ppo_tc = tc_path and int(agent.net.layout.k0_pad) in (80, 160)     # the two compiled shapes of the PPO step
     four = ppo_tc and (world == 1 or (agent._peers is not None and agent._dp_step == "fused"))
-    launches_update = 2 + n_minibatches * (4 if four else 5)
+    # opt-in (FLYB_ADAM_FUSED=1, measured slower): clip + Adam inside the reduction when its whole grid (one CTA per 256
+    # entries) can be resident at once: two CTAs of that kernel per SM (tc_ppo_grad checks the same by the occupancy API)
+    adam_in = four and (int(agent.net.layout.total) + 255) // 256 <= 2 * 148 and os.environ.get("FLYB_ADAM_FUSED", "0") == "1"
+    launches_update = 2 + n_minibatches * (3 if adam_in else 4 if four else 5)
     launches = K * REPEATS * (launches_rollout + launches_update)
 
     # ---------------- per-kernel device times, each kernel alone in a graph (pool rotation keeps L2 cold)

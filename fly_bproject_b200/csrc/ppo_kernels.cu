@@ -36,7 +36,8 @@ struct StepFuse {
   float *params, *exp_avg, *exp_avg_sq, *grad_norm_out;
   double lr, beta1, beta2, eps, max_norm;
   int done;   // out: 1 = the step was completed by the tail (no Adam launch needed); 2 = the reduction did the
-              // fused exchange (grad = sum over ranks, sq_part filled): clip + Adam are left
+              // fused exchange (grad = sum over ranks, sq_part filled): clip + Adam are left; 3 = the reduction also ran
+              // clip + Adam (no launch left)
   float grad_scale;   // 1 / world when the tail also does the data-parallel exchange (peers != NULL), else 1
   int exchange;   // in: with peers and no tail, the reducing kernel does the exchange itself (flyb_ppo_step_dp)
 };
@@ -595,7 +596,7 @@ extern "C" int flyb_ppo_step_dp(const FlybNetLayout* net, const FlybPpoCfg* cfg,
   rc = tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
                    workspace, peers, st, &fuse);
   if (rc != FLYB_OK) return rc;
-  if (fuse.done == 1) return FLYB_OK;   // cooperative tail: everything happened in the weight-gradient kernel
+  if (fuse.done == 1 || fuse.done == 3) return FLYB_OK;   // cooperative tail, or clip + Adam inside the reduction
   // fused exchange: the reduction left the sum over ranks in `grad` and its squared-norm partials; Adam closes the epoch
   return launch_adam(net, cfg, params, grad, exp_avg, exp_avg_sq, (const long long*)step, grad_scale, grad_norm_out,
                      fuse.sq_part, fuse.sq_parts, wpack, peers, st);
@@ -636,7 +637,7 @@ extern "C" int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, fl
   rc = tc_ppo_grad(net, cfg, params, wpack, obs, action, old_logp, target, advantage, action_var, rows, grad, loss,
                    workspace, nullptr, st, &fuse);
   if (rc != FLYB_OK) return rc;
-  if (fuse.done) return FLYB_OK;   // 2 launches: chain, weight gradients + reduction + clip + Adam
+  if (fuse.done) return FLYB_OK;   // cooperative tail (2 launches) or clip + Adam inside the reduction (3 launches)
   return launch_adam(net, cfg, params, grad, exp_avg, exp_avg_sq, (const long long*)step, 1.0f, grad_norm_out,
                      fuse.sq_part, fuse.sq_parts, wpack, nullptr, st);
 }

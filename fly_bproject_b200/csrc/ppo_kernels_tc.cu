@@ -1106,6 +1106,19 @@ struct ReduceArgs {
   long long* step;  // with sq_part: Adam's step counter, += 1 (the norm kernel's other job)
   float scale;      // PEERS == 2: the squares are taken of scale * (sum over ranks), scale = 1 / world
 };
+// ADAM: clip + Adam ride in the same launch.  Every CTA publishes its sum of squares as a 64-bit word tagged with the
+// launch's number, warp 0 of every CTA gathers all of them (spinning on the tag; the grid is small enough to be resident
+// as a whole — checked by the host — and every CTA publishes before it waits), adds them in ppo_adam_kernel's order (same
+// clip coefficient, bit for bit) and the threads that hold the gradient quads apply Adam to their own entries.  One
+// launch and one launch gap fewer per optimiser step than reduce -> ppo_adam_kernel — and 4 us slower (opt-in).
+struct ReduceAdam {
+  unsigned long long* sq_tag;   // [gridDim.x]  {launch tag << 32 | float bits}
+  float *params, *exp_avg, *exp_avg_sq, *grad_norm_out, *wpack;
+  const int4* wpack_index;
+  uint32_t* peer_epoch;         // nullable: data-parallel exchange epoch, closed here
+  AdamArgs adam;
+};
+__device__ unsigned g_red_seq;   // launches of the ADAM form completed on this device (strictly increasing): the tag
 // 256 threads: 64 QUADS of gradient entries (four consecutive floats, one 128-bit load per partial) x 4 interleaved
 // partial groups.  Per entry the association is what it was with one entry per thread — group g adds partials g, g + 4,
 // ... in order, then (s0 + s1) + (s2 + s3) — so the gradient bits do not depend on the vector width.
@@ -1115,15 +1128,23 @@ struct ReduceArgs {
 // peer_ll_sum4), so that `grad` leaves this kernel as the sum over ranks, with its squared-norm partials, and clip + Adam
 // follow with no norm kernel.
 constexpr int RED_QUADS = 64, RED_ELEMS = 4 * RED_QUADS, RED_GROUPS = 4;
-template <int PEERS>
+template <int PEERS, bool ADAM>
 __global__ void __launch_bounds__(RED_QUADS * RED_GROUPS)
 ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restrict__ dw_part,
                      const float* __restrict__ loss_part, float* __restrict__ grad, float* __restrict__ loss,
-                     const __grid_constant__ PeerView pv) {
+                     const __grid_constant__ PeerView pv, const __grid_constant__ ReduceAdam ad) {
   __shared__ float4 s_acc[RED_GROUPS][RED_QUADS];
   __shared__ float s_sq[2];
+  __shared__ AdamCoef s_coef;
   const int e = threadIdx.x & (RED_QUADS - 1), pg = threadIdx.x / RED_QUADS;
   const int i = blockIdx.x * RED_ELEMS + 4 * e;      // first entry of this thread's quad (total is a multiple of 4)
+  // ADAM: both are advanced by CTA 0 only after every CTA has published, i.e. after every thread has read them here
+  unsigned tag = 0u;
+  long long step_new = 0;
+  if (ADAM) {
+    tag = *(volatile const unsigned*)&g_red_seq + 1u;
+    step_new = *(volatile const long long*)a.step + 1;
+  }
   uint32_t epoch = 0;
   if (PEERS) {
     epoch = *(volatile const uint32_t*)pv.epoch;   // bumped by ppo_adam_kernel, i.e. after this exchange
@@ -1177,8 +1198,14 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
   if (a.sq_part) {
     __syncthreads();
     if (threadIdx.x == 0) {
-      a.sq_part[blockIdx.x] = s_sq[0] + s_sq[1];
-      if (blockIdx.x == 0) *a.step += 1;
+      const float sq = s_sq[0] + s_sq[1];
+      if (ADAM) {
+        const unsigned long long w = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(sq);
+        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(ad.sq_tag + blockIdx.x), "l"(w) : "memory");
+      } else {
+        a.sq_part[blockIdx.x] = sq;
+        if (blockIdx.x == 0) *a.step += 1;
+      }
       if (PEERS == 2 && blockIdx.x == 0) pv.stamp[5] = global_ns();
     }
   }
@@ -1192,6 +1219,37 @@ ppo_reduce_tc_kernel(const __grid_constant__ ReduceArgs a, const float* __restri
     y = warp_sum(y);
     if (threadIdx.x == 0) *loss = -x * a.inv_rows + y * a.inv_rows;
   }
+  if (ADAM) {
+    if (threadIdx.x < 32) {
+      float t = 0.0f;   // ppo_adam_kernel's order: lane l adds partials l, l + 32, ...; then the butterfly
+      for (int k = threadIdx.x; k < (int)gridDim.x; k += 32) {
+        unsigned long long w;
+        for (;;) {
+          asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(ad.sq_tag + k) : "memory");
+          if ((unsigned)(w >> 32) == tag) break;
+          __nanosleep(32);
+        }
+        t += __uint_as_float((unsigned)w);
+      }
+      t = warp_sum(t);
+      if (threadIdx.x == 0) {
+        s_coef = adam_coefficients(ad.adam, t, step_new);
+        if (blockIdx.x == 0) {   // every CTA has published, so every thread of the grid has read step / tag / epoch
+          if (ad.grad_norm_out) *ad.grad_norm_out = s_coef.total_norm;
+          *a.step = step_new;
+          if (ad.peer_epoch) *ad.peer_epoch += 1;   // this exchange is over
+          atomicAdd(&g_red_seq, 1u);
+        }
+      }
+    }
+    __syncthreads();
+    if (pg == 0 && i < a.total) {
+      const AdamCoef c = s_coef;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)   // grad[i + j] was stored by this very thread
+        adam_entry(i + j, ad.adam, c, ad.params, grad, ad.exp_avg, ad.exp_avg_sq, ad.wpack, ad.wpack_index);
+    }
+  }
 }
 
 struct Ws {
@@ -1200,6 +1258,7 @@ struct Ws {
   float* loss_part;
   float* dw_part;
   float* sq_part;     // [red_grid] per-CTA sums of squared gradient entries (flyb_ppo_step)
+  unsigned long long* sq_tag;   // [red_grid] the same as tagged words (reduction with clip + Adam inside)
   int grid1, ctas_per_role, red_grid;
   size_t bytes;
 };
@@ -1231,6 +1290,7 @@ static Ws carve_ws(const FlybNetLayout& net, long long rows, void* basep) {
   w.dw_part = take((size_t)w.ctas_per_role * net.total);
   w.red_grid = (net.total + RED_ELEMS - 1) / RED_ELEMS;
   w.sq_part = take((size_t)w.red_grid);
+  w.sq_tag = reinterpret_cast<unsigned long long*>(take((size_t)2 * w.red_grid));
   w.bytes = off;
   return w;
 }
@@ -1329,17 +1389,43 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
     fuse->sq_part = w.sq_part;
     fuse->sq_parts = red_grid;
   }
+  // Opt-in (FLYB_ADAM_FUSED=1; measured SLOWER than the separate Adam kernel: 142.9 vs 138.7 us per optimiser step —
+  // gathering 272 partials in every CTA and 64 threads per CTA doing Adam cost more than the launch they save): clip +
+  // Adam inside the reduction, when the caller goes straight on to Adam and the whole grid can be resident at once (its
+  // CTAs wait for each other's norm partials).
+  const dim3 rb(RED_QUADS * RED_GROUPS);
+  ReduceAdam ad{};
+  bool adam_in = false;
+  if (fuse && (!peers || fused_exchange) && fuse->params) {
+    const char* env = getenv("FLYB_ADAM_FUSED");   // read per call: a test flips it
+    static const int resident = [] {
+      int per_sm0 = 0, per_sm2 = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm0, ppo_reduce_tc_kernel<0, true>, RED_QUADS * RED_GROUPS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, ppo_reduce_tc_kernel<2, true>, RED_QUADS * RED_GROUPS, 0);
+      return std::min(per_sm0, per_sm2) * num_sms();
+    }();
+    adam_in = env && env[0] == '1' && red_grid <= resident;
+  }
+  if (adam_in) {
+    ad.sq_tag = w.sq_tag;
+    ad.params = fuse->params; ad.exp_avg = fuse->exp_avg; ad.exp_avg_sq = fuse->exp_avg_sq;
+    ad.grad_norm_out = fuse->grad_norm_out;
+    ad.wpack = (float*)const_cast<void*>(wpack);
+    ad.wpack_index = (const int4*)tc_wpack_index(net, wpack);
+    ad.peer_epoch = peers ? make_peer_view(*peers).epoch : nullptr;
+    ad.adam = AdamArgs{fuse->lr, fuse->beta1, fuse->beta2, fuse->eps, fuse->max_norm, peers ? fuse->grad_scale : 1.0f};
+  }
   if (fused_exchange) {
     r.scale = fuse->grad_scale;
-    ppo_reduce_tc_kernel<2><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
-                                                                         make_peer_view(*peers));
-    fuse->done = 2;   // exchanged: only clip + Adam are left
+    if (adam_in) ppo_reduce_tc_kernel<2, true><<<red_grid, rb, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss, make_peer_view(*peers), ad);
+    else ppo_reduce_tc_kernel<2, false><<<red_grid, rb, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss, make_peer_view(*peers), ad);
+    fuse->done = adam_in ? 3 : 2;   // 2: exchanged, only clip + Adam are left; 3: the whole step is done
   } else if (peers) {
-    ppo_reduce_tc_kernel<1><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
-                                                                         make_peer_view(*peers));
+    ppo_reduce_tc_kernel<1, false><<<red_grid, rb, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss, make_peer_view(*peers), ad);
   } else {
-    ppo_reduce_tc_kernel<0><<<red_grid, RED_QUADS * RED_GROUPS, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss,
-                                                                         PeerView{});
+    if (adam_in) ppo_reduce_tc_kernel<0, true><<<red_grid, rb, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss, PeerView{}, ad);
+    else ppo_reduce_tc_kernel<0, false><<<red_grid, rb, 0, st>>>(r, w.dw_part, w.loss_part, grad, loss, PeerView{}, ad);
+    if (adam_in) fuse->done = 3;
   }
   FLYB_LAUNCH_CHECK("ppo_reduce_tc_kernel");
   return FLYB_OK;

@@ -461,10 +461,12 @@ def test_ppo_step_is_grad_plus_apply_and_keeps_the_weight_stream_in_step():
                                            g["roll_target"][0:mc], g["roll_adv"][0:mc], g["roll_var"])]
     out = {}
     import os
-    for mode in ("split", "fused", "fused_tail"):
-        # "fused_tail": FLYB_PPO_TAIL=1, the two-launch form (reduction + clip + Adam behind grid barriers in the tail of
-        # the cooperatively launched weight-gradient kernel) — opt-in, measured slower than the four launches
+    for mode in ("split", "fused", "fused_3", "fused_tail"):
+        # "fused": four launches (the default); "fused_3": FLYB_ADAM_FUSED=1, clip + Adam inside the gradient reduction
+        # (three launches; opt-in, measured slower); "fused_tail": FLYB_PPO_TAIL=1, the two-launch form (reduction + clip + Adam behind grid
+        # barriers in the tail of the cooperatively launched weight-gradient kernel) — opt-in, measured slower
         os.environ["FLYB_PPO_TAIL"] = "1" if mode == "fused_tail" else "0"
+        os.environ["FLYB_ADAM_FUSED"] = "1" if mode == "fused_3" else "0"
         net = golden_net(g)
         ws = torch.zeros(lib.flyb_ppo_workspace_bytes(C.byref(net.layout), rows) + 256, dtype=torch.uint8, device=DEV)
         wsp = (ws.data_ptr() + 255) // 256 * 256
@@ -492,10 +494,16 @@ def test_ppo_step_is_grad_plus_apply_and_keeps_the_weight_stream_in_step():
             norms.append(float(gn))
             if it == 0:
                 out[mode] = [net.flat.clone(), m.clone(), v.clone(), loss.clone()]
-        out[mode] += [float(loss), norms]
+        out[mode] += [float(loss), norms, net.flat.clone(), m.clone(), v.clone()]
     os.environ.pop("FLYB_PPO_TAIL", None)
+    os.environ.pop("FLYB_ADAM_FUSED", None)
+    if TC:   # Adam inside the reduction adds the norm partials in the Adam kernel's own order: nothing moves, not a bit
+        a, b = out["fused"], out["fused_3"]
+        assert a[4] == b[4] and a[5] == b[5]
+        for k in (0, 1, 2, 3, 6, 7, 8):
+            assert torch.equal(a[k], b[k]), k
     a = out["split"]
-    for other in ("fused", "fused_tail"):
+    for other in ("fused", "fused_3", "fused_tail"):
         b = out[other]
         # step 1: same gradient bit for bit; the forms differ only in how the norm's partial sums are grouped, i.e. the
         # clip coefficient moves by an ulp or two.  Later steps start from those ulp-apart parameters.
