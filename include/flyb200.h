@@ -331,6 +331,8 @@ int flyb_ppo_apply(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* param
  * launched cooperatively, its tail — behind grid barriers — summing the per-CTA partials in the fixed order of the
  * stand-alone reduction (bit-identical gradient), taking the norm and running clip + Adam; measured 3 us slower per
  * step than the four launches, hence opt-in.
+ * FLYB_ADAM_FUSED=1 selects a three-launch form (clip + Adam inside the reduction, the CTAs gathering each other's
+ * tagged norm partials; bit-identical results): measured 4 us slower per step as well, opt-in.
  * Same results as the two calls up to the association of the norm's partial sums.  `grad` ends as p.grad after
  * clipping, as with flyb_ppo_apply. */
 int flyb_ppo_step(const FlybNetLayout* net, const FlybPpoCfg* cfg, float* params, void* wpack, const float* obs,
