@@ -86,6 +86,7 @@ SIGNATURES = {
     "flyb_pack_weights": (C.c_int, [C.POINTER(NetLayout), _P, _P, _P]),
     "flyb_env_scratch_bytes": (C.c_size_t, [C.c_int32]),
     "flyb_env_post_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 18 + [C.POINTER(StepTail), _P]),
+    "flyb_env_post_physics_static": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 17 + [C.POINTER(StepTail), _P]),
     "flyb_env_pre_physics": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 10),
     "flyb_env_reset": (C.c_int, [C.POINTER(EnvCfg)] + [_P] * 7),
     "flyb_env_step_fused_supported": (C.c_int, [C.POINTER(NetLayout), C.POINTER(EnvCfg)]),

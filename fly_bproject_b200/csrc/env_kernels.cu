@@ -15,6 +15,7 @@
 //     one 64-bit mask per CTA -> the last CTA to finish scans the bitmap and writes the id list; the count
 //     stays on the device — the reference's host sync at fly.py:447-450 is gone.
 #include <cstdlib>
+#include <mutex>
 
 #include "env_math.cuh"
 #include "env_scan.cuh"
@@ -484,6 +485,66 @@ extern "C" int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, c
       reward_copy, reward_sum, t, tc_get_trace(), force_bulk);
   FLYB_LAUNCH_CHECK("post_physics_kernel");
   return FLYB_OK;
+}
+
+// ---- flyb_env_post_physics for hosts that have no way to hand us scratch memory.
+// Who that is: a binding that only forwards the simulator's own tensors (the ctypes stub of INTEGRATION.md run without
+// torch or a CUDA-runtime binding has device pointers to Isaac Gym's wrapped views but no allocator of its own), and a
+// host that calls us from inside the simulator's step loop, where a cudaMalloc would stall the whole device (it
+// synchronises implicitly) or simply fail because the simulator reserved the card's memory up front.
+// The reset-id compaction needs a counter and one mask word per 64 envs that are neither input nor output.  Here they
+// live in the library image itself: every GPU that loads libflyb200.so carries these ~40 KB until the process exits.
+constexpr size_t static_scratch_need(size_t n) {   // == scan_scratch_bytes(n), spelled as a constant expression
+  return 16 + ((n + SCAN_ENVS - 1) / SCAN_ENVS + 1) * 8 + ((((n + 127) / 128 + 1) + 1) / 2) * 8;
+}
+constexpr size_t STATIC_SCRATCH_BYTES = (static_scratch_need(FLYB_STATIC_MAX_ENVS) + 255) / 256 * 256;
+static __device__ __align__(256) unsigned char g_static_env_scratch[STATIC_SCRATCH_BYTES];
+
+// In host code `g_static_env_scratch` is only a handle for the runtime's symbol table, NOT an address a kernel may
+// dereference; the device address differs per GPU and is looked up once per device, with that device current.
+static int static_env_scratch(void** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static void* dev_ptr[MAX_DEV] = {};
+  int dev = -1;
+  int rc = flyb::check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(dev >= 0 && dev < MAX_DEV, "flyb_env_post_physics_static: device ordinal %d out of [0, %d)", dev, MAX_DEV);
+  std::lock_guard<std::mutex> lock(mu);
+  if (dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    rc = flyb::check_cuda(cudaGetSymbolAddress(&p, g_static_env_scratch), "cudaGetSymbolAddress(static env scratch)");
+    if (rc != FLYB_OK) return rc;
+    FLYB_REQUIRE(p != nullptr, "flyb_env_post_physics_static: the runtime returned no address for the built-in scratch");
+    dev_ptr[dev] = p;
+  }
+  *out = dev_ptr[dev];
+  return FLYB_OK;
+}
+
+extern "C" int flyb_env_post_physics_static(const FlybEnvCfg* cfg, const float* root, const float* dof_state,
+                                            const float* force, const float* actions_scaled, float* potentials,
+                                            float* prev_potentials, int64_t* progress, int64_t* reset, float* obs,
+                                            float* reward, float* up_vec, float* heading_vec, int32_t* reset_ids,
+                                            int32_t* reset_count, float* obs_copy, float* reward_copy,
+                                            float* reward_sum, const FlybStepTail* tail, void* stream) {
+  int rc = validate_cfg(cfg);
+  if (rc != FLYB_OK) return rc;
+  FLYB_REQUIRE(cfg->num_envs <= FLYB_STATIC_MAX_ENVS,
+               "flyb_env_post_physics_static: num_envs %d exceeds the built-in scratch (FLYB_STATIC_MAX_ENVS = %d); "
+               "use flyb_env_post_physics with a caller-owned scratch buffer", cfg->num_envs, FLYB_STATIC_MAX_ENVS);
+  FLYB_REQUIRE(scan_scratch_bytes(cfg->num_envs) <= STATIC_SCRATCH_BYTES,
+               "flyb_env_post_physics_static: scratch layout grew past the built-in array");
+  void* scratch = nullptr;
+  rc = static_env_scratch(&scratch);   // first call on this device: symbol look-up (may load the module)
+  if (rc != FLYB_OK) return rc;
+  // The array still holds whatever the previous call (any env count, any stream) left.  The kernel relies on the
+  // finished-CTA counter starting at zero; the mask words need no clearing (every CTA stores its own before counting).
+  rc = flyb::check_cuda(cudaMemsetAsync(scratch, 0, 16, (cudaStream_t)stream), "cudaMemsetAsync(static env scratch header)");
+  if (rc != FLYB_OK) return rc;
+  return flyb_env_post_physics(cfg, root, dof_state, force, actions_scaled, potentials, prev_potentials, progress,
+                               reset, obs, reward, up_vec, heading_vec, reset_ids, reset_count, scratch, obs_copy,
+                               reward_copy, reward_sum, tail, stream);
 }
 
 extern "C" int flyb_env_pre_physics(const FlybEnvCfg* cfg, const float* actions, float* actions_scaled,

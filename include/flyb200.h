@@ -152,6 +152,29 @@ int flyb_env_post_physics(const FlybEnvCfg* cfg, const float* root, const float*
                           int32_t* reset_ids, int32_t* reset_count, void* scratch, float* obs_copy,
                           float* reward_copy, float* reward_sum, const FlybStepTail* tail, void* stream);
 
+/* ---- flyb_env_post_physics without a scratch argument.  No counterpart in the reference: it exists for hosts of this
+ *      library that cannot allocate device memory — a binding that only passes the simulator's wrapped tensors through
+ *      (plain ctypes / C, no torch and no CUDA-runtime binding to allocate with), or a caller inside the simulator's
+ *      step loop, where cudaMalloc would synchronise the whole device or fail because the simulator took the memory up
+ *      front.  The counter and reset masks the kernel needs live in an array built into the library image (~40 KB of
+ *      device memory on every GPU that loads the library, held until the process exits); inputs and outputs are still
+ *      the caller's.  Same arguments, same kernel and same results as flyb_env_post_physics.  The call itself
+ *      allocates nothing (no cudaMalloc / cudaFree, no library routine that allocates).
+ *      Limits and rules:
+ *      - cfg->num_envs <= FLYB_STATIC_MAX_ENVS, else FLYB_EINVAL with a message naming the limit;
+ *      - the first call on each device looks the array's device address up (cudaGetSymbolAddress, with that device
+ *        current) and caches it; make that first call outside any stream capture;
+ *      - all calls on a device share the one array and it keeps the previous call's contents: the entry point clears
+ *        the 16-byte counter header on `stream` before every launch, so calls of different env counts may follow each
+ *        other, but two calls that can overlap on the GPU (different streams without an ordering, several host threads)
+ *        race on it — serialise them, or give all but one a buffer of their own through flyb_env_post_physics. */
+#define FLYB_STATIC_MAX_ENVS 262144
+int flyb_env_post_physics_static(const FlybEnvCfg* cfg, const float* root, const float* dof_state, const float* force,
+                                 const float* actions_scaled, float* potentials, float* prev_potentials,
+                                 int64_t* progress, int64_t* reset, float* obs, float* reward, float* up_vec,
+                                 float* heading_vec, int32_t* reset_ids, int32_t* reset_count, float* obs_copy,
+                                 float* reward_copy, float* reward_sum, const FlybStepTail* tail, void* stream);
+
 /* ---- env: reference Fly.step up to simulate() (fly.py:626-660): scale policy actions to the joint range,
  *      scatter into the DOF position-target vector, then Fly.reset() (fly.py:446-480) for envs whose mask is set.
  * In:  actions (N,A) in [-1,1].  Out: actions_scaled (N,A), dof_targets (N*D).
