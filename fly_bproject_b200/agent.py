@@ -191,8 +191,11 @@ class PPO:
             if self.verbose:
                 print("loaded from: ", str(args.load_path))
             # ppo.py:147-149; a `.flyb.pt` sidecar next to the file (checkpoint.py) also brings back what the reference
-            # loses on resume, unless args.resume is False
-            sd, resume_state = checkpoint.load_checkpoint(args.load_path, o, a, want_sidecar=bool(_get(args, "resume", True)))
+            # loses on resume, unless args.resume is False.  Evaluation (args.testing: trainer.py --testing --load_path,
+            # ppo.py:151) takes the weights only: it must act at action_var = 0.01 with fresh counters, not at the
+            # saved training variance
+            want_sidecar = bool(_get(args, "resume", True)) and not bool(_get(args, "testing", False))
+            sd, resume_state = checkpoint.load_checkpoint(args.load_path, o, a, want_sidecar=want_sidecar)
             self.net.load_state_dict(sd)
 
         action_var = 0.01 if _get(args, "testing", False) else 0.2                    # ppo.py:151-152

@@ -117,3 +117,13 @@ def test_resume_is_bit_identical_to_uninterrupted_run(tmp_path):
     # without the sidecar the same file is a plain reference checkpoint: weights only
     c = fb.PPO(mk(load=True, load_path=base + "75.pth", resume=False))
     assert c.optim_step == 0 and float(c.action_var[0]) == pytest.approx(0.2) and int(c.adam_step.item()) == 0
+    # evaluation (trainer.py --testing --load_path, ppo.py:151): weights from the file, variance 0.01 and fresh counters
+    # even though a sidecar with the training variance sits next to it
+    assert os.path.exists(ck.sidecar_path(base + "75.pth"))
+    d = fb.PPO(mk(load=True, load_path=base + "75.pth", testing=True))
+    assert torch.equal(d.action_var, torch.full_like(d.action_var, 0.01))
+    assert d.optim_step == 0 and d.run_step == 0 and int(d.adam_step.item()) == 0
+    e = fb.PPO(mk(load=True, load_path=base + "75.pth", resume=False))
+    assert torch.equal(d.net.flat, e.net.flat)
+    d.run()
+    assert torch.equal(d.action_var, torch.full_like(d.action_var, 0.01))      # testing mode does not anneal
