@@ -398,6 +398,9 @@ class PPO:
             self._rollout_kernels(noise)
             self.run_step += t
             return
+        if noise is not None:
+            raise _lib.FlybError("collect_rollout: explicit `noise` needs use_graph=False (the captured rollout draws "
+                                 "from Philox; a replay could not pick up a new noise tensor)")
         g = self._graphs.get("rollout")
         if g is None:
             pool = len(getattr(self.env.state, "pool", [None]))

@@ -632,3 +632,13 @@ def test_fused_rollout_is_bit_identical_to_the_two_kernel_rollout(n, horizon, po
         torch.cuda.synchronize()
         for name in ("_obs_ring", "all_acts", "all_log_prob", "all_reward", "action_var"):
             assert torch.equal(getattr(a, name), getattr(c, name)), name
+
+
+def test_captured_rollout_refuses_explicit_noise():
+    """A captured rollout draws from Philox: handing it a noise tensor must fail loudly, not be dropped."""
+    ag = fb.PPO(fb.make_args(num_envs=256, sim_device=DEV, horizon=4, verbose=False, state_pool=2))
+    noise = torch.zeros(4, 256, 18, device=DEV)
+    with pytest.raises(fb.FlybError, match="use_graph=False"):
+        ag.collect_rollout(noise=noise)
+    ag.collect_rollout(use_graph=False, noise=noise)        # eager takes it: zero noise -> action == clip(mu)
+    assert ag.run_step == 4
