@@ -464,6 +464,11 @@ struct StepFinal : ActFinal {
   int force_bulk;          // 0: gather through the LSU
   unsigned force_phase;    // phase of s.obs_full
   bool first_tile;
+  // back-pressure from the spare warp (persistent loop, more than one tile per CTA): it arrives here once it holds a
+  // tile's masks in registers; the epilogue warps hand over the NEXT tile's masks (bar.arrive 3) only after that, so
+  // named barrier 3 never collects two arrivals of the same warp and mask[][] is never overwritten unread
+  uint64_t* aux_done;
+  unsigned tiles_handed;   // tiles of this CTA whose masks the epilogue warps have handed to the spare warp
 
   int tb_;   // next env-phase trace slot (172..189), thread 0 of CTA 0
   FLYB_D void emark() {
@@ -729,6 +734,9 @@ struct StepFinal : ActFinal {
       }
     }
     tc::fence_proxy_async();   // the tile's rows in s.obs -> visible to the bulk stores of begin_tile
+    // the spare warp has taken the previous tile's masks (its arrival number `tiles_handed - 1`, phases alternate)
+    if (tiles_handed > 0u && threadIdx.x == 0) tc::mbar_wait(aux_done, (tiles_handed - 1u) & 1u);
+    ++tiles_handed;
     tcm::epi_bar_sync();
     asm volatile("bar.arrive 3, %0;" ::"n"(STEP_AUX_BAR_THREADS) : "memory");   // masks are in shared memory: wake the spare warp
     parity ^= 1u;
@@ -783,6 +791,8 @@ struct StepFinal : ActFinal {
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, par ^= 1u) {
       asm volatile("bar.sync 3, %0;" ::"n"(STEP_AUX_BAR_THREADS) : "memory");
       const unsigned m[4] = {st->mask[par][0], st->mask[par][1], st->mask[par][2], st->mask[par][3]};
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(aux_done);   // masks taken: the epilogue warps may hand over the next tile's
       compact_tile_warp(e.tile_cnt, tag, tile, ntiles, m, e.reset_ids, e.reset_count);
       if (lane == 0) {
         __threadfence();
@@ -859,8 +869,14 @@ env_step_tc_kernel(const __grid_constant__ FlybNetLayout net, const __grid_const
                    const __grid_constant__ StepTcArgs y, const __grid_constant__ FlybEnvCfg cfg) {
   __shared__ ActTables tab;
   __shared__ StepTables stab;
+  __shared__ __align__(8) uint64_t aux_done_bar;
+  if (threadIdx.x == 0) {   // every other thread passes forward_persistent's opening __syncthreads() before using it
+    tc::mbar_init(&aux_done_bar, 1);
+    tc::fence_mbar_init();
+  }
   const ActTcArgs& x = y.act;
   StepFinal fin;
+  fin.aux_done = &aux_done_bar; fin.tiles_handed = 0u;
   fin.noise = x.noise; fin.seed = x.seed;
   fin.draw = x.offset + (x.offset_dev ? __ldg(x.offset_dev) : 0ull);
   fin.action = x.action; fin.logp = x.logp; fin.mu_out = x.mu_out; fin.obs_store = x.obs_store;
