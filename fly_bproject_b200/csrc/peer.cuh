@@ -140,7 +140,10 @@ FLYB_D void peer_wait_all(const PeerView& pv, uint32_t want) {
 // slot on every rank and then polls the same quad of every rank's slot in its OWN buffer, adding them in rank order:
 // the latency is one NVLink crossing, where push + system fence + flag + poll pays three.  Nothing here waits for
 // another thread of this grid, and what a thread waits for is stored by the peers' threads of the same index before
-// THEY wait: no dead-lock however the grids are scheduled.  Slots are double-buffered by epoch parity and a rank's next
+// THEY wait: no dead-lock AS LONG AS the whole reducing grid is resident on every rank (every CTA then pushes before
+// it waits, in whatever order CTAs are dispatched).  A grid larger than the GPU holds could fill the machine with CTAs
+// that wait for peers' CTAs not yet scheduled: flyb_ppo_step_dp checks residency (tc_ppo_exchange_resident) and runs
+// the split exchange otherwise; SMs taken by other clients of the GPU are beyond that check.  Slots are double-buffered by epoch parity and a rank's next
 // reducing kernel starts only after this one has ended on that rank (stream order), so a rank can be at most one
 // exchange ahead and never overwrites words a peer still has to read.  Twice the bytes of the float slots.
 FLYB_D unsigned long long ll_pack(float v, uint32_t tag) {

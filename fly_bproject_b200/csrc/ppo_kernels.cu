@@ -569,9 +569,12 @@ extern "C" int flyb_ppo_step_dp(const FlybNetLayout* net, const FlybPpoCfg* cfg,
                                 float* exp_avg, float* exp_avg_sq, int64_t* step, float grad_scale, float* grad_norm_out,
                                 void* workspace, const FlybPeerGroup* peers, void* stream) {
   FLYB_REQUIRE(peers, "flyb_ppo_step_dp: NULL peer group");
-  if (!wpack || !tc_ppo_supported(net)) {   // CUDA-core gradient: the two halves as they are (whole-buffer exchange)
-    int rc0 = flyb_ppo_grad(net, cfg, params, nullptr, obs, action, old_logp, target, advantage, action_var, rows, grad,
-                            loss, workspace, peers, stream);
+  const bool tc = wpack && tc_ppo_supported(net);
+  // CUDA-core gradient, or a GPU too small to hold the fused exchange's reducing grid all at once (its CTAs wait for
+  // the peers' CTAs of the same index: not resident = possible dead-lock): the two halves as they are (split exchange)
+  if (!tc || !tc_ppo_exchange_resident(net)) {
+    int rc0 = flyb_ppo_grad(net, cfg, params, tc ? wpack : nullptr, obs, action, old_logp, target, advantage, action_var,
+                            rows, grad, loss, workspace, peers, stream);
     if (rc0 != FLYB_OK) return rc0;
     return flyb_ppo_apply(net, cfg, params, grad, exp_avg, exp_avg_sq, step, grad_scale, grad_norm_out, workspace, wpack,
                           peers, stream);

@@ -1431,6 +1431,25 @@ int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* pa
   return FLYB_OK;
 }
 
+// The fused exchange makes CTA c of ppo_reduce_tc_kernel<2, *> wait for the words CTA c of every peer's grid pushes.
+// That cannot dead-lock only if, on every rank, the whole grid is resident at once (then every CTA pushes before it
+// waits, whatever order the hardware dispatches them in).  With a grid larger than the GPU holds, two ranks that
+// dispatch their CTAs in different orders could each fill the machine with CTAs waiting for peers' CTAs that are not
+// scheduled yet.  True on B200 for both compiled shapes (272 / 370 CTAs against 148 SMs x several CTAs); the check keeps
+// it true on a smaller part.  It cannot see SMs held by OTHER work (MPS clients, a concurrent stream of the caller's).
+bool tc_ppo_exchange_resident(const FlybNetLayout* net) {
+  static const int resident = [] {
+    int per_sm = 0, per_sm_adam = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tcb::ppo_reduce_tc_kernel<2, false>, tcb::RED_QUADS * tcb::RED_GROUPS, 0) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_adam, tcb::ppo_reduce_tc_kernel<2, true>, tcb::RED_QUADS * tcb::RED_GROUPS, 0) != cudaSuccess) {
+      cudaGetLastError();
+      return 0;
+    }
+    return std::min(per_sm, per_sm_adam) * num_sms();
+  }();
+  return (net->total + tcb::RED_ELEMS - 1) / tcb::RED_ELEMS <= resident;
+}
+
 }  // namespace FLYB_TC_VNS
 
 }  // namespace flyb

@@ -30,6 +30,7 @@ struct StepFuse;
   namespace NS {                                                                                                         \
   bool tc_ppo_supported(const FlybNetLayout* net);                                                                       \
   size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows);                                               \
+  bool tc_ppo_exchange_resident(const FlybNetLayout* net);                                                               \
   int tc_ppo_grad(const FlybNetLayout* net, const FlybPpoCfg* cfg, const float* params, const void* wpack,              \
                   const float* obs, const float* action, const float* old_logp, const float* target,                     \
                   const float* advantage, const float* action_var, long long rows, float* grad, float* loss,             \
@@ -52,6 +53,10 @@ inline bool tc_supported(const FlybNetLayout* net) { return tcn::tc_supported(ne
 inline bool tc_ppo_supported(const FlybNetLayout* net) { return tcn::tc_ppo_supported(net) || tcw::tc_ppo_supported(net); }
 inline size_t tc_ppo_workspace_bytes(const FlybNetLayout* net, long long rows) {
   return tcn::tc_ppo_supported(net) ? tcn::tc_ppo_workspace_bytes(net, rows) : tcw::tc_ppo_workspace_bytes(net, rows);
+}
+// the fused gradient exchange's reducing grid fits the GPU all at once (it must: see ppo_kernels_tc.cu)
+inline bool tc_ppo_exchange_resident(const FlybNetLayout* net) {
+  return tcn::tc_ppo_supported(net) ? tcn::tc_ppo_exchange_resident(net) : tcw::tc_ppo_exchange_resident(net);
 }
 template <class... Args>
 inline int tc_ppo_grad(const FlybNetLayout* net, Args... args) {

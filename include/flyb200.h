@@ -281,8 +281,9 @@ int flyb_gae(const float* reward, const float* values, const int64_t* reset_last
  *   (bit-identical on every rank), writes `grad` and its share of the squared norm; clip + Adam follow with no norm
  *   kernel: 4 launches, as on one GPU.  One NVLink crossing of latency.  Measured per optimiser step of 32 768 samples
  *   per rank: 138.9 us at 2 GPUs against 138.4 us on one (split form 148.5); 144.3 at 8 GPUs against 137.8 (split 151.6).
- *   A thread waits only for the peers' threads of the same index, which store before THEY wait: no dead-lock however
- *   the grids are scheduled.
+ *   A thread waits only for the peers' threads of the same index, which store before THEY wait: no dead-lock as long
+ *   as the reducing grid (272 / 370 CTAs) is resident all at once on every rank — flyb_ppo_step_dp checks that against
+ *   the device's occupancy and runs the SPLIT form otherwise; do not share the GPU with other long-running kernels.
  * SPLIT (flyb_ppo_grad + flyb_ppo_apply; what a caller with its own work between the halves uses):
  *   flyb_ppo_grad  : its last kernel (the fixed-order reduction of the per-CTA partial gradients) stores every
  *                    gradient entry straight into slot [epoch & 1][rank] of EVERY rank's buffer (posted NVLink
