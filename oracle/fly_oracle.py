@@ -94,13 +94,17 @@ def reward_reset(obs: Tensor, reset_buf: Tensor, progress_buf: Tensor, actions: 
                  leg_tip_ids: Tensor, action_idx: Tensor, upper: Tensor, lower: Tensor, num_actions: int,
                  up_weight: float, heading_weight: float, actions_cost_scale: float, energy_cost_scale: float,
                  joints_at_limit_cost_scale: float, termination_height: float, termination_height_up: float,
-                 death_cost: float, max_episode_length: float, walking: bool) -> Tuple[Tensor, Tensor]:
+                 death_cost: float, max_episode_length: float, walking: bool,
+                 walking_leg_term: bool = True) -> Tuple[Tensor, Tensor]:
     """reference fly.py:685-768 (compute_fly_reward2).
 
     ``walking=False`` is the live standing total (fly.py:750).  ``walking=True`` is the commented-out
-    walking total of fly.py:747-748 plus the leg term the report (p.7) includes — pinned by executing the reference's
-    function with those two lines switched back on (ref_harness.load_walking_reward, tests/test_oracle_vs_reference.py,
-    fixture tests/golden/env_walking_d18_a18_n211.npz).
+    walking total of fly.py:747-748 — pinned by executing the reference's function with those two lines switched back on
+    (ref_harness.load_walking_reward, tests/test_oracle_vs_reference.py).  Inside that dead line the leg term is
+    commented out once more (``#+ leg_ground_reward``): ``walking_leg_term=True`` (default; what the CUDA kernels
+    compute) re-enables it too, an interpretation that follows BASELINE.json configs[2] / the report (p.7), fixture
+    tests/golden/env_walking_d18_a18_n211.npz; ``walking_leg_term=False`` is the literal un-commenting, fixture
+    env_walking_literal_d18_a18_n211.npz.
     """
     n = obs.shape[0]
     height = obs[:, 0]
@@ -135,7 +139,9 @@ def reward_reset(obs: Tensor, reset_buf: Tensor, progress_buf: Tensor, actions: 
     if walking:
         total = progress_reward * 2 + alive_reward + up_reward * orient_reward + heading_reward - \
             actions_cost_scale * actions_cost - energy_cost_scale * electricity_cost - \
-            at_limit * joints_at_limit_cost_scale + legs
+            at_limit * joints_at_limit_cost_scale
+        if walking_leg_term:
+            total = total + legs
     else:
         total = alive_reward + up_reward * orient_reward - energy_cost_scale * electricity_cost - \
             at_limit * joints_at_limit_cost_scale + legs
@@ -242,7 +248,7 @@ def apply_reset(t: EnvTables, s: EnvState) -> Tensor:
 
 
 def post_physics(t: EnvTables, s: EnvState, walking: bool = False,
-                 energy_cost_scale: float = ENERGY_COST_SCALE) -> None:
+                 energy_cost_scale: float = ENERGY_COST_SCALE, walking_leg_term: bool = True) -> None:
     """reference fly.py:676-681 → get_obs (397-411), progress += 1 (678), get_reward (413-443).
     ``energy_cost_scale``: 0.005 (fly.py:47) or 1 for the low-gravity variant (flyLowGrav.py:44)."""
     n, d = t.num_envs, t.num_dof
@@ -257,7 +263,7 @@ def post_physics(t: EnvTables, s: EnvState, walking: bool = False,
         s.obs_buf, s.reset_buf, s.progress_buf, s.actions.view(n, -1), s.potentials, s.prev_potentials,
         s.root[:, 3:7], s.force, t.abdomen_ids, t.leg_tip_ids, t.action_idx_one, t.upper, t.lower, t.num_act,
         UP_WEIGHT, HEADING_WEIGHT, ACTIONS_COST_SCALE, energy_cost_scale, JOINTS_AT_LIMIT_COST_SCALE,
-        TERMINATION_HEIGHT, TERMINATION_HEIGHT_UP, DEATH_COST, MAX_EPISODE_LENGTH, walking)
+        TERMINATION_HEIGHT, TERMINATION_HEIGHT_UP, DEATH_COST, MAX_EPISODE_LENGTH, walking, walking_leg_term)
     s.reward_buf[:], s.reset_buf[:] = rew, reset
 
 

@@ -97,20 +97,27 @@ def load_fly_lowgrav():
     return _lowgrav
 
 
-_walking = None
+_walking = {}
 
 
-def load_walking_reward():
+def load_walking_reward(leg_term: bool = True):
     """``compute_fly_reward2`` with the reference's OWN commented-out walking total switched back on.
 
-    reference fly.py:747-748 keeps the walking total as two ``#`` lines (its trailing ``#+ leg_ground_reward`` is the leg
-    term BASELINE.json configs[2] names); fly.py:750 is the live standing total.  The function's source is taken from
-    the reference file as it lies, the ``#`` in front of those two lines (and of the leg term) is removed, the standing
-    total line is dropped, and the result is compiled by ``torch.jit.script`` in the reference module's own namespace —
-    every other line of the function runs as written.  Returns the scripted function.
+    reference fly.py:747-748 keeps the walking total as two ``#`` lines; fly.py:750 is the live standing total.  The
+    function's source is taken from the reference file as it lies, the ``#`` in front of those two lines is removed, the
+    standing total line is dropped, and the result is compiled by ``torch.jit.script`` — every other line of the function
+    runs as written.  Returns the scripted function.
+
+    Two readings, both pinned (fixtures env_walking_d18_a18_n211.npz / env_walking_literal_d18_a18_n211.npz):
+    ``leg_term=False`` is the LITERAL un-commenting: inside the dead line the author had commented the leg term out once
+    more (``#+ leg_ground_reward``), so as written the walking total has no leg term.
+    ``leg_term=True`` (what ``walking=True`` means in the oracle and in the CUDA kernels) also re-enables that nested
+    ``#+ leg_ground_reward``.  This is an INTERPRETATION, not code the reference can execute as written: it follows
+    BASELINE.json configs[2] / the project report (p.7), which list the leg-contact term in the walking reward, and the
+    live standing total (fly.py:750), which does add it.
     """
     global _walking
-    if _walking is None:
+    if leg_term not in _walking:
         load_fly()                                          # stubs in place, reference importable
         with open(os.path.join(REFERENCE_ROOT, "fly.py")) as f:
             lines = f.read().split("\n")
@@ -122,7 +129,11 @@ def load_walking_reward():
             if st.startswith("#total_reward = progress_reward * 2"):
                 out.append("    " + st[1:]); seen += 1
             elif st.startswith("#") and "actions_cost_scale * actions_cost" in st and seen == 1:
-                out.append("        " + st[1:].strip().replace("#+ leg_ground_reward", "+ leg_ground_reward")); seen += 1
+                cont = st[1:].strip()
+                if "#+ leg_ground_reward" not in cont:
+                    raise RuntimeError("reference fly.py:748 does not end in the nested '#+ leg_ground_reward'")
+                cont = cont.replace("#+ leg_ground_reward", "+ leg_ground_reward" if leg_term else "")
+                out.append("        " + cont.rstrip()); seen += 1
             elif st.startswith("total_reward = alive_reward + up_reward * orient_reward") and seen == 2:
                 seen += 1                                   # the standing total (fly.py:750) gives way
             else:
@@ -140,8 +151,8 @@ def load_walking_reward():
         spec = importlib.util.spec_from_file_location("fly_walking_total", path)
         mod = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(mod)
-        _walking = torch.jit.script(mod.compute_fly_reward_walking)
-    return _walking
+        _walking[leg_term] = torch.jit.script(mod.compute_fly_reward_walking)
+    return _walking[leg_term]
 
 
 def load_ppo(env_cls):

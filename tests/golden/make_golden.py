@@ -233,6 +233,11 @@ def main():
         save("env_walking_d18_a18_n211.npz",
              env_case(fly, "limited_18", 211, True, 515, 0.2, reward_fn=ref_harness.load_walking_reward()))
         return
+    if "--walking-literal-only" in sys.argv:   # later addition, same rule: the literal un-commenting (no leg term); same
+        lit = env_case(fly, "limited_18", 211, True, 515, 0.2,   # inputs as env_walking_d18_a18_n211.npz, outputs only
+                       reward_fn=ref_harness.load_walking_reward(leg_term=False))
+        save("env_walking_literal_d18_a18_n211.npz", {k: lit[k] for k in ("reward", "reset", "potentials_in")})
+        return
     save("env_lowgrav_d18_a18_n193.npz", lowgrav_case(ref_harness.load_fly_lowgrav(), "limited_18", 193, True, 2024, 0.25))
     save("env_walking_d18_a18_n211.npz",
          env_case(fly, "limited_18", 211, True, 515, 0.2, reward_fn=ref_harness.load_walking_reward()))

@@ -50,6 +50,25 @@ def test_walking_total_matches_reference_golden():
     assert 0.5 < float(progress2.abs().max()) < 8.0          # the term is there, at a live rollout's scale
 
 
+def test_walking_total_literal_reading_matches_reference_golden():
+    """The same inputs, the LITERAL un-commenting of fly.py:747-748 (the nested `#+ leg_ground_reward` stays a comment):
+    fixture env_walking_literal_d18_a18_n211.npz against the oracle with `walking_leg_term=False`.  Keeps both readings
+    of the dead line pinned (the default one, with the leg term, is an interpretation: oracle/ref_harness.py)."""
+    g, lit = load_golden("env_walking_d18_a18_n211.npz"), load_golden("env_walking_literal_d18_a18_n211.npz")
+    assert torch.equal(lit["potentials_in"], g["potentials_in"])        # same inputs as the other fixture
+    n = 211
+    t = oracle_tables("limited_18", n, True)
+    s = fo.EnvState(t)
+    s.root, s.dof_states, s.force = g["root"].clone(), g["dof_states"].clone(), g["force"].clone()
+    s.progress_buf, s.reset_buf = g["progress_in"].clone(), g["reset_in"].clone()
+    s.potentials = g["potentials_in"].clone()
+    s.actions, _ = fo.scale_actions(t, g["actions_in"])
+    fo.post_physics(t, s, walking=True, walking_leg_term=False)
+    torch.testing.assert_close(s.reward_buf, lit["reward"], rtol=1e-6, atol=1e-6)
+    assert torch.equal(s.reset_buf, lit["reset"]) and torch.equal(lit["reset"], g["reset"])
+    assert not torch.equal(lit["reward"], g["reward"])                   # the leg term is what separates them
+
+
 def _params(g, tag="w0"):
     return {k: g[f"{tag}/{k}"].clone() for k in fo.PARAM_ORDER}
 

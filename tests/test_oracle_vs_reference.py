@@ -66,12 +66,15 @@ def test_env_oracle_equals_executed_reference(asset, n, full, seed, variant):
     assert 0 < int(reset.sum()) < n
 
 
+@pytest.mark.parametrize("leg_term", [True, False])
 @pytest.mark.parametrize("asset,n,full,seed", [("limited_18", 513, True, 41), ("full_42", 97, True, 42)])
-def test_walking_total_equals_the_references_commented_out_line_executed(asset, n, full, seed):
+def test_walking_total_equals_the_references_commented_out_line_executed(asset, n, full, seed, leg_term):
     """configs[2]'s reward: the oracle's `walking=True` branch against compute_fly_reward2 with the reference's own
-    commented-out total (fly.py:747-748, leg term included) switched back on (ref_harness.load_walking_reward)."""
+    commented-out total (fly.py:747-748) switched back on (ref_harness.load_walking_reward) — in both readings: with the
+    nested `#+ leg_ground_reward` re-enabled as well (an interpretation, the oracle's and the kernels' default) and as
+    the literal un-commenting, which leaves the leg term out."""
     mod = ref_harness.load_fly()
-    walking = ref_harness.load_walking_reward()
+    walking = ref_harness.load_walking_reward(leg_term=leg_term)
     t = oracle_tables(asset, n, full)
     st = fo.synth_state(t, seed)
     g = torch.Generator().manual_seed(seed + 1)
@@ -87,12 +90,22 @@ def test_walking_total_equals_the_references_commented_out_line_executed(asset, 
     s.root, s.dof_states, s.force = st["root"].clone(), st["dof_states"].clone(), st["force"].clone()
     s.progress_buf, s.reset_buf, s.potentials = st["progress"].clone(), reset_prev.clone(), potentials.clone()
     s.actions = scaled
-    fo.post_physics(t, s, walking=True)
+    fo.post_physics(t, s, walking=True, walking_leg_term=leg_term)
     assert torch.equal(s.reset_buf, reset) and torch.equal(reset, reset_standing)
     # same operations in the same order on the same obs: the totals agree to the last bit or one rounding
     torch.testing.assert_close(s.reward_buf, rew, rtol=1e-6, atol=1e-6)
     live = reset == 0
     assert float((rew - rew_standing)[live].abs().max()) > 1.0      # it IS a different total (progress term)
+    # the two readings differ by exactly the leg-contact term (0.1 per leg tip on the ground, fly.py:744) on live envs
+    other = ref_harness.load_walking_reward(leg_term=not leg_term)(
+        obs, reset_prev.clone(), progress, scaled.view(n, -1), 0.75, 0.5, pot, prev, 0.005, 0.005, 0.1, 1.1, 6, -2.0,
+        1500, t.action_idx_one, t.upper, t.lower, n, st["root"][:, 3:7], a, st["force"], t.abdomen_ids, t.leg_tip_ids)[0]
+    legs = obs[:, 13 + 3 * a:19 + 3 * a].sum(dim=1) * 0.1
+    alive = rew != -2.0
+    sign = 1.0 if leg_term else -1.0
+    # (this test's previous potentials are random, so the totals are O(1e5): an ulp there is 0.0078)
+    torch.testing.assert_close((rew - other)[alive], sign * legs[alive], rtol=0, atol=0.02)
+    assert float(legs[alive].max()) > 0.0
 
 
 def _reference_agent(n, o, a):
