@@ -71,11 +71,23 @@ FLYB_HD Quat env_torso_quat(const float* root, const FlybEnvCfg& c) {
   const Quat isr = {c.inv_start_rot[0], c.inv_start_rot[1], c.inv_start_rot[2], c.inv_start_rot[3]};
   return quat_mul(q, isr);
 }
+// |v|^2 the way torch's CPU norm forms it (fly.py:781): every product and every sum rounded on its own.  nvcc would
+// contract x*x + y*y into an FMA, which moves the potential (O(6e4), ulp 2^-8) by an ulp in ~10 % of the envs — and the
+// walking total holds 2 * (potential - previous potential).  With this form the golden potentials are reproduced bit
+// for bit (sqrt and the division by dt are IEEE-exact on both sides).  Host builds use -ffp-contract=off.
+FLYB_HD float sumsq3_rn(float x, float y, float z) {
+#ifdef __CUDA_ARCH__
+  return __fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z));
+#else
+  const float a = x * x, b = y * y, c = z * z;
+  return (a + b) + c;
+#endif
+}
 // potential, compute_heading_and_up (fly.py:778-783, 789-790)
 FLYB_HD void env_head_heading(const float* root, const FlybEnvCfg& c, const Quat& tq, EnvObsHead& o) {
   const Vec3 pos = {root[0], root[1], root[2]};
   Vec3 tt = {c.target[0] - pos.x, c.target[1] - pos.y, 0.0f};
-  const float nrm = sqrtf(tt.x * tt.x + tt.y * tt.y + tt.z * tt.z);
+  const float nrm = sqrtf(sumsq3_rn(tt.x, tt.y, tt.z));
   o.potential = -nrm / c.dt;
   const float nc = fmaxf(nrm, 1e-9f);
   const Vec3 dir = {tt.x / nc, tt.y / nc, tt.z / nc};

@@ -87,14 +87,14 @@ def test_whole_config_rollout_gae_and_one_minibatch_step(asset, full, walking, n
             assert_obs_close(env.obs_buf.cpu(), s.obs_buf, a_dim, atol=SCALED_ACTION_ATOL)
             torch.testing.assert_close(env.dof_targets.cpu(), targets, rtol=1e-5, atol=SCALED_ACTION_ATOL)
             rerr = (env.reward_buf.cpu() - s.reward_buf).abs()
-            roff = rerr > (0.016 if walking else ATOL_ENV) + RTOL_ENV * s.reward_buf.abs()
+            roff = rerr > ATOL_ENV + RTOL_ENV * s.reward_buf.abs()
             assert int(roff.sum()) <= max(1, n // 100000), f"{int(roff.sum())} rewards off at step {i}"
     ring[horizon] = s.obs_buf
     torch.cuda.synchronize()
     torch.testing.assert_close(agent.action_var.cpu(), var, rtol=1e-6, atol=0)
     got_rew = agent.all_reward.cpu()
     err = (got_rew - rews).abs()
-    off = err > (0.016 if walking else ATOL_ENV) + RTOL_ENV * rews.abs()
+    off = err > ATOL_ENV + RTOL_ENV * rews.abs()
     assert float(off.float().mean()) <= 1e-5, f"{int(off.sum())} rewards off"
     if off.any():      # threshold flips of the joints-at-limit count: whole multiples of 0.1
         steps = err[off] / 0.1

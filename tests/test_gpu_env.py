@@ -39,7 +39,7 @@ def test_env_kernels_match_reference_golden(name, asset, n, full):
     assert env.reset_buf.dtype == torch.int64 and env.progress_buf.dtype == torch.int64
     assert_obs_close(env.obs_buf.cpu(), g["obs"], env.num_act)
     torch.testing.assert_close(env.reward_buf.cpu(), g["reward"], rtol=RTOL_ENV, atol=ATOL_ENV)
-    torch.testing.assert_close(env.potentials.cpu(), g["potentials"], rtol=1e-6, atol=0)
+    assert torch.equal(env.potentials.cpu(), g["potentials"])                 # bit-exact (env_math.cuh: sumsq3_rn)
     assert torch.equal(env.prev_potentials.cpu(), g["prev_potentials"])
     torch.testing.assert_close(env.up_vec.cpu(), g["up_vec"], rtol=RTOL_ENV, atol=ATOL_ENV)
     torch.testing.assert_close(env.heading_vec.cpu(), g["heading_vec"], rtol=RTOL_ENV, atol=ATOL_ENV)
@@ -86,11 +86,11 @@ def test_env_step_matches_oracle(n, asset, full, walking):
     assert torch.equal(env.reset_buf.cpu(), s.reset_buf)
     assert torch.equal(env.progress_buf.cpu(), s.progress_buf)
     assert_obs_close(env.obs_buf.cpu(), s.obs_buf, env.num_act)
-    # walking total holds 2*(pot - prev_pot), a difference of O(6e4) potentials: one ulp of the potential (2^-8) is
-    # 0.0078 in the reward; the potentials themselves are held to 1e-6 relative just below
-    torch.testing.assert_close(env.reward_buf.cpu(), s.reward_buf, rtol=RTOL_ENV, atol=0.016 if walking else ATOL_ENV)
-    torch.testing.assert_close(env.potentials.cpu(), s.potentials, rtol=1e-6, atol=0)
-    torch.testing.assert_close(env.prev_potentials.cpu(), s.prev_potentials, rtol=1e-6, atol=0)
+    # the walking total holds 2*(pot - prev_pot), a difference of O(6e4) potentials: they are bit-exact (just below), so
+    # the walking reward is held to the same bar as the standing one
+    torch.testing.assert_close(env.reward_buf.cpu(), s.reward_buf, rtol=RTOL_ENV, atol=ATOL_ENV)
+    assert torch.equal(env.potentials.cpu(), s.potentials)
+    assert torch.equal(env.prev_potentials.cpu(), s.prev_potentials)
     torch.testing.assert_close(env.dof_targets.cpu(), targets, rtol=1e-6, atol=1e-6)
     want_ids = s.reset_buf.nonzero().squeeze(-1).to(torch.int32)
     cnt = int(env.reset_count.item())
@@ -189,8 +189,8 @@ def test_lowgrav_variant_matches_reference_golden():
     assert torch.equal(env.progress_buf.cpu(), g["progress"])
     assert_obs_close(env.obs_buf.cpu(), g["obs"], env.num_act)
     torch.testing.assert_close(env.reward_buf.cpu(), g["reward"], rtol=RTOL_ENV, atol=ATOL_ENV)
-    torch.testing.assert_close(env.potentials.cpu(), g["potentials"], rtol=1e-6, atol=0)
-    torch.testing.assert_close(env.prev_potentials.cpu(), g["prev_potentials"], rtol=1e-6, atol=0)
+    assert torch.equal(env.potentials.cpu(), g["potentials"])
+    assert torch.equal(env.prev_potentials.cpu(), g["prev_potentials"])
     want_ids = g["reset"].nonzero().squeeze(-1).to(torch.int32)
     cnt = int(env.reset_count.item())
     assert cnt == want_ids.numel() and torch.equal(env.reset_ids[:cnt].cpu(), want_ids)
@@ -211,9 +211,8 @@ def test_walking_total_matches_reference_golden():
     torch.cuda.synchronize()
     assert torch.equal(env.reset_buf.cpu(), g["reset"])
     assert_obs_close(env.obs_buf.cpu(), g["obs"], env.num_act)
-    torch.testing.assert_close(env.potentials.cpu(), g["potentials"], rtol=1e-6, atol=0)
-    # 2 * (potential - previous): the potentials are O(6e4), one ulp there is 2^-8, so the total carries 2 * 2 ulps
-    torch.testing.assert_close(env.reward_buf.cpu(), g["reward"], rtol=RTOL_ENV, atol=0.016)
+    assert torch.equal(env.potentials.cpu(), g["potentials"])    # bit-exact, so 2 * (potential - previous) is exact too
+    torch.testing.assert_close(env.reward_buf.cpu(), g["reward"], rtol=RTOL_ENV, atol=ATOL_ENV)
     live = g["reset"] == 0
     err = (env.reward_buf.cpu() - g["reward"])[live].abs()
     assert float(err.median()) <= 1e-5                           # typical env: no ulp flips at all
@@ -241,5 +240,5 @@ def test_reset_method_resets_flagged_envs():
     assert torch.equal(env.progress_buf.cpu(), s.progress_buf)
     assert torch.equal(env.state.root.cpu(), s.root)
     torch.testing.assert_close(env.state.dof_state.cpu(), s.dof_states, rtol=1e-6, atol=1e-7)
-    torch.testing.assert_close(env.potentials.cpu(), s.potentials, rtol=1e-6, atol=0)
-    torch.testing.assert_close(env.prev_potentials.cpu(), s.prev_potentials, rtol=1e-6, atol=0)
+    assert torch.equal(env.potentials.cpu(), s.potentials)
+    assert torch.equal(env.prev_potentials.cpu(), s.prev_potentials)
