@@ -415,6 +415,8 @@ def run_own(args, cfg):
         "kernel": ("ppo_fwd_bwd_tc_kernel + ppo_dw_tc_kernel (+ ppo_reduce_tc_kernel, ppo_adam_kernel): one optimiser step"
                    if tc_path else "ppo_fwd_bwd_kernel + ppo_dw_kernel (+ reduce, norm, Adam): one optimiser step"),
         "traffic": traffic.get("ppo_minibatch_step"),
+        "traffic_source": ("profiles/traffic.json <- " + str(traffic.get("_source", "profiles/r03_hot_metrics.txt")) +
+                           " (one ncu --set full capture, not measured by this run)") if traffic else None,
         "algorithmic_per_launch": {"flops": wm["flops_update"] * rows_mb, "samples": rows_mb},
         "share_of_bench_step": n_minibatches * kt["ppo_minibatch_step"] / iter_ms,
         "peak_source": pk["tf_src"] + " (bf16 sustained: timed inside a long step)"})
@@ -491,6 +493,29 @@ def run_own(args, cfg):
     d2h_bytes = sum(v.numel() * v.element_size() for v in back.values())
     e2e_value = n * ke * world / (e2e_ms * 1e-3)
 
+    # N > 1: a correctness bit for the data-parallel update.  After the timed iterations every rank must hold the same
+    # parameters and Adam state (the gradient sum is the only thing the ranks share) and no exchange may have timed out.
+    dp_check = None
+    if world > 1:
+        torch.cuda.synchronize()
+
+        def digest(t):      # position-weighted sum of the raw bits, mod 2^64
+            bits = t.contiguous().view(torch.int32).to(torch.int64)
+            return (bits * torch.arange(1, bits.numel() + 1, device=bits.device, dtype=torch.int64)).sum()
+
+        status = agent._peers.status() if agent._peers is not None else 0
+        mine = torch.stack([digest(agent.net.flat), digest(agent.exp_avg), digest(agent.exp_avg_sq),
+                            torch.tensor(int(status), dtype=torch.int64, device=dev),
+                            torch.tensor(int(agent.optim_step), dtype=torch.int64, device=dev)])
+        everyone = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(everyone, mine)
+        everyone = torch.stack(everyone).cpu()
+        dp_check = {"identical": bool((everyone[:, [0, 1, 2, 4]] == everyone[0, [0, 1, 2, 4]]).all()),
+                    "peer_status": int(everyone[:, 3].max()), "optimiser_steps": int(everyone[0, 4]),
+                    "finite": bool(torch.isfinite(agent.net.flat).all()),
+                    "what": "64-bit checksums of parameters, exp_avg, exp_avg_sq and the step count all-gathered after "
+                            "the timed region: equal on every rank; sticky peer-exchange error word 0 on every rank"}
+
     if rank == 0:
         if env.state.pool_bytes > 126e6:
             l2 = (f"inputs larger than L2: pool of {pool} synthetic states = {env.state.pool_bytes / 1e6:.0f} MB, rotated "
@@ -537,10 +562,15 @@ def run_own(args, cfg):
                 "sample": f"iteration composed from bounded samples (oracle/ref_bench.py): 12 PPO.run() calls "
                           f"({res['t_env_step_s'] * 1e3:.1f} ms median), one make_data ({res['t_make_data_s']:.2f} s), "
                           f"5 optimiser steps of {rows_mb} samples ({res['t_minibatch_s']:.3f} s each) x {n_minibatches}"}
+        if dp_check is not None:
+            line["dp_check"] = dp_check
         print(json.dumps(line), flush=True)
     if world > 1:
         agent.exit()            # unmaps the peers' exchange buffers (collective)
         dist.destroy_process_group()
+        if not (dp_check["identical"] and dp_check["peer_status"] == 0 and dp_check["finite"]):
+            print(f"bench.py: data-parallel check FAILED on rank {rank}: {dp_check}", file=sys.stderr)
+            sys.exit(3)
 
 
 def main():
