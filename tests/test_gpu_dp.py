@@ -147,3 +147,146 @@ def test_peer_exchange_soak(tmp_path):
             assert torch.equal(r[k], rs[0][k]), k
     assert bool(torch.isfinite(rs[0]["flat"]).all())
     print(f"soak: {rs[0]['steps']} exchanges x {world} ranks, parameters / Adam state bit-identical on every rank")
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The data-parallel CUDA step against the ORACLE: SURVEY.md §4 / §8(e) — "an N-shard step equals the reference
+# single-process step on the concatenated batch up to fp reassociation" (reference ppo.py:183-199 is the step).
+def _oracle_step_worker(rank, world, port, path, mode):
+    import ctypes as C
+    import torch.distributed as dist
+    import fly_bproject_b200 as fb
+    from fly_bproject_b200 import _lib, dp
+    from oracle import fly_oracle as fo
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    os.environ["FLYB_DP"] = "peer"
+    os.environ["FLYB_DP_TAIL"] = "0"
+    dev = f"cuda:{rank}"
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        d = torch.load(path)
+        o, a = d["obs"].shape[-1], d["acts"].shape[-1]
+        net = fb.Net(o, a, dev, init=False, tensor_cores=True)
+        net.load_state_dict(d["p0"])
+        assert net.wpack is not None
+        peers = dp.make_exchange(net.layout.total, torch.device(dev))
+        assert peers is not None, "peer exchange unavailable on this box"
+        n = d["obs"].shape[1]
+        lo, hi = rank * n // world, (rank + 1) * n // world            # this rank's envs of the minibatch
+        dv = [d[k][:, lo:hi].contiguous().to(dev) for k in ("obs", "acts", "logp", "target", "adv")]
+        var = d["var"].to(dev)
+        rows = dv[0].shape[0] * (hi - lo)
+        lib, p = _lib.lib(), _lib.ptr
+        cfg = _lib.PpoCfg(0.2, 1e-3, 0.9, 0.999, 1e-8, 1.0)
+        ws = torch.zeros(lib.flyb_ppo_workspace_bytes(C.byref(net.layout), rows) + 256, dtype=torch.uint8, device=dev)
+        wsp = (ws.data_ptr() + 255) // 256 * 256
+        grad, m, v = torch.zeros_like(net.flat), torch.zeros_like(net.flat), torch.zeros_like(net.flat)
+        loss, gn = torch.zeros(1, device=dev), torch.zeros(1, device=dev)
+        step = torch.zeros(1, dtype=torch.int64, device=dev)
+        st = _lib.current_stream()
+        if mode == "fused":
+            _lib.check(lib.flyb_ppo_step_dp(C.byref(net.layout), C.byref(cfg), p(net.flat), p(net.wpack), p(dv[0]),
+                                            p(dv[1]), p(dv[2]), p(dv[3]), p(dv[4]), p(var), rows, p(grad), p(loss), p(m),
+                                            p(v), p(step), 1.0 / world, p(gn), wsp, peers.byref(), st), "flyb_ppo_step_dp")
+        else:
+            _lib.check(lib.flyb_ppo_grad(C.byref(net.layout), C.byref(cfg), p(net.flat), p(net.wpack), p(dv[0]), p(dv[1]),
+                                         p(dv[2]), p(dv[3]), p(dv[4]), p(var), rows, p(grad), p(loss), wsp,
+                                         peers.byref(), st), "flyb_ppo_grad")
+            _lib.check(lib.flyb_ppo_apply(C.byref(net.layout), C.byref(cfg), p(net.flat), p(grad), p(m), p(v), p(step),
+                                          1.0 / world, p(gn), wsp, p(net.wpack), peers.byref(), st), "flyb_ppo_apply")
+        torch.cuda.synchronize()
+        views = lambda flat: {k: x.cpu().clone() for k, x in net.make_views(flat).items()}
+        torch.save({"w": {k: x.cpu() for k, x in net.state_dict().items()}, "m": views(m), "v": views(v),
+                    "g": views(grad), "flat": net.flat.cpu(), "loss": float(loss), "norm": float(gn),
+                    "step": int(step.item()), "status": peers.status()}, f"{path}.{mode}.{rank}")
+        peers.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def _minibatch(shape):
+    """(data dict, oracle results) of one optimiser step on the WHOLE minibatch."""
+    from oracle import fly_oracle as fo
+    from tests.helpers import load_golden
+    if shape == "narrow":       # the golden minibatch of the executed reference: rows [0:mc] of ppo_n64_t32.npz
+        g = load_golden("ppo_n64_t32.npz")
+        mc = int(g["meta"][2])
+        d = {"obs": g["roll_obs"][0:mc], "acts": g["roll_acts"][0:mc], "logp": g["roll_logp"][0:mc],
+             "target": g["roll_target"][0:mc], "adv": g["roll_adv"][0:mc], "var": g["roll_var"],
+             "p0": {k: g["w0/" + k].clone() for k in fo.PARAM_ORDER}}
+    else:                       # the 42-joint shape (O = 145, A = 42): seeded synthetic minibatch, 2 x 512 rows
+        o, a, t, n = 145, 42, 2, 512
+        gen = torch.Generator().manual_seed(77)
+        p0 = fo.init_params(o, a, seed=3)
+        obs = torch.randn(t, n, o, generator=gen)
+        var = torch.full((a,), 0.15)
+        with torch.no_grad():
+            mu = fo.pi(p0, obs.view(-1, o))
+        act = (mu + 0.4 * torch.randn(t * n, a, generator=gen)).clip(-1, 1)
+        old = fo.gaussian_logp(mu, act, var) + 0.3 * torch.randn(t * n, generator=gen)
+        ratio = torch.exp(fo.gaussian_logp(mu, act, var) - old)        # keep rows clear of the clip's discontinuity
+        old = torch.where(((ratio - 0.8).abs() < 1e-3) | ((ratio - 1.2).abs() < 1e-3), old + 0.05, old)
+        d = {"obs": obs, "acts": act.view(t, n, a), "logp": old.view(t, n),
+             "target": 2 * torch.randn(t, n, 1, generator=gen), "adv": torch.randn(t, n, 1, generator=gen), "var": var,
+             "p0": p0}
+    p1 = {k: x.clone() for k, x in d["p0"].items()}
+    st = fo.AdamState(p1)
+    o, a = d["obs"].shape[-1], d["acts"].shape[-1]
+    loss, norm, grads = fo.minibatch_step(p1, st, d["obs"].reshape(-1, o), d["acts"].reshape(-1, a),
+                                          d["logp"].reshape(-1), d["target"].reshape(-1, 1), d["adv"].reshape(-1, 1),
+                                          d["var"])
+    coef = min(1.0, 1.0 / (norm + 1e-6))
+    return d, {"w": p1, "m": st.m, "v": st.v, "g": {k: x * coef for k, x in grads.items()}, "graw": grads,
+               "loss": loss, "norm": norm}
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("shape,mode", [("narrow", "fused"), ("narrow", "split"), ("wide", "fused")])
+def test_data_parallel_step_matches_oracle_on_the_whole_minibatch(tmp_path, shape, mode):
+    """One flyb_ppo_step_dp (or flyb_ppo_grad + flyb_ppo_apply) per rank, each rank on ITS envs of a minibatch, against
+    the oracle's optimiser step on the whole minibatch — for the narrow shape the golden step of the executed
+    reference (w1 / m1 / v1 of ppo_n64_t32.npz).  Bars and the Adam-sign carve-out are those of the single-GPU test
+    (test_gpu_agent.py: test_ppo_minibatch_step_matches_reference_golden): 1e-4."""
+    from oracle import fly_oracle as fo
+    from tests.helpers import RTOL_PPO, load_golden
+    world = int(os.environ.get("FLYB_TEST_WORLD", "2"))
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} CUDA devices")
+    d, want = _minibatch(shape)
+    if shape == "narrow":       # the oracle's step IS the reference's: pin it to the fixture before using it as the bar
+        g = load_golden("ppo_n64_t32.npz")
+        for k in fo.PARAM_ORDER:
+            torch.testing.assert_close(want["w"][k], g["w1/" + k], rtol=1e-5, atol=1e-6)   # bar of test_oracle_golden.py
+    path = str(tmp_path / f"mb_{shape}.pt")
+    torch.save(d, path)
+    _spawn(_oracle_step_worker, world, path, mode)
+    rs = [torch.load(f"{path}.{mode}.{r}") for r in range(world)]
+    for r in rs:
+        assert r["status"] == 0 and r["step"] == 1
+        assert torch.equal(r["flat"], rs[0]["flat"])                       # every rank holds the same parameters
+        for k in fo.PARAM_ORDER:
+            assert torch.equal(r["m"][k], rs[0]["m"][k]) and torch.equal(r["v"][k], rs[0]["v"][k]), k
+    assert sum(r["loss"] for r in rs) / world == pytest.approx(want["loss"], rel=RTOL_PPO, abs=1e-6)
+    got = rs[0]
+    assert got["norm"] == pytest.approx(want["norm"], rel=1e-4)
+    ill, total = 0, 0
+    for k in fo.PARAM_ORDER:
+        gref = want["g"][k]
+        gmax = float(gref.abs().max())
+        torch.testing.assert_close(got["g"][k], gref, rtol=RTOL_PPO, atol=RTOL_PPO * gmax, msg="clipped grad " + k)
+        torch.testing.assert_close(got["m"][k], want["m"][k], rtol=RTOL_PPO,
+                                   atol=RTOL_PPO * float(want["m"][k].abs().max()), msg="exp_avg " + k)
+        torch.testing.assert_close(got["v"][k], want["v"][k], rtol=2 * RTOL_PPO,
+                                   atol=2 * RTOL_PPO * float(want["v"][k].abs().max()), msg="exp_avg_sq " + k)
+        # Adam's first step is +-lr wherever |g| >> eps: elements whose gradient is rounding noise of the row
+        # reduction (below 1e-4 of the tensor's largest) may land anywhere within +-lr — counted and bounded
+        well = gref.abs() > RTOL_PPO * gmax
+        err = (got["w"][k] - want["w"][k]).abs()
+        tol = 1e-6 + RTOL_PPO * want["w"][k].abs()
+        bad = (err > tol) & well
+        assert not bad.any(), f"param {k}: {int(bad.sum())} well-conditioned elements off, worst {float(err[well].max()):.3e}"
+        assert float(err[~well].max() if (~well).any() else 0.0) <= 2.0 * 1e-3 + 1e-6, "param " + k
+        ill += int(((err > tol) & ~well).sum())
+        total += err.numel()
+    assert ill <= 0.005 * total, f"{ill} near-zero-gradient elements moved differently"
