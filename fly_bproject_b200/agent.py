@@ -38,8 +38,10 @@ class Net:
     """
 
     def __init__(self, num_obs: int, num_act: int, device="cuda:0", init: bool = True, tensor_cores: bool = True):
-        """`tensor_cores`: run the GEMMs as 3xTF32 products on tcgen05 (where the shape is covered: num_obs <= 80,
-        num_act <= 32); False = the exact-fp32 CUDA-core kernels."""
+        """`tensor_cores`: run the GEMMs as 3xTF32 products on tcgen05 where a compiled shape covers the net
+        (flyb_wpack_bytes > 0): num_obs in (64, 80] with num_act <= 32 — forward, act, fused env step and the PPO
+        step — or anything else up to num_obs <= 160, num_act <= 48 — forward and act; the PPO step too when num_obs is
+        in (144, 160], the 42-joint set.  False, or a shape outside both = the exact-fp32 CUDA-core kernels."""
         self.lib = _lib.lib()
         self.device = torch.device(device)
         self.layout = _lib.NetLayout()
