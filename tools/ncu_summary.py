@@ -18,7 +18,19 @@ KEYS = [
     "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
     "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
     "smsp__cycles_active.avg", "sm__inst_executed_pipe_uniform.sum",
+    # shared memory / L2 / tensor pipe: what "smem-bound" and "issue-bound" claims rest on
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld.sum",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_st.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+    "smsp__inst_executed_op_shared_ld.sum", "smsp__inst_executed_op_shared_st.sum",
+    "lts__t_sector_hit_rate.pct", "lts__t_sectors_srcunit_tex_op_read.sum", "lts__t_sectors_srcunit_tex_op_write.sum",
+    "sm__inst_executed_pipe_tensor.sum", "sm__inst_executed_pipe_tensor_subpipe_hmma.sum",
+    "sm__inst_executed_pipe_lsu.sum", "sm__inst_executed_pipe_alu.sum", "sm__inst_executed_pipe_fma.sum",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__warps_eligible.avg.per_cycle_active",
 ]
+# warp-stall breakdown (WarpStateStats section of --set full): cycles a warp spends stalled for each reason per
+# instruction it issues; the summary prints the five largest
+STALL_PREFIXES = ("smsp__average_warps_issue_stalled_", "smsp__average_warp_latency_issue_stalled_",
+                  "smsp__pcsamp_warps_issue_stalled_")
 
 
 def launches(path):
@@ -53,6 +65,17 @@ def report(path):
             if k in hdr:
                 i = hdr.index(k)
                 print(f"    {k:70s} {r[i]:>18s} {units[i]}")
+        stalls = []
+        for i, h in enumerate(hdr):
+            if h.startswith(STALL_PREFIXES) and not h.endswith("_not_issued") and r[i] not in ("", "n/a"):
+                try:
+                    stalls.append((float(r[i].replace(",", "")), h, units[i]))
+                except ValueError:
+                    pass
+        for fam in STALL_PREFIXES:
+            top = sorted((x for x in stalls if x[1].startswith(fam)), reverse=True)[:5]
+            for v, h, u in top:
+                print(f"    stall  {h:63s} {v:18.3f} {u}")
 
 
 if __name__ == "__main__":
